@@ -1,0 +1,218 @@
+"""Host-side input builders for the shipped examples.
+
+Each builder returns a `Problem`: the energy-file name, the `dimensions` array and the flat
+`problemparams` list in the positions the energy file fixes, as host
+numpy arrays / scalars.  They restate what the reference's example drivers do before calling
+`Opt_ProblemSolve` (cited per function); synthetic builders follow SURVEY.md section 8(d).
+Nothing here computes: arrays are handed to the C-ABI library (device copies are made by
+`opt_b200.solver.OptSolver`) or, in tests, to the CPU oracle.
+"""
+from dataclasses import dataclass, field
+
+import numpy as np
+
+
+@dataclass
+class Problem:
+    energy: str                  # e.g. "image_warping.t"
+    dims: list                   # Opt_ProblemPlan dimensions
+    params: list                 # problemparams; np.ndarray | np.float32 scalar | None
+    unknowns: list               # indices into params that are unknown images
+    solver: dict = field(default_factory=dict)   # solver parameters (nIterations, lIterations, ...)
+    kind: str = "gaussNewtonGPU"
+    double: bool = False
+
+    def clone(self):
+        return Problem(self.energy, list(self.dims),
+                       [p.copy() if isinstance(p, np.ndarray) else p for p in self.params],
+                       list(self.unknowns), dict(self.solver), self.kind, self.double)
+
+    def as_double(self):
+        """opt_float images become double; Param(float) scalars and index/uint8 arrays stay
+        (o.t:2430)."""
+        q = self.clone()
+        q.double = True
+        q.params = [p.astype(np.float64) if isinstance(p, np.ndarray) and p.dtype == np.float32 else p
+                    for p in q.params]
+        return q
+
+
+# ---------------------------------------------------------------------------------------------
+def image_warping(mask, constraints, alpha=1.0, n_iter=1, l_iter=1):
+    """examples/image_warping/src/CombinedSolver.h:129-134 (weights), :165-197 (resetGPU),
+    :199-227 (setConstraintImage); main.cpp:157-177 (border pixels pinned)."""
+    H, W = mask.shape
+    maskf = mask.astype(np.float32)
+    ys, xs = np.mgrid[0:H, 0:W]
+    ur = np.stack([xs, ys], -1).astype(np.float32)
+    offset = ur.copy()
+    angle = np.full((H, W), 1e-5, dtype=np.float32)
+    cons = [list(c) for c in constraints]
+    for y in range(H):
+        for x in range(W):
+            if y == 0 or x == 0 or y == H - 1 or x == W - 1:
+                cons.append([x, y, x, y])
+    cimg = np.full((H, W, 2), -1.0, dtype=np.float32)
+    a = np.float32(alpha)
+    for x, y, tx, ty in cons:
+        if maskf[y, x] == 0:
+            cimg[y, x, 0] = (np.float32(1) - a) * np.float32(x) + a * np.float32(tx)
+            cimg[y, x, 1] = (np.float32(1) - a) * np.float32(y) + a * np.float32(ty)
+    w_fit, w_reg = np.sqrt(np.float32(100.0)), np.sqrt(np.float32(0.01))
+    return Problem("image_warping.t", [W, H], [offset, angle, ur, cimg, maskf, w_fit, w_reg], [0, 1],
+                   {"nIterations": n_iter, "lIterations": l_iter})
+
+
+def image_warping_golden(npz):
+    shape = tuple(npz["shape"])
+    is_zero = np.unpackbits(npz["mask_is_zero"])[: shape[0] * shape[1]].reshape(shape).astype(bool)
+    mask = np.where(is_zero, 0, 255).astype(np.uint8)
+    return image_warping(mask, npz["constraints"].tolist())
+
+
+def volumetric(bbox_min, bbox_max, grid=(5, 20, 5), n_iter=1, l_iter=1):
+    """examples/volumetric_mesh_deformation/src/CombinedSolver.h:47-51 (weights), :81-108
+    (setConstraints), :232-252 (initializeWarpGrid), :254-262 (bounding box + EPS).
+    The driver stores node (i,j,k) at i*(Dy+1)*(Dz+1) + j*(Dz+1) + k and passes dims
+    {Dx+1,Dy+1,Dz+1}; Opt reads d0 fastest, so the array is reproduced byte for byte."""
+    f32 = np.float32
+    gx, gy, gz = grid
+    eps = f32(0.000001)
+    mn = bbox_min.astype(f32) - eps
+    mx = bbox_max.astype(f32) + eps
+    delta = (mx - mn) / np.array([gx, gy, gz], dtype=f32)
+    ii, jj, kk = np.meshgrid(np.arange(gx + 1), np.arange(gy + 1), np.arange(gz + 1), indexing="ij")
+    fac = np.stack([ii, jj, kk], -1).astype(f32)
+    pos = (mn + fac * delta).astype(f32)                  # [i][j][k][3], k fastest
+    target = np.full(pos.shape, -np.inf, dtype=f32)
+    target[:, 0] = pos[:, 0]
+    ang = f32(np.deg2rad(np.float32(-90.0)))              # mLib matrix3x3.h:157-166 (degrees, ccw)
+    s, c = f32(np.sin(ang)), f32(np.cos(ang))
+    R = np.array([[c, -s, 0], [s, c, 0], [0, 0, 1]], dtype=f32)
+    mid = mn + np.array([gx / 2.0, float(gy), gz / 2.0], dtype=f32) * delta
+    v = pos[:, gy]
+    target[:, gy] = ((v - mid) @ R.T + mid + np.array([2.5, -2.5, 0.0], dtype=f32)).astype(f32)
+    n = (gx + 1) * (gy + 1) * (gz + 1)
+    offset = pos.reshape(n, 3).copy()
+    angle = np.zeros((n, 3), dtype=f32)
+    w_fit, w_reg = np.sqrt(f32(1.0)), np.sqrt(f32(0.05))
+    return Problem("volumetric_mesh_deformation.t", [gx + 1, gy + 1, gz + 1],
+                   [offset, angle, offset.copy(), target.reshape(n, 3), w_fit, w_reg], [0, 1],
+                   {"nIterations": n_iter, "lIterations": l_iter})
+
+
+def volumetric_golden(npz):
+    return volumetric(npz["bbox_min"], npz["bbox_max"], tuple(int(g) for g in npz["grid"]))
+
+
+# ---------------------------------------------------------------------------------------------
+# synthetic inputs of the BASELINE.json shapes, seed 1234
+def poisson_synthetic(W, H, seed=1234, n_iter=1, l_iter=100):
+    """X,T in U[0,255] (4 channels, w = 255), mask = 0 (unknown) inside a centred rectangle covering
+    50 % of the area, 255 elsewhere (examples/poisson_image_editing/src/CombinedSolver.h:79-82,
+    main.cpp:102-106)."""
+    rng = np.random.default_rng(seed)
+    X = rng.uniform(0, 255, (H, W, 4)).astype(np.float32)
+    T = rng.uniform(0, 255, (H, W, 4)).astype(np.float32)
+    X[..., 3] = 255
+    T[..., 3] = 255
+    M = np.full((H, W), 255, dtype=np.float32)
+    rw, rh = int(round(W * np.sqrt(0.5))), int(round(H * np.sqrt(0.5)))
+    x0, y0 = (W - rw) // 2, (H - rh) // 2
+    M[y0:y0 + rh, x0:x0 + rw] = 0
+    return Problem("poisson_image_editing.t", [W, H], [X, T, M], [0],
+                   {"nIterations": n_iter, "lIterations": l_iter})
+
+
+def image_warping_synthetic(W, H, seed=1234, n_iter=2, l_iter=10):
+    rng = np.random.default_rng(seed)
+    ys, xs = np.mgrid[0:H, 0:W]
+    mask = np.where(((xs - W / 2) ** 2 + (ys - H / 2) ** 2) < (0.45 * min(W, H)) ** 2, 0, 255).astype(np.uint8)
+    cons = []
+    for _ in range(8):
+        x, y = int(rng.integers(W // 4, 3 * W // 4)), int(rng.integers(H // 4, 3 * H // 4))
+        cons.append([x, y, x + int(rng.integers(-5, 6)), y + int(rng.integers(-5, 6))])
+    pr = image_warping(mask, cons, n_iter=n_iter, l_iter=l_iter)
+    pr.params[1] = (0.05 * rng.standard_normal((H, W))).astype(np.float32)          # non-trivial angles
+    pr.params[0] = (pr.params[0] + 0.3 * rng.standard_normal((H, W, 2))).astype(np.float32)
+    return pr
+
+
+def volumetric_synthetic(W, H, D, seed=1234, n_iter=2, l_iter=10):
+    """dims {W,H,D}; lattice in the unit-aspect box; plane d1==0 fixed, plane d1==H-1 rotated -90 deg
+    about z and shifted.  Angles get small random values in the test
+    variant so that the rotation derivatives are exercised."""
+    rng = np.random.default_rng(seed)
+    f32 = np.float32
+    kk, jj, ii = np.meshgrid(np.arange(D), np.arange(H), np.arange(W), indexing="ij")   # d0 fastest
+    pos = np.stack([ii, jj, kk], -1).astype(f32) / f32(max(W, H, D) - 1)
+    target = np.full(pos.shape, -np.inf, dtype=f32)
+    target[:, 0] = pos[:, 0]
+    R = np.array([[0, 1, 0], [-1, 0, 0], [0, 0, 1]], dtype=f32)
+    mid = np.array([0.5 * (W - 1), H - 1, 0.5 * (D - 1)], dtype=f32) / f32(max(W, H, D) - 1)
+    target[:, H - 1] = ((pos[:, H - 1] - mid) @ R.T + mid + np.array([0.25, -0.25, 0], dtype=f32)).astype(f32)
+    n = W * H * D
+    offset = (pos.reshape(n, 3) + 0.01 * rng.standard_normal((n, 3))).astype(f32)
+    angle = (0.05 * rng.standard_normal((n, 3))).astype(f32)
+    w_fit, w_reg = np.sqrt(f32(1.0)), np.sqrt(f32(0.05))
+    return Problem("volumetric_mesh_deformation.t", [W, H, D],
+                   [offset, angle, pos.reshape(n, 3).copy(), target.reshape(n, 3), w_fit, w_reg], [0, 1],
+                   {"nIterations": n_iter, "lIterations": l_iter})
+
+
+def optical_flow_synthetic(W, H, seed=1234, n_iter=3, l_iter=20, kind="gaussNewtonGPU"):
+    """I = sum of low-frequency sinusoids in [0,255]; I_hat = I translated by (+1.5,-0.75) px;
+    dx,dy by the 3x3 kernel of examples/optical_flow/src/CombinedSolver.h:152-178."""
+    rng = np.random.default_rng(seed)
+    ys, xs = np.mgrid[0:H, 0:W].astype(np.float64)
+
+    def field(sx, sy):
+        r = np.random.default_rng(seed + 1)
+        out = np.zeros((H, W))
+        for _ in range(8):
+            fx, fy, ph = r.uniform(0.5, 4.0), r.uniform(0.5, 4.0), r.uniform(0, 2 * np.pi)
+            out += np.sin(2 * np.pi * (fx * (xs + sx) / W + fy * (ys + sy) / H) + ph)
+        return out
+
+    lo, hi = field(0, 0).min(), field(0, 0).max()
+    I = ((field(0, 0) - lo) / (hi - lo) * 255).astype(np.float32)
+    Ih = ((field(1.5, -0.75) - lo) / (hi - lo) * 255).astype(np.float32)
+    pad = np.pad(Ih, 1, mode="edge")
+    dx = ((pad[:-2, 2:] + pad[1:-1, 2:] + pad[2:, 2:]) - (pad[:-2, :-2] + pad[1:-1, :-2] + pad[2:, :-2])) / np.float32(8)
+    dy = ((pad[2:, :-2] + pad[2:, 1:-1] + pad[2:, 2:]) - (pad[:-2, :-2] + pad[:-2, 1:-1] + pad[:-2, 2:])) / np.float32(8)
+    X = (0.1 * rng.standard_normal((H, W, 2))).astype(np.float32)
+    w_fit, w_reg = np.sqrt(np.float32(10.0)), np.sqrt(np.float32(0.1))
+    return Problem("optical_flow.t", [W, H], [w_fit, w_reg, X, I, Ih, dx.astype(np.float32), dy.astype(np.float32)], [2],
+                   {"nIterations": n_iter, "lIterations": l_iter}, kind=kind)
+
+
+def grid_mesh_edges(nx, ny):
+    """Directed edges of a regular height-field triangulation, both directions of every mesh
+    edge, sorted by head vertex (the order examples/shared/OptGraph.h:78-89 produces)."""
+    idx = np.arange(nx * ny).reshape(ny, nx)
+    pairs = [(idx[:, :-1], idx[:, 1:]), (idx[:-1, :], idx[1:, :]), (idx[:-1, :-1], idx[1:, 1:])]
+    a = np.concatenate([p[0].ravel() for p in pairs] + [p[1].ravel() for p in pairs])
+    b = np.concatenate([p[1].ravel() for p in pairs] + [p[0].ravel() for p in pairs])
+    order = np.lexsort((b, a))
+    return a[order].astype(np.int32), b[order].astype(np.int32)
+
+
+def arap_synthetic(nx, ny, seed=1234, n_iter=2, l_iter=10):
+    """examples/arap_mesh_deformation/src/CombinedSolver.h:84-102,161-167; main.cpp:137-138."""
+    rng = np.random.default_rng(seed)
+    f32 = np.float32
+    ys, xs = np.mgrid[0:ny, 0:nx]
+    z = 0.1 * np.sin(6.0 * xs / nx) * np.cos(5.0 * ys / ny)
+    ur = np.stack([xs / max(nx, ny), ys / max(nx, ny), z], -1).reshape(-1, 3).astype(f32)
+    n = nx * ny
+    v0, v1 = grid_mesh_edges(nx, ny)
+    cons = np.full((n, 3), -np.inf, dtype=f32)
+    pick = rng.choice(n, max(4, n // 1000), replace=False)
+    cons[pick] = ur[pick] + (0.05 * rng.standard_normal((len(pick), 3))).astype(f32)
+    offset = ur.copy()
+    angle = np.full((n, 3), 0.1, dtype=f32)
+    w_fit, w_reg = np.sqrt(f32(4.0)), np.sqrt(f32(1.0))
+    ecount = np.array([len(v0)], dtype=np.int32)
+    return Problem("arap_mesh_deformation.t", [n, len(v0)],
+                   [w_fit, w_reg, offset, angle, ur, cons, ecount, v0, v1], [2, 3],
+                   {"nIterations": n_iter, "lIterations": l_iter})
