@@ -1,0 +1,74 @@
+"""In-tree build of libOptB200.so (CUDA sm_100a engine + C host) and of the CPU oracle.
+
+`python -m opt_b200.build` or `__graft_entry__.build()`.  nvcc cross-compiles without a GPU.
+Objects are rebuilt only when a source or header is newer.
+"""
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(ROOT, "opt_b200", "csrc")
+OBJ = os.path.join(ROOT, "build", "obj")
+LIB = os.path.join(ROOT, "opt_b200", "libOptB200.so")
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+HOST_CC = "/usr/bin/gcc"
+HOST_CXX = "/usr/bin/g++"
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-ccbin", HOST_CXX, "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
+
+
+def _headers():
+    out = []
+    for d, _, fs in os.walk(CSRC):
+        out += [os.path.join(d, f) for f in fs if f.endswith((".cuh", ".h"))]
+    out += [os.path.join(ROOT, "include", f) for f in os.listdir(os.path.join(ROOT, "include"))]
+    return out
+
+
+def _stale(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def _compile(src, verbose):
+    obj = os.path.join(OBJ, os.path.basename(src) + ".o")
+    if not _stale(obj, [src] + _headers()):
+        return obj, ""
+    if src.endswith(".cu"):
+        cmd = [NVCC] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+    else:
+        cmd = [HOST_CC, "-O2", "-std=c11", "-fPIC", "-Wall", "-c", src, "-o", obj]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("build failed: %s\n%s\n%s" % (" ".join(cmd), r.stdout, r.stderr))
+    return obj, r.stderr
+
+
+def build(verbose=False, oracle=True):
+    os.makedirs(OBJ, exist_ok=True)
+    srcs = [os.path.join(CSRC, "opt_api.c"), os.path.join(CSRC, "registry.cu")]
+    ex = os.path.join(CSRC, "examples")
+    srcs += sorted(os.path.join(ex, f) for f in os.listdir(ex) if f.endswith(".cu"))
+    with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as pool:
+        results = list(pool.map(lambda s: _compile(s, verbose), srcs))
+    objs = [o for o, _ in results]
+    if verbose:
+        for _, log in results:
+            if log:
+                sys.stderr.write(log)
+    if _stale(LIB, objs):
+        cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-ccbin", HOST_CXX, "-lcudart"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("link failed: %s\n%s" % (" ".join(cmd), r.stderr))
+    if oracle:
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(verbose="-v" in sys.argv))

@@ -2,7 +2,7 @@
 
 Only declarations live here: the struct layout and the argument/return types of the twelve
 entry points.  `bind(lib, prefix)` attaches them to a loaded shared library; the product library
-exports the bare `Opt_*` names, the CPU oracle (test infrastructure) exports `OptOracle_*`.
+exports the bare `Opt_*` names; test infrastructure may bind a differently prefixed library.
 """
 import ctypes as C
 

@@ -1,0 +1,638 @@
+// engine.cuh -- the generic GN/LM + PCG engine, templated over a per-example functor.
+//
+// Replaces, for one example, the kernel set the reference JIT-compiles from
+// solverGPUGaussNewton.t:521-1345 plus the generated fmap.* functions.  Layout:
+//   * every solver vector (delta r b Adelta z p Ap CtC pre SSq prevX) is SoA: U planes of Npad
+//     elements, x fastest inside a plane (the reference is AoS per image, o.t:1056-1100);
+//   * the streaming kernels (PCGStep2/3 and friends) treat a vector as one flat array of
+//     U*Npad elements and move it with 128-bit loads/stores.  They need no exclude test:
+//     excluded sites hold 0 in delta/r/p/z/Ap from allocation on and every update maps 0 to 0;
+//   * reductions are block-level (warp shuffle -> smem -> one double atomicAdd per block) into
+//     device-resident double scalars that the next kernel reads (no host sync in the GN loop).
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+#include "common.cuh"
+#include "optk.h"
+
+// The C handle is the abstract base class of every Engine<F>.
+struct OptK_Plan {
+    virtual ~OptK_Plan() {}
+    virtual void bind(void** pp) = 0;
+    virtual void set_lm(double radius, double min_diag, double max_diag) = 0;
+    virtual void precompute() = 0;
+    virtual double cost() = 0;
+    virtual void pcg_begin(int nIter) = 0;
+    virtual void pcg_iter(int lIter, int reset) = 0;
+    virtual void pcg_run(int lIterations) = 0;
+    virtual double fetch_q() = 0;
+    virtual double model_cost() = 0;
+    virtual void save_unknowns() = 0;
+    virtual void linear_update() = 0;
+    virtual void revert_update() = 0;
+    virtual int unknown_channels() const = 0;
+    virtual long site_count() const = 0;
+    virtual int debug_read(const char* name, void* host_out) = 0;
+    virtual void debug_apply_jtj(const void* host_p, void* host_out) = 0;
+
+    // ---- launch bookkeeping shared by all engines -------------------------------------------
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_in = nullptr, ev_out = nullptr;
+    long launches = 0;
+    bool timing = false;
+    struct Timed { const char* name; cudaEvent_t a, b; };
+    std::vector<Timed> timed;
+
+    void base_init(bool collect_timing) {
+        timing = collect_timing;
+        OPTK_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+        OPTK_CUDA(cudaEventCreateWithFlags(&ev_in, cudaEventDisableTiming));
+        OPTK_CUDA(cudaEventCreateWithFlags(&ev_out, cudaEventDisableTiming));
+    }
+    void base_destroy() {
+        for (auto& t : timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+        if (ev_in) cudaEventDestroy(ev_in);
+        if (ev_out) cudaEventDestroy(ev_out);
+        if (stream) cudaStreamDestroy(stream);
+    }
+    // The reference runs on the default stream (SURVEY 8b "Threading").  The engine runs on its
+    // own stream (so the PCG loop can be captured in a CUDA graph) and fences it against the
+    // legacy default stream at both ends of every API call, which preserves those semantics.
+    void begin_call() {
+        OPTK_CUDA(cudaEventRecord(ev_in, cudaStreamLegacy));
+        OPTK_CUDA(cudaStreamWaitEvent(stream, ev_in, 0));
+    }
+    void end_call() {
+        OPTK_CUDA(cudaEventRecord(ev_out, stream));
+        OPTK_CUDA(cudaStreamWaitEvent(cudaStreamLegacy, ev_out, 0));
+    }
+    void pre_launch(const char* name) {
+        ++launches;
+        if (timing) {
+            Timed t; t.name = name;
+            OPTK_CUDA(cudaEventCreate(&t.a)); OPTK_CUDA(cudaEventCreate(&t.b));
+            OPTK_CUDA(cudaEventRecord(t.a, stream));
+            timed.push_back(t);
+        }
+    }
+    void post_launch() {
+        OPTK_CUDA(cudaGetLastError());                      // backend_cuda.t:827
+        if (timing) OPTK_CUDA(cudaEventRecord(timed.back().b, stream));
+    }
+    // every kernel of the engine goes through here: launch counter, optional event pair, error check
+    template <class... KA, class... A>
+    void launch(const char* name, dim3 grid, dim3 block, void (*kernel)(KA...), A... args) {
+        pre_launch(name);
+        kernel<<<grid, block, 0, stream>>>(args...);
+        post_launch();
+    }
+    void print_timing() {                                    // backend_cuda.t:262-297
+        if (!timing || timed.empty()) return;
+        OPTK_CUDA(cudaStreamSynchronize(stream));
+        std::map<std::string, std::pair<int, double>> agg;
+        std::vector<std::string> order;
+        for (auto& t : timed) {
+            float ms = 0; cudaEventElapsedTime(&ms, t.a, t.b);
+            if (!agg.count(t.name)) order.push_back(t.name);
+            agg[t.name].first++; agg[t.name].second += ms;
+        }
+        printf("--------------------------------------------------------\n");
+        printf("        Kernel        |   Count  |   Total   | Average \n");
+        printf("----------------------+----------+-----------+----------\n");
+        for (auto& n : order)
+            printf(" %-20s |   %4d   | %8.3fms| %7.4fms\n", n.c_str(), agg[n].first, agg[n].second, agg[n].second / agg[n].first);
+        printf("--------------------------------------------------------\n");
+    }
+};
+
+namespace optk {
+
+// ------------------------------------------------------------------------------ site mapping
+template <class F>
+__device__ __forceinline__ bool thread_site(const F& f, int& x, int& y, int& z, long& s) {
+    x = blockIdx.x * blockDim.x + threadIdx.x;
+    y = blockIdx.y * blockDim.y + threadIdx.y;
+    z = blockIdx.z * blockDim.z + threadIdx.z;
+    s = x + (long)f.W * (y + (long)f.H * z);
+    return x < f.W && y < f.H && z < f.D;
+}
+
+// ------------------------------------------------------------------------------ site kernels
+// PCGInit1 (solver:521-563).  For graph problems the raw diagonal is stored and inverted later.
+template <class F>
+__global__ void k_pcg_init1(F f, Vec<typename F::Scalar> delta, Vec<typename F::Scalar> r,
+                            Vec<typename F::Scalar> p, Vec<typename F::Scalar> pre, double* aNum) {
+    using T = typename F::Scalar;
+    constexpr int U = F::U;
+    int x, y, z; long s;
+    double acc = 0.0;
+    if (thread_site(f, x, y, z, s)) {
+        T g[U], d[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) g[u] = d[u] = T(0);
+        const bool ex = f.exclude(x, y, z, s);
+        if (!ex) {
+            f.evalJTF(x, y, z, s, g, d);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                delta(u, s) = T(0);
+                g[u] = -g[u];
+                r(u, s) = g[u];
+                if (!F::USE_PRE) d[u] = T(1);
+            }
+            if (F::GV == 0) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    d[u] = guarded_invert(d[u]);
+                    T pp = d[u] * g[u];
+                    p(u, s) = pp;
+                    acc += (double)(g[u] * pp);
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) pre(u, s) = d[u];
+    }
+    if (F::GV == 0) block_accumulate(acc, aNum);
+}
+
+// PCGStep1 / computeAdelta (solver:607-632, 873-878): out = (J^T J [+ CtC]) dir over non-excluded sites
+template <class F, bool LM>
+__global__ void k_apply_jtj(F f, Vec<typename F::Scalar> dir, Vec<typename F::Scalar> out,
+                            Vec<typename F::Scalar> CtC, double* den, double* zero_slot) {
+    using T = typename F::Scalar;
+    constexpr int U = F::U;
+    int x, y, z; long s;
+    double acc = 0.0;
+    if (zero_slot && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && linear_tid() == 0) *zero_slot = 0.0;
+    if (thread_site(f, x, y, z, s) && !f.exclude(x, y, z, s)) {
+        T o[U];
+        f.applyJTJ(x, y, z, s, dir, o);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            T pv = dir(u, s);
+            if (LM) o[u] += CtC(u, s) * pv;
+            out(u, s) = o[u];
+            acc += (double)(pv * o[u]);
+        }
+    }
+    block_accumulate(acc, den);
+}
+
+// computeCost (solver:971-997)
+template <class F>
+__global__ void k_cost(F f, double* target) {
+    using T = typename F::Scalar;
+    int x, y, z; long s;
+    double acc = 0.0;
+    if (thread_site(f, x, y, z, s) && !f.exclude(x, y, z, s)) acc = (double)(T)(0.5 * (double)f.cost(x, y, z, s));
+    block_accumulate(acc, target);
+}
+
+// computeModelCost (solver:1105-1118)
+template <class F>
+__global__ void k_model_cost(F f, Vec<typename F::Scalar> delta, double* target) {
+    using T = typename F::Scalar;
+    int x, y, z; long s;
+    double acc = 0.0;
+    if (thread_site(f, x, y, z, s) && !f.exclude(x, y, z, s)) acc = (double)(T(0.5) * f.modelCost(x, y, z, s, delta));
+    block_accumulate(acc, target);
+}
+
+// PCGComputeCtC (solver:1042-1048): CtC = diag(J^T J) / radius
+template <class F>
+__global__ void k_compute_ctc(F f, Vec<typename F::Scalar> CtC, typename F::Scalar inv_radius) {
+    using T = typename F::Scalar;
+    constexpr int U = F::U;
+    int x, y, z; long s;
+    if (thread_site(f, x, y, z, s) && !f.exclude(x, y, z, s)) {
+        T g[U], d[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) g[u] = d[u] = T(0);
+        f.evalJTF(x, y, z, s, g, d);
+#pragma unroll
+        for (int u = 0; u < U; ++u) CtC(u, s) = d[u] * inv_radius;
+    }
+}
+
+// PCGFinalizeDiagonal (solver:1061-1099)
+template <class F>
+__global__ void k_finalize_diagonal(F f, Vec<typename F::Scalar> CtC, Vec<typename F::Scalar> SSq,
+                                    Vec<typename F::Scalar> pre, Vec<typename F::Scalar> r,
+                                    Vec<typename F::Scalar> b, Vec<typename F::Scalar> p,
+                                    Vec<typename F::Scalar> delta, typename F::Scalar radius,
+                                    typename F::Scalar min_diag, typename F::Scalar max_diag,
+                                    double* aNum, double* q) {
+    using T = typename F::Scalar;
+    constexpr int U = F::U;
+    int x, y, z; long s;
+    double acc = 0.0, qacc = 0.0;
+    if (thread_site(f, x, y, z, s) && !f.exclude(x, y, z, s)) {
+        T qq = T(0);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            T unclamped = CtC(u, s);
+            T invS = T(1) / SSq(u, s);
+            T mult = invS / radius;
+            T c = fmin(fmax(unclamped, min_diag * mult), max_diag * mult);
+            CtC(u, s) = c;
+            T m = T(1) / (c + radius * unclamped);
+            pre(u, s) = m;
+            T res = r(u, s);
+            b(u, s) = res;
+            T pp = m * res;
+            p(u, s) = pp;
+            acc += (double)(res * pp);
+            qq += delta(u, s) * (res + res);
+        }
+        qacc = (double)(T(0.5) * qq);
+    }
+    block_accumulate(acc, aNum);
+    block_accumulate(qacc, q);
+}
+
+// PCGLinearUpdate / savePreviousUnknowns / revertUpdate (solver:854-887); MODE 0: X += delta,
+// 1: prevX = X, 2: X = prevX
+template <class F, int MODE>
+__global__ void k_unknown_update(F f, Vec<typename F::Scalar> v) {
+    constexpr int U = F::U;
+    int x, y, z; long s;
+    if (thread_site(f, x, y, z, s) && !f.exclude(x, y, z, s)) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            typename F::Scalar* xp = f.xptr(s, u);
+            if (MODE == 0) *xp = *xp + v(u, s);
+            else if (MODE == 1) v(u, s) = *xp;
+            else *xp = v(u, s);
+        }
+    }
+}
+
+template <class F>
+__global__ void k_precompute(F f) {
+    int x, y, z; long s;
+    if (thread_site(f, x, y, z, s)) f.precompute(x, y, z, s);
+}
+
+// ------------------------------------------------------------------------------ graph kernels
+// PCGInit1_Graph (solver:1188-1197): scatter -dr/du * r into r, (dr/du)^2 into pre
+template <class F>
+__global__ void k_graph_jtf(F f, long E, Vec<typename F::Scalar> r, Vec<typename F::Scalar> pre) {
+    long e = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (e < E) f.graphJTF(e, r, pre);
+}
+// PCGInit1_Finish (solver:570-598): no exclude test
+template <class F>
+__global__ void k_pcg_init1_finish(F f, Vec<typename F::Scalar> r, Vec<typename F::Scalar> pre,
+                                   Vec<typename F::Scalar> p, double* aNum) {
+    using T = typename F::Scalar;
+    constexpr int U = F::U;
+    int x, y, z; long s;
+    double acc = 0.0;
+    if (thread_site(f, x, y, z, s)) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            T res = r(u, s);
+            T m = guarded_invert(pre(u, s));
+            if (!F::USE_PRE) m = T(1);
+            T pp = m * res;
+            pre(u, s) = m;
+            p(u, s) = pp;
+            acc += (double)(res * pp);
+        }
+    }
+    block_accumulate(acc, aNum);
+}
+// PCGStep1_Graph / computeAdelta_Graph (solver:1216-1244)
+template <class F>
+__global__ void k_graph_jtj(F f, long E, Vec<typename F::Scalar> dir, Vec<typename F::Scalar> out, double* den) {
+    long e = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    double acc = 0.0;
+    if (e < E) acc = (double)f.graphJTJ(e, dir, out);
+    block_accumulate(acc, den);
+}
+template <class F>
+__global__ void k_graph_cost(F f, long E, double* target) {
+    using T = typename F::Scalar;
+    long e = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    double acc = 0.0;
+    if (e < E) acc = (double)(T)(0.5 * (double)f.graphCost(e));
+    block_accumulate(acc, target);
+}
+template <class F>
+__global__ void k_graph_model_cost(F f, long E, Vec<typename F::Scalar> delta, double* target) {
+    using T = typename F::Scalar;
+    long e = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    double acc = 0.0;
+    if (e < E) acc = (double)(T(0.5) * f.graphModelCost(e, delta));
+    block_accumulate(acc, target);
+}
+template <class F>
+__global__ void k_graph_ctc(F f, long E, Vec<typename F::Scalar> CtC, typename F::Scalar inv_radius) {
+    long e = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (e < E) f.graphCtC(e, CtC, inv_radius);
+}
+
+// ------------------------------------------------------------------------------ flat streaming kernels
+// PCGStep2 (solver:665-731): alpha = aNum/aDen; delta += alpha p; r -= alpha Ap; z = M^-1 r;
+// betaNum += z.r ; LM: q += 0.5 delta.(r+b).   One 128-bit vector per thread and array.
+template <class T, bool USE_PRE, bool LM>
+__global__ void __launch_bounds__(256) k_pcg_step2(long nvec, T* __restrict__ delta, const T* __restrict__ p,
+                                                   T* __restrict__ r, const T* __restrict__ Ap,
+                                                   const T* __restrict__ pre, const T* __restrict__ b,
+                                                   T* __restrict__ z, const double* aNum, const double* aDen,
+                                                   double* bNum, double* q, double* zero_slot) {
+    using V = typename VecIO<T>::V;
+    constexpr int VW = VecIO<T>::W;
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    const T alpha = (T)(*aNum) / (T)(*aDen);
+    if (i == 0 && zero_slot) *zero_slot = 0.0;
+    double bacc = 0.0, qacc = 0.0;
+    if (i < nvec) {
+        V d = reinterpret_cast<const V*>(delta)[i];
+        V pv = reinterpret_cast<const V*>(p)[i];
+        V rv = reinterpret_cast<const V*>(r)[i];
+        V av = reinterpret_cast<const V*>(Ap)[i];
+        V mv, bv, zv;
+        if (USE_PRE) mv = reinterpret_cast<const V*>(pre)[i];
+        if (LM) bv = reinterpret_cast<const V*>(b)[i];
+        T bsum = T(0), qsum = T(0);
+#pragma unroll
+        for (int k = 0; k < VW; ++k) {
+            T dl = comp(d, k) + alpha * comp(pv, k);
+            comp(d, k) = dl;
+            T rr = comp(rv, k) - alpha * comp(av, k);
+            comp(rv, k) = rr;
+            T zz = USE_PRE ? comp(mv, k) * rr : rr;
+            comp(zv, k) = zz;
+            bsum += zz * rr;
+            if (LM) qsum += dl * (rr + comp(bv, k));
+        }
+        reinterpret_cast<V*>(delta)[i] = d;
+        reinterpret_cast<V*>(r)[i] = rv;
+        if (USE_PRE) reinterpret_cast<V*>(z)[i] = zv;
+        bacc = (double)bsum;
+        qacc = (double)(T(0.5) * qsum);
+    }
+    block_accumulate(bacc, bNum);
+    if (LM) block_accumulate(qacc, q);
+}
+
+// PCGStep3 (solver:814-845): beta = bNum/aNum; p = z + beta p
+template <class T>
+__global__ void __launch_bounds__(256) k_pcg_step3(long nvec, const T* __restrict__ z, T* __restrict__ p,
+                                                   const double* bNum, const double* aNum, double* zero_slot) {
+    using V = typename VecIO<T>::V;
+    constexpr int VW = VecIO<T>::W;
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    const T beta = (T)(*bNum) / (T)(*aNum);
+    if (i == 0 && zero_slot) *zero_slot = 0.0;
+    if (i < nvec) {
+        V zv = reinterpret_cast<const V*>(z)[i];
+        V pv = reinterpret_cast<const V*>(p)[i];
+#pragma unroll
+        for (int k = 0; k < VW; ++k) comp(pv, k) = comp(zv, k) + beta * comp(pv, k);
+        reinterpret_cast<V*>(p)[i] = pv;
+    }
+}
+
+// PCGStep2_1stHalf (solver:738-762): delta += alpha p
+template <class T>
+__global__ void __launch_bounds__(256) k_axpy_alpha(long nvec, T* __restrict__ delta, const T* __restrict__ p,
+                                                    const double* aNum, const double* aDen) {
+    using V = typename VecIO<T>::V;
+    constexpr int VW = VecIO<T>::W;
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    const T alpha = (T)(*aNum) / (T)(*aDen);
+    if (i < nvec) {
+        V d = reinterpret_cast<const V*>(delta)[i];
+        V pv = reinterpret_cast<const V*>(p)[i];
+#pragma unroll
+        for (int k = 0; k < VW; ++k) comp(d, k) = comp(d, k) + alpha * comp(pv, k);
+        reinterpret_cast<V*>(delta)[i] = d;
+    }
+}
+
+// PCGStep2_2ndHalf (solver:766-799): r = b - A delta; z = M^-1 r; betaNum += z.r; q += 0.5 delta.(r+b)
+template <class T, bool USE_PRE>
+__global__ void __launch_bounds__(256) k_residual_reset(long nvec, const T* __restrict__ delta, T* __restrict__ r,
+                                                        const T* __restrict__ Adelta, const T* __restrict__ pre,
+                                                        const T* __restrict__ b, T* __restrict__ z,
+                                                        double* bNum, double* q, double* zero_slot) {
+    using V = typename VecIO<T>::V;
+    constexpr int VW = VecIO<T>::W;
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (i == 0 && zero_slot) *zero_slot = 0.0;
+    double bacc = 0.0, qacc = 0.0;
+    if (i < nvec) {
+        V d = reinterpret_cast<const V*>(delta)[i];
+        V av = reinterpret_cast<const V*>(Adelta)[i];
+        V bv = reinterpret_cast<const V*>(b)[i];
+        V mv, rv, zv;
+        if (USE_PRE) mv = reinterpret_cast<const V*>(pre)[i];
+        T bsum = T(0), qsum = T(0);
+#pragma unroll
+        for (int k = 0; k < VW; ++k) {
+            T rr = comp(bv, k) - comp(av, k);
+            comp(rv, k) = rr;
+            T zz = USE_PRE ? comp(mv, k) * rr : rr;
+            comp(zv, k) = zz;
+            bsum += zz * rr;
+            qsum += comp(d, k) * (rr + comp(bv, k));
+        }
+        reinterpret_cast<V*>(r)[i] = rv;
+        if (USE_PRE) reinterpret_cast<V*>(z)[i] = zv;
+        bacc = (double)bsum;
+        qacc = (double)(T(0.5) * qsum);
+    }
+    block_accumulate(bacc, bNum);
+    block_accumulate(qacc, q);
+}
+
+// ------------------------------------------------------------------------------ the engine
+template <class F>
+struct Engine : OptK_Plan {
+    using T = typename F::Scalar;
+    static constexpr int U = F::U;
+    static constexpr bool GRAPH = F::GV > 0;
+
+    F f;
+    bool lm;
+    long N, Npad, E;
+    T* pool = nullptr;
+    Vec<T> delta, r, b, Adelta, z, p, Ap, CtC, pre, SSq, prevX;
+    double* scal = nullptr;
+    double* h_scal = nullptr;    // pinned
+    T radius = 0, min_diag = 0, max_diag = 0;
+    dim3 sgrid, sblock;
+
+    Engine(const unsigned* dims, bool is_lm, bool collect_timing) : lm(is_lm) {
+        base_init(collect_timing);
+        f.plan(dims);
+        N = (long)f.W * f.H * f.D;
+        E = GRAPH ? (long)f.E : 0;
+        Npad = round_up(N, 64);
+        const int nvec = lm ? 11 : 7;
+        size_t bytes = (size_t)nvec * U * Npad * sizeof(T);
+        OPTK_CUDA(cudaMalloc(&pool, bytes));
+        OPTK_CUDA(cudaMemsetAsync(pool, 0, bytes, stream));
+        Vec<T>* vs[11] = {&delta, &r, &z, &p, &Ap, &pre, &prevX, &b, &Adelta, &CtC, &SSq};
+        for (int i = 0; i < 11; ++i) {
+            vs[i]->plane = Npad;
+            vs[i]->d = i < nvec ? pool + (size_t)i * U * Npad : nullptr;
+        }
+        if (!F::USE_PRE) z = r;                             // M^-1 = 1: z aliases r (solver:705-711)
+        OPTK_CUDA(cudaMalloc(&scal, S_COUNT * sizeof(double)));
+        OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
+        OPTK_CUDA(cudaMallocHost(&h_scal, S_COUNT * sizeof(double)));
+        if (F::ND == 1) { sblock = dim3(256, 1, 1); }
+        else if (F::ND == 2) { sblock = dim3(32, 8, 1); }
+        else { sblock = dim3(32, 4, 2); }
+        sgrid = dim3((f.W + sblock.x - 1) / sblock.x, (f.H + sblock.y - 1) / sblock.y, (f.D + sblock.z - 1) / sblock.z);
+        f.alloc_temporaries(stream);
+        OPTK_CUDA(cudaStreamSynchronize(stream));
+    }
+    ~Engine() override {
+        cudaStreamSynchronize(stream);
+        f.free_temporaries();
+        cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal);
+        base_destroy();
+    }
+    int unknown_channels() const override { return U; }
+    long site_count() const override { return N; }
+    void bind(void** pp) override { f.bind(pp); }
+    void set_lm(double rad, double mn, double mx) override { radius = (T)rad; min_diag = (T)mn; max_diag = (T)mx; }
+
+    double* S(int slot) const { return scal + slot; }
+    long flat_vecs() const { return (long)U * Npad / VecIO<T>::W; }
+    dim3 flat_grid() const { return dim3((unsigned)((flat_vecs() + 255) / 256)); }
+    dim3 edge_grid() const { return dim3((unsigned)((E + 255) / 256)); }
+
+    double read_scalar(int slot) {                          // blocking D2H (backend_cuda.t:353-355)
+        OPTK_CUDA(cudaMemcpyAsync(h_scal, scal + slot, sizeof(double), cudaMemcpyDeviceToHost, stream));
+        OPTK_CUDA(cudaStreamSynchronize(stream));
+        return h_scal[0];
+    }
+
+    void precompute() override {
+        if (F::HAS_PRECOMPUTE) this->launch("precompute", sgrid, dim3(sblock), k_precompute<F>, f);
+    }
+    double cost() override {
+        OPTK_CUDA(cudaMemsetAsync(S(S_COST), 0, sizeof(double), stream));
+        this->launch("computeCost", sgrid, dim3(sblock), k_cost<F>, f, S(S_COST));
+        if (GRAPH) this->launch("computeCost_Graph", edge_grid(), dim3(256), k_graph_cost<F>, f, E, S(S_COST));
+        return (double)(T)read_scalar(S_COST);
+    }
+    double model_cost() override {
+        OPTK_CUDA(cudaMemsetAsync(S(S_MODEL), 0, sizeof(double), stream));
+        this->launch("computeModelCost", sgrid, dim3(sblock), k_model_cost<F>, f, delta, S(S_MODEL));
+        if (GRAPH) this->launch("computeModelCost_Graph", edge_grid(), dim3(256), k_graph_model_cost<F>, f, E, delta, S(S_MODEL));
+        return (double)(T)read_scalar(S_MODEL);
+    }
+    double fetch_q() override { return (double)(T)read_scalar(S_Q); }
+
+    void pcg_begin(int nIter) override {
+        OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
+        this->launch("PCGInit1", sgrid, dim3(sblock), k_pcg_init1<F>, f, delta, r, p, pre, S(S_RZ0));
+        if (GRAPH) {
+            this->launch("PCGInit1_Graph", edge_grid(), dim3(256), k_graph_jtf<F>, f, E, r, pre);
+            this->launch("PCGInit1_Finish", sgrid, dim3(sblock), k_pcg_init1_finish<F>, f, r, pre, p, S(S_RZ0));
+        }
+        if (lm) {
+            OPTK_CUDA(cudaMemsetAsync(S(S_RZ0), 0, sizeof(double), stream));
+            if (nIter == 0)                                  // PCGSaveSSq (solver:1052-1057), flat copy
+                OPTK_CUDA(cudaMemcpyAsync(SSq.d, pre.d, (size_t)U * Npad * sizeof(T), cudaMemcpyDeviceToDevice, stream));
+            const T inv_radius = T(1) / radius;
+            this->launch("PCGComputeCtC", sgrid, dim3(sblock), k_compute_ctc<F>, f, CtC, inv_radius);
+            if (GRAPH) this->launch("PCGComputeCtC_Graph", edge_grid(), dim3(256), k_graph_ctc<F>, f, E, CtC, inv_radius);
+            this->launch("PCGFinalizeDiagonal", sgrid, dim3(sblock), k_finalize_diagonal<F>, f, CtC, SSq, pre, r, b, p, delta, radius, min_diag, max_diag, S(S_RZ0), S(S_Q));
+        }
+    }
+
+    void apply_A(const char* name, const char* gname, Vec<T> dir, Vec<T> out, double* den, double* zero_slot) {
+        if (lm) this->launch(name, sgrid, dim3(sblock), k_apply_jtj<F, true>, f, dir, out, CtC, den, zero_slot);
+        else    this->launch(name, sgrid, dim3(sblock), k_apply_jtj<F, false>, f, dir, out, CtC, den, zero_slot);
+        if (GRAPH) this->launch(gname, edge_grid(), dim3(256), k_graph_jtj<F>, f, E, dir, out, den);
+    }
+
+    void pcg_iter(int l, int reset) override {
+        double* aNum = S(S_RZ0 + l % 3);
+        double* bNum = S(S_RZ0 + (l + 1) % 3);
+        double* nextB = S(S_RZ0 + (l + 2) % 3);
+        double* aDen = S(S_ADEN0 + (l & 1));
+        double* nextDen = S(S_ADEN0 + ((l + 1) & 1));
+        // PCGStep1 also clears q for this iteration (solver:2090)
+        apply_A("PCGStep1", "PCGStep1_Graph", p, Ap, aDen, lm ? S(S_Q) : nullptr);
+        const long nv = flat_vecs();
+        if (lm && reset) {
+            this->launch("PCGStep2_1stHalf", flat_grid(), dim3(256), k_axpy_alpha<T>, nv, delta.d, p.d, aNum, aDen);
+            apply_A("computeAdelta", "computeAdelta_Graph", delta, Adelta, S(S_DUMMY), nullptr);
+            this->launch("PCGStep2_2ndHalf", flat_grid(), dim3(256), k_residual_reset<T, F::USE_PRE>, nv, delta.d, r.d, Adelta.d, pre.d, b.d, z.d, bNum, S(S_Q), nextDen);
+        } else if (lm) {
+            this->launch("PCGStep2", flat_grid(), dim3(256), k_pcg_step2<T, F::USE_PRE, true>, nv, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
+        } else {
+            this->launch("PCGStep2", flat_grid(), dim3(256), k_pcg_step2<T, F::USE_PRE, false>, nv, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
+        }
+        this->launch("PCGStep3", flat_grid(), dim3(256), k_pcg_step3<T>, nv, z.d, p.d, bNum, aNum, nextB);
+    }
+    void pcg_run(int lIterations) override {
+        for (int l = 0; l < lIterations; ++l) pcg_iter(l, 0);
+    }
+
+    void save_unknowns() override { this->launch("savePreviousUnknowns", sgrid, dim3(sblock), k_unknown_update<F, 1>, f, prevX); }
+    void linear_update() override { this->launch("PCGLinearUpdate", sgrid, dim3(sblock), k_unknown_update<F, 0>, f, delta); }
+    void revert_update() override { this->launch("revertUpdate", sgrid, dim3(sblock), k_unknown_update<F, 2>, f, prevX); }
+
+    Vec<T>* vec_by_name(const char* n) {
+        struct { const char* n; Vec<T>* v; } tab[] = {{"delta", &delta}, {"r", &r}, {"p", &p}, {"Ap", &Ap}, {"z", &z},
+                                                      {"pre", &pre}, {"CtC", &CtC}, {"b", &b}, {"prevX", &prevX}};
+        for (auto& t : tab) if (!strcmp(t.n, n)) return t.v;
+        return nullptr;
+    }
+    int debug_read(const char* name, void* host_out) override {
+        Vec<T>* v = vec_by_name(name);
+        if (!v || !v->d) return -1;
+        std::vector<T> tmp((size_t)U * Npad);
+        OPTK_CUDA(cudaStreamSynchronize(stream));
+        OPTK_CUDA(cudaMemcpy(tmp.data(), v->d, tmp.size() * sizeof(T), cudaMemcpyDeviceToHost));
+        T* o = (T*)host_out;
+        for (long s = 0; s < N; ++s) for (int u = 0; u < U; ++u) o[s * U + u] = tmp[(size_t)u * Npad + s];
+        return 0;
+    }
+    void debug_apply_jtj(const void* host_p, void* host_out) override {
+        std::vector<T> tmp((size_t)U * Npad, T(0));
+        const T* hp = (const T*)host_p;
+        for (long s = 0; s < N; ++s) for (int u = 0; u < U; ++u) tmp[(size_t)u * Npad + s] = hp[s * U + u];
+        OPTK_CUDA(cudaMemcpy(p.d, tmp.data(), tmp.size() * sizeof(T), cudaMemcpyHostToDevice));
+        OPTK_CUDA(cudaMemsetAsync(Ap.d, 0, tmp.size() * sizeof(T), stream));
+        bool saved = lm; lm = false;
+        apply_A("PCGStep1", "PCGStep1_Graph", p, Ap, S(S_DUMMY), nullptr);
+        lm = saved;
+        debug_read("Ap", host_out);
+    }
+};
+
+// functors without ComputedArrays / graphs inherit these no-ops
+template <class T>
+struct FunctorDefaults {
+    static constexpr bool HAS_PRECOMPUTE = false;
+    static constexpr int GV = 0;
+    int E = 0;
+    void alloc_temporaries(cudaStream_t) {}
+    void free_temporaries() {}
+    __device__ void precompute(int, int, int, long) const {}
+    __device__ void graphJTF(long, Vec<T>, Vec<T>) const {}
+    __device__ T graphJTJ(long, Vec<T>, Vec<T>) const { return T(0); }
+    __device__ T graphCost(long) const { return T(0); }
+    __device__ T graphModelCost(long, Vec<T>) const { return T(0); }
+    __device__ void graphCtC(long, Vec<T>, T) const {}
+};
+
+template <template <class> class F>
+OptK_Plan* make_engine(int is_double, int is_lm, const unsigned* dims, int timing) {
+    if (is_double) return new Engine<F<double>>(dims, is_lm != 0, timing != 0);
+    return new Engine<F<float>>(dims, is_lm != 0, timing != 0);
+}
+
+}  // namespace optk

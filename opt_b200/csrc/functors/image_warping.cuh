@@ -1,0 +1,113 @@
+// functors/image_warping.cuh -- image_warping (examples/image_warping/image_warping.t:12-43,105-107)
+//   reg_o(i) = v(i,n) w_r [ (O_i - O_n) - R(A_i)(U_i - U_n) ],  v = inb(n) [M_n==0] [M_i==0]   (2 channels, 4 offsets)
+//   fit(i)   = w_f [C_i.x>=0][C_i.y>=0] (O_i - C_i)
+//   Exclude(M != 0), UsePreconditioner(true); unknown element = (Offset.xy, Angle)
+// Closed forms: SURVEY.md App. D, with D_ab = -R'(A_a)(U_a - U_b).
+#pragma once
+#include "math.cuh"
+
+namespace optk {
+
+template <class T>
+struct ImageWarpingFunctor : FunctorDefaults<T> {
+    using Scalar = T;
+    static constexpr int U = 3, ND = 2;
+    static constexpr bool USE_PRE = true;
+    int W, H, D;
+    T* O; T* A; const T* Ur; const T* Cn; const T* M;
+    T w_fit, w_reg;
+    void plan(const unsigned* d) { W = d[0]; H = d[1]; D = 1; }
+    void bind(void** pp) {
+        O = (T*)pp[0]; A = (T*)pp[1]; Ur = (const T*)pp[2]; Cn = (const T*)pp[3]; M = (const T*)pp[4];
+        w_fit = (T) * (const float*)pp[5]; w_reg = (T) * (const float*)pp[6];
+    }
+    __device__ bool exclude(int, int, int, long s) const { return M[s] != T(0); }
+    __device__ T* xptr(long s, int u) const { return u < 2 ? O + s * 2 + u : A + s; }
+
+    template <class Fn> __device__ __forceinline__ void neighbours(int x, int y, long s, Fn&& fn) const {
+        const bool mi = M[s] == T(0);
+        if (x + 1 < W && mi && M[s + 1] == T(0)) fn(s + 1);
+        if (x > 0 && mi && M[s - 1] == T(0)) fn(s - 1);
+        if (y + 1 < H && mi && M[s + W] == T(0)) fn(s + W);
+        if (y > 0 && mi && M[s - W] == T(0)) fn(s - W);
+    }
+    // d = (O_a - O_b) - R(A_a) u ; Dv = -R'(A_a) u, u = U_a - U_b
+    __device__ __forceinline__ static void rot(T sa, T ca, const T* u, T* Ru, T* Dv) {
+        Ru[0] = ca * u[0] - sa * u[1]; Ru[1] = sa * u[0] + ca * u[1];
+        Dv[0] = sa * u[0] + ca * u[1]; Dv[1] = -ca * u[0] + sa * u[1];
+    }
+    __device__ T cost(int x, int y, int, long s) const {
+        T oi[2], ui[2], ci[2]; load2(O + s * 2, oi); load2(Ur + s * 2, ui); load2(Cn + s * 2, ci);
+        T sa, ca; sincos_t(A[s], sa, ca);
+        T sum = T(0);
+        if (ci[0] >= T(0) && ci[1] >= T(0)) { T r0 = w_fit * (oi[0] - ci[0]), r1 = w_fit * (oi[1] - ci[1]); sum += r0 * r0 + r1 * r1; }
+        neighbours(x, y, s, [&](long n) {
+            T on[2], un[2]; load2(O + n * 2, on); load2(Ur + n * 2, un);
+            T u[2] = {ui[0] - un[0], ui[1] - un[1]}, Ru[2], Dv[2]; rot(sa, ca, u, Ru, Dv);
+            T r0 = w_reg * ((oi[0] - on[0]) - Ru[0]), r1 = w_reg * ((oi[1] - on[1]) - Ru[1]);
+            sum += r0 * r0 + r1 * r1;
+        });
+        return sum;
+    }
+    __device__ void evalJTF(int x, int y, int, long s, T* g, T* d) const {
+        T oi[2], ui[2], ci[2]; load2(O + s * 2, oi); load2(Ur + s * 2, ui); load2(Cn + s * 2, ci);
+        T sa, ca; sincos_t(A[s], sa, ca);
+        const T wf2 = w_fit * w_fit, wr2 = w_reg * w_reg;
+        if (ci[0] >= T(0) && ci[1] >= T(0)) {
+            g[0] += wf2 * (oi[0] - ci[0]); g[1] += wf2 * (oi[1] - ci[1]);
+            d[0] += wf2; d[1] += wf2;
+        }
+        neighbours(x, y, s, [&](long n) {
+            T on[2], un[2]; load2(O + n * 2, on); load2(Ur + n * 2, un);
+            T sn, cn; sincos_t(A[n], sn, cn);
+            T u[2] = {ui[0] - un[0], ui[1] - un[1]}, Ru[2], Dv[2], Rnu[2], Dn[2];
+            rot(sa, ca, u, Ru, Dv); rot(sn, cn, u, Rnu, Dn);
+            T din[2] = {(oi[0] - on[0]) - Ru[0], (oi[1] - on[1]) - Ru[1]};          // d(i,n)
+            T dni[2] = {(on[0] - oi[0]) + Rnu[0], (on[1] - oi[1]) + Rnu[1]};        // d(n,i) = (O_n-O_i) - R(A_n)(U_n-U_i)
+            g[0] += wr2 * (din[0] - dni[0]); g[1] += wr2 * (din[1] - dni[1]);
+            g[2] += wr2 * (Dv[0] * din[0] + Dv[1] * din[1]);
+            d[0] += T(2) * wr2; d[1] += T(2) * wr2;
+            d[2] += wr2 * (Dv[0] * Dv[0] + Dv[1] * Dv[1]);
+        });
+    }
+    __device__ void applyJTJ(int x, int y, int, long s, const Vec<T>& p, T* out) const {
+        T ui[2], ci[2]; load2(Ur + s * 2, ui); load2(Cn + s * 2, ci);
+        T sa, ca; sincos_t(A[s], sa, ca);
+        const T wf2 = w_fit * w_fit, wr2 = w_reg * w_reg;
+        const T p0 = p(0, s), p1 = p(1, s), pa = p(2, s);
+        T a0 = T(0), a1 = T(0), a2 = T(0);
+        neighbours(x, y, s, [&](long n) {
+            T un[2]; load2(Ur + n * 2, un);
+            T sn, cn; sincos_t(A[n], sn, cn);
+            T u[2] = {ui[0] - un[0], ui[1] - un[1]}, Ru[2], Dv[2], Rnu[2], Dn[2];
+            rot(sa, ca, u, Ru, Dv);
+            T um[2] = {-u[0], -u[1]}; rot(sn, cn, um, Rnu, Dn);                     // D_ni = -R'(A_n)(U_n - U_i)
+            const T q0 = p0 - p(0, n), q1 = p1 - p(1, n), pan = p(2, n);
+            a0 += T(2) * q0 + Dv[0] * pa - Dn[0] * pan;
+            a1 += T(2) * q1 + Dv[1] * pa - Dn[1] * pan;
+            a2 += Dv[0] * (q0 + Dv[0] * pa) + Dv[1] * (q1 + Dv[1] * pa);
+        });
+        const T vf = (ci[0] >= T(0) && ci[1] >= T(0)) ? wf2 : T(0);
+        out[0] = vf * p0 + wr2 * a0; out[1] = vf * p1 + wr2 * a1; out[2] = wr2 * a2;
+    }
+    __device__ T modelCost(int x, int y, int, long s, const Vec<T>& dl) const {
+        T oi[2], ui[2], ci[2]; load2(O + s * 2, oi); load2(Ur + s * 2, ui); load2(Cn + s * 2, ci);
+        T sa, ca; sincos_t(A[s], sa, ca);
+        const T d0 = dl(0, s), d1 = dl(1, s), da = dl(2, s);
+        T sum = T(0);
+        if (ci[0] >= T(0) && ci[1] >= T(0)) {
+            T m0 = w_fit * (oi[0] - ci[0]) + w_fit * d0, m1 = w_fit * (oi[1] - ci[1]) + w_fit * d1;
+            sum += m0 * m0 + m1 * m1;
+        }
+        neighbours(x, y, s, [&](long n) {
+            T on[2], un[2]; load2(O + n * 2, on); load2(Ur + n * 2, un);
+            T u[2] = {ui[0] - un[0], ui[1] - un[1]}, Ru[2], Dv[2]; rot(sa, ca, u, Ru, Dv);
+            T m0 = w_reg * ((oi[0] - on[0]) - Ru[0]) + w_reg * ((d0 - dl(0, n)) + Dv[0] * da);
+            T m1 = w_reg * ((oi[1] - on[1]) - Ru[1]) + w_reg * ((d1 - dl(1, n)) + Dv[1] * da);
+            sum += m0 * m0 + m1 * m1;
+        });
+        return sum;
+    }
+};
+
+}  // namespace optk

@@ -1,0 +1,54 @@
+/* optk.h -- the thin C ABI between the C host (opt_api.c) and the CUDA engine (engine.cuh and the
+ * per-example translation units).  Plain pointers and scalars only.
+ *
+ * One OptK_Plan corresponds to the reference's PlanData (solverGPUGaussNewton.t:208-272): the
+ * solver vectors, the device-resident reduction scalars and the bound problem parameters.
+ * Each function launches the kernel(s) that replace one reference kernel or kernel group; the
+ * citation next to each gives the reference code it stands in for. */
+#ifndef OPTK_H
+#define OPTK_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct OptK_Plan OptK_Plan;
+
+/* Returns NULL (after printing why) if `energy` has no built-in functor set. */
+OptK_Plan* optk_create(const char* energy, int is_double, int is_lm, const unsigned* dims,
+                       int collect_timing);
+void  optk_destroy(OptK_Plan*);
+int   optk_has_energy(const char* energy);
+
+/* util.initParameters (util.t:677-721): image pointers, host scalars, graph index arrays */
+void  optk_bind(OptK_Plan*, void** problemparams);
+/* LM parameters that the reference injects as problem parameters (o.t:1575-1580) */
+void  optk_set_lm(OptK_Plan*, double trust_region_radius, double min_lm_diagonal, double max_lm_diagonal);
+
+void   optk_begin_call(OptK_Plan*);           /* order the plan's stream after the caller's default stream */
+void   optk_end_call(OptK_Plan*);             /* ... and the default stream after the plan's stream */
+
+void   optk_precompute(OptK_Plan*);           /* solver:1028-1039 */
+double optk_cost(OptK_Plan*);                 /* computeCost + computeCost_Graph + D2H (solver:1389-1441) */
+void   optk_pcg_begin(OptK_Plan*, int nIter); /* PCGInit1[_Graph,_Finish]; LM: SaveSSq, ComputeCtC[_Graph], FinalizeDiagonal */
+void   optk_pcg_iter(OptK_Plan*, int lIter, int residual_reset);  /* PCGStep1[_Graph], Step2 (or 1stHalf/Adelta/2ndHalf), Step3 */
+void   optk_pcg_run(OptK_Plan*, int lIterations);                  /* GN: the whole inner loop, no host sync */
+double optk_fetch_q(OptK_Plan*);              /* fetchQ (solver:1480-1501) */
+double optk_model_cost(OptK_Plan*);           /* computeModelCost[_Graph] + D2H (solver:1445-1476) */
+void   optk_save_unknowns(OptK_Plan*);        /* savePreviousUnknowns (solver:882-887) */
+void   optk_linear_update(OptK_Plan*);        /* PCGLinearUpdate (solver:854-859) */
+void   optk_revert_update(OptK_Plan*);        /* revertUpdate (solver:864-869) */
+
+/* statistics and debugging */
+long   optk_launch_count(OptK_Plan*);         /* kernels launched since creation */
+void   optk_print_timing(OptK_Plan*);         /* Kernel | Count | Total | Average table (backend_cuda.t:152-297) */
+int    optk_unknown_channels(OptK_Plan*);
+long   optk_site_count(OptK_Plan*);
+/* copies an internal solver vector ("delta","r","p","Ap","z","pre","CtC") to the host as AoS [site][U] of opt_float */
+int    optk_debug_read(OptK_Plan*, const char* name, void* host_out);
+/* out = J^T J p for a host AoS [site][U] direction (test hook; runs PCGStep1 on it) */
+void   optk_debug_apply_jtj(OptK_Plan*, const void* host_p, void* host_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,67 @@
+// registry.cu -- energy-name -> engine factory table and the extern "C" forwarding layer of optk.h.
+// Opt_ProblemDefine keys on the basename of the energy file (SURVEY.md 3.1 "New design"): each of
+// the shipped example energies is bound to a hand-written functor set; anything else is rejected.
+#include "engine.cuh"
+
+extern "C" {
+#define OPTK_DECL(name) OptK_Plan* optk_make_##name(int, int, const unsigned*, int);
+OPTK_DECL(poisson_image_editing)
+OPTK_DECL(image_warping)
+OPTK_DECL(volumetric_mesh_deformation)
+OPTK_DECL(optical_flow)
+OPTK_DECL(arap_mesh_deformation)
+#undef OPTK_DECL
+}
+
+namespace {
+struct Entry { const char* name; OptK_Plan* (*make)(int, int, const unsigned*, int); };
+const Entry kTable[] = {
+    {"poisson_image_editing", optk_make_poisson_image_editing},
+    {"image_warping", optk_make_image_warping},
+    {"volumetric_mesh_deformation", optk_make_volumetric_mesh_deformation},
+    {"optical_flow", optk_make_optical_flow},
+    {"arap_mesh_deformation", optk_make_arap_mesh_deformation},
+};
+const Entry* find(const char* energy) {
+    for (const Entry& e : kTable) if (!strcmp(e.name, energy)) return &e;
+    return nullptr;
+}
+}  // namespace
+
+extern "C" {
+
+int optk_has_energy(const char* energy) { return find(energy) != nullptr; }
+
+OptK_Plan* optk_create(const char* energy, int is_double, int is_lm, const unsigned* dims, int collect_timing) {
+    const Entry* e = find(energy);
+    if (!e) { fprintf(stderr, "Opt: energy '%s' has no built-in functor set\n", energy); return nullptr; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        fprintf(stderr, "Opt: no CUDA device available; this library has no CPU fallback\n");
+        return nullptr;
+    }
+    return e->make(is_double, is_lm, dims, collect_timing);
+}
+void optk_destroy(OptK_Plan* p) { delete p; }
+void optk_bind(OptK_Plan* p, void** pp) { p->bind(pp); }
+void optk_set_lm(OptK_Plan* p, double r, double mn, double mx) { p->set_lm(r, mn, mx); }
+void optk_begin_call(OptK_Plan* p) { p->begin_call(); }
+void optk_end_call(OptK_Plan* p) { p->end_call(); }
+void optk_precompute(OptK_Plan* p) { p->precompute(); }
+double optk_cost(OptK_Plan* p) { return p->cost(); }
+void optk_pcg_begin(OptK_Plan* p, int nIter) { p->pcg_begin(nIter); }
+void optk_pcg_iter(OptK_Plan* p, int l, int reset) { p->pcg_iter(l, reset); }
+void optk_pcg_run(OptK_Plan* p, int n) { p->pcg_run(n); }
+double optk_fetch_q(OptK_Plan* p) { return p->fetch_q(); }
+double optk_model_cost(OptK_Plan* p) { return p->model_cost(); }
+void optk_save_unknowns(OptK_Plan* p) { p->save_unknowns(); }
+void optk_linear_update(OptK_Plan* p) { p->linear_update(); }
+void optk_revert_update(OptK_Plan* p) { p->revert_update(); }
+long optk_launch_count(OptK_Plan* p) { return p->launches; }
+void optk_print_timing(OptK_Plan* p) { p->print_timing(); }
+int optk_unknown_channels(OptK_Plan* p) { return p->unknown_channels(); }
+long optk_site_count(OptK_Plan* p) { return p->site_count(); }
+int optk_debug_read(OptK_Plan* p, const char* name, void* out) { return p->debug_read(name, out); }
+void optk_debug_apply_jtj(OptK_Plan* p, const void* hp, void* out) { p->debug_apply_jtj(hp, out); }
+
+}  // extern "C"

@@ -160,29 +160,35 @@ def volumetric_synthetic(W, H, D, seed=1234, n_iter=2, l_iter=10):
                    {"nIterations": n_iter, "lIterations": l_iter})
 
 
-def optical_flow_synthetic(W, H, seed=1234, n_iter=3, l_iter=20, kind="gaussNewtonGPU"):
-    """I = sum of low-frequency sinusoids in [0,255]; I_hat = I translated by (+1.5,-0.75) px;
+def optical_flow_synthetic(W, H, seed=1234, n_iter=3, l_iter=20, kind="gaussNewtonGPU", shift=(0.4, -0.2)):
+    """I = sum of low-frequency sinusoids in [0,255]; I_hat = I translated by `shift` px (sub-pixel, so plain Gauss-Newton stays in the linear regime);
     dx,dy by the 3x3 kernel of examples/optical_flow/src/CombinedSolver.h:152-178."""
     rng = np.random.default_rng(seed)
     ys, xs = np.mgrid[0:H, 0:W].astype(np.float64)
+
+    fmax_x, fmax_y = max(1.0, min(4.0, W / 24.0)), max(1.0, min(4.0, H / 24.0))   # keep periods well above the shift
 
     def field(sx, sy):
         r = np.random.default_rng(seed + 1)
         out = np.zeros((H, W))
         for _ in range(8):
-            fx, fy, ph = r.uniform(0.5, 4.0), r.uniform(0.5, 4.0), r.uniform(0, 2 * np.pi)
+            fx, fy, ph = r.uniform(0.5, fmax_x), r.uniform(0.5, fmax_y), r.uniform(0, 2 * np.pi)
             out += np.sin(2 * np.pi * (fx * (xs + sx) / W + fy * (ys + sy) / H) + ph)
         return out
 
     lo, hi = field(0, 0).min(), field(0, 0).max()
     I = ((field(0, 0) - lo) / (hi - lo) * 255).astype(np.float32)
-    Ih = ((field(1.5, -0.75) - lo) / (hi - lo) * 255).astype(np.float32)
-    pad = np.pad(Ih, 1, mode="edge")
-    dx = ((pad[:-2, 2:] + pad[1:-1, 2:] + pad[2:, 2:]) - (pad[:-2, :-2] + pad[1:-1, :-2] + pad[2:, :-2])) / np.float32(8)
-    dy = ((pad[2:, :-2] + pad[2:, 1:-1] + pad[2:, 2:]) - (pad[:-2, :-2] + pad[:-2, 1:-1] + pad[:-2, 2:])) / np.float32(8)
-    X = (0.1 * rng.standard_normal((H, W, 2))).astype(np.float32)
+    Ih = ((field(shift[0], shift[1]) - lo) / (hi - lo) * 255).astype(np.float32)
+    # computeDU / computeDV: 3x3 differences / 8 in the interior, 0 on the 1-pixel border
+    dx = np.zeros((H, W), dtype=np.float32)
+    dy = np.zeros((H, W), dtype=np.float32)
+    c = Ih
+    dx[1:-1, 1:-1] = ((c[:-2, 2:] + c[1:-1, 2:] + c[2:, 2:]) - (c[:-2, :-2] + c[1:-1, :-2] + c[2:, :-2])) / np.float32(8)
+    dy[1:-1, 1:-1] = ((c[2:, :-2] + c[2:, 1:-1] + c[2:, 2:]) - (c[:-2, :-2] + c[:-2, 1:-1] + c[:-2, 2:])) / np.float32(8)
+    X = np.zeros((H, W, 2), dtype=np.float32)            # driver starts from zero flow (resetFlowVectors)
+    X[1:-1, 1:-1] = (0.1 * rng.standard_normal((H - 2, W - 2, 2))).astype(np.float32)   # off-grid sample positions
     w_fit, w_reg = np.sqrt(np.float32(10.0)), np.sqrt(np.float32(0.1))
-    return Problem("optical_flow.t", [W, H], [w_fit, w_reg, X, I, Ih, dx.astype(np.float32), dy.astype(np.float32)], [2],
+    return Problem("optical_flow.t", [W, H], [w_fit, w_reg, X, I, Ih, dx, dy], [2],
                    {"nIterations": n_iter, "lIterations": l_iter}, kind=kind)
 
 

@@ -1,0 +1,77 @@
+"""CPU: the oracle against the reference's own golden final costs
+(examples/test_final_cost.py:56-66, acceptance rel. error < 1e-5 at :117-122)."""
+import os
+
+import numpy as np
+import pytest
+
+from opt_b200 import examples
+from oracle_api import OracleSolver
+
+GOLDEN = [
+    ("image_warping_cat512.npz", examples.image_warping_golden),
+    ("volumetric_head.npz", examples.volumetric_golden),
+]
+
+
+@pytest.mark.parametrize("fname,builder", GOLDEN)
+@pytest.mark.parametrize("double", [False, True])
+def test_oracle_matches_reference_final_cost(built, golden_dir, fname, builder, double):
+    d = np.load(os.path.join(golden_dir, fname))
+    pr = builder(d)
+    if double:
+        pr = pr.as_double()
+    s = OracleSolver(pr.dims, pr.energy, pr.kind, double=double, threads=4)
+    s.set_params(nIterations=1, lIterations=1)
+    cost = s.solve(pr.params)
+    golden = float(d["golden_cost"])
+    assert abs(cost - golden) / golden < 1e-5, (cost, golden)
+
+
+def test_oracle_thread_count_does_not_change_result(built, golden_dir):
+    d = np.load(os.path.join(golden_dir, "image_warping_cat512.npz"))
+    costs = []
+    for th in (1, 4):
+        pr = examples.image_warping_golden(d)
+        s = OracleSolver(pr.dims, pr.energy, threads=th)
+        s.set_params(nIterations=2, lIterations=3)
+        costs.append(s.solve(pr.params))
+    assert abs(costs[0] - costs[1]) <= 1e-6 * abs(costs[0])
+
+
+def test_oracle_rejects_unknown_energy(built):
+    from oracle_api import lib
+    from opt_b200 import capi
+    f = capi.bind(lib(), "OptOracle_")
+    st = f["NewState"](capi.Opt_InitializationParameters())
+    assert not f["ProblemDefine"](st, b"no_such_energy.t", b"gaussNewtonGPU")
+
+
+@pytest.mark.parametrize("builder,args", [
+    (examples.poisson_synthetic, (24, 17)),
+    (examples.optical_flow_synthetic, (21, 16)),
+    (examples.arap_synthetic, (7, 6)),
+    (examples.volumetric_synthetic, (5, 6, 4)),
+])
+@pytest.mark.parametrize("kind", ["gaussNewtonGPU", "LMGPU"])
+def test_oracle_cost_decreases(built, builder, args, kind):
+    pr = builder(*args)
+    s = OracleSolver(pr.dims, pr.energy, kind, threads=2)
+    s.set_params(nIterations=3, lIterations=8)
+    s.solve(pr.params)
+    h = s.cost_history()
+    assert h[-1] < h[0] and np.isfinite(h[-1]), h
+
+
+def test_oracle_jtj_is_symmetric_psd(built):
+    """Size-independent property: p.(J^T J q) == q.(J^T J p) and p.(J^T J p) >= 0."""
+    pr = examples.image_warping_synthetic(19, 14).as_double()
+    s = OracleSolver(pr.dims, pr.energy, double=True)
+    rng = np.random.default_rng(0)
+    n = s.unknown_count()
+    mask = (pr.params[4] == 0).reshape(-1)
+    p = rng.standard_normal(n) * np.repeat(mask, 3)
+    q = rng.standard_normal(n) * np.repeat(mask, 3)
+    Ap, Aq = s.apply_jtj(pr.params, p), s.apply_jtj(pr.params, q)
+    assert abs(q @ Ap - p @ Aq) < 1e-9 * abs(q @ Ap)
+    assert p @ Ap >= 0

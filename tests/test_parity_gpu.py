@@ -1,0 +1,101 @@
+"""GPU: the CUDA engine (through the C-ABI) against the CPU oracle on identical seeded inputs, and
+against the reference's golden final costs."""
+import os
+
+import numpy as np
+import pytest
+
+from opt_b200 import examples
+from gpu_util import (OP_RTOL, assert_costs_close, assert_unknowns_close, run_gpu, run_oracle)
+
+pytestmark = pytest.mark.gpu
+
+CASES = {
+    "poisson": (examples.poisson_synthetic, (67, 45), dict(n_iter=2, l_iter=12)),
+    "poisson_aligned": (examples.poisson_synthetic, (128, 64), dict(n_iter=1, l_iter=20)),
+    "image_warping": (examples.image_warping_synthetic, (61, 47), dict(n_iter=3, l_iter=10)),
+    "volumetric": (examples.volumetric_synthetic, (11, 9, 7), dict(n_iter=3, l_iter=10)),
+    "optical_flow": (examples.optical_flow_synthetic, (53, 38), dict(n_iter=3, l_iter=10)),
+    "arap": (examples.arap_synthetic, (13, 11), dict(n_iter=3, l_iter=10)),
+}
+
+
+def make(case, kind="gaussNewtonGPU", double=False):
+    b, args, kw = CASES[case]
+    pr = b(*args, **kw)
+    pr.kind = kind
+    return pr.as_double() if double else pr
+
+
+@pytest.mark.parametrize("double", [False, True])
+@pytest.mark.parametrize("kind", ["gaussNewtonGPU", "LMGPU"])
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_solve_matches_oracle(built, case, kind, double):
+    pr = make(case, kind, double)
+    gc, gx, sol, _ = run_gpu(pr)
+    rc, rx, _ = run_oracle(pr)
+    assert_costs_close(gc, rc, double)
+    assert_unknowns_close(gx, rx, double)
+    assert sol.launch_count() > 0
+
+
+@pytest.mark.parametrize("double", [False, True])
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_jtf_and_jtj_match_oracle(built, case, double):
+    """One application of the operators at the initial unknowns: r = -J^T F, the preconditioner and
+    J^T J p for a random p (zero at excluded sites)."""
+    from opt_b200 import solver as S
+    from oracle_api import OracleSolver
+    pr = make(case, double=double)
+    named = S.upload(pr)
+    sol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=double)
+    o = OracleSolver(pr.dims, pr.energy, pr.kind, double=double, threads=4)
+    dt = np.float64 if double else np.float32
+    sol.debug_pcg_begin(named)
+    r_gpu, pre_gpu = sol.debug_read("r"), sol.debug_read("pre")
+    r_ref, pre_ref = o.eval_jtf(pr.params, dt)
+    tol = OP_RTOL[double]
+    assert np.abs(r_gpu - r_ref).max() <= tol * np.abs(r_ref).max()
+    assert np.abs(pre_gpu - pre_ref).max() <= tol * np.abs(pre_ref).max()
+    rng = np.random.default_rng(7)
+    p = rng.standard_normal(r_ref.shape).astype(dt) * (r_ref != 0)      # excluded sites carry p = 0
+    ap_gpu = sol.debug_apply_jtj(named, p)
+    ap_ref = o.apply_jtj(pr.params, p)
+    assert np.abs(ap_gpu - ap_ref).max() <= tol * np.abs(ap_ref).max()
+
+
+GOLDEN = [("image_warping_cat512.npz", examples.image_warping_golden),
+          ("volumetric_head.npz", examples.volumetric_golden)]
+
+
+@pytest.mark.parametrize("fname,builder", GOLDEN)
+def test_reference_golden_final_cost(built, golden_dir, fname, builder):
+    """examples/test_final_cost.py:56-66 with its own acceptance threshold (rel. error < 1e-5)."""
+    d = np.load(os.path.join(golden_dir, fname))
+    pr = builder(d)
+    gc, _, _, _ = run_gpu(pr)
+    golden = float(d["golden_cost"])
+    assert abs(gc[-1] - golden) / golden < 1e-5, (gc, golden)
+
+
+def test_final_cost_line_and_timing_table(built, capfd):
+    """stdout contract: `final cost=` line (solver:1903) that the reference's tests regex."""
+    import re
+    from opt_b200 import solver as S
+    pr = make("poisson")
+    named = S.upload(pr)
+    sol = S.OptSolver(pr.dims, pr.energy, pr.kind, verbosity=1, timing=True)
+    cost = sol.solve(pr.solver, named)
+    out = capfd.readouterr().out
+    m = re.search("final cost=(.*)", out)
+    assert m and abs(float(m.group(1)) - cost) <= 1e-6 * cost
+    assert "PCGStep1" in out and "PCGStep2" in out
+
+
+def test_solve_equals_init_step_loop(built):
+    from opt_b200 import solver as S
+    pr = make("image_warping")
+    a = S.OptSolver(pr.dims, pr.energy, pr.kind)
+    ca = a.solve_blocking(pr.solver, S.upload(pr))
+    gc, _, _, _ = run_gpu(pr)
+    assert abs(ca - gc[-1]) <= 1e-6 * abs(ca)
