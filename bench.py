@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""bench.py -- PCG iterations/s and solve time of the GN/LM + PCG hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+A "step" is one complete Opt_ProblemSolve of the workload (Init, nIterations Gauss-Newton steps of
+lIterations PCG iterations each, final cost).  Default workload at N=1 is BASELINE.json configs[1]:
+poisson_image_editing on a synthetic 4096x4096 float4 image, Gauss-Newton + PCG, fp32
+(nIterations=1, lIterations=100).  Rank 0 prints ONE JSON line.
+
+  value      PCG iterations/s with every input already resident in HBM (device arrays handed to
+             the C-ABI); the unknown image is restored by a device-to-device copy each step.
+  e2e        same metric through the same C-ABI call sequence but starting from pinned HOST
+             buffers: H2D of every image and D2H of the solved unknown inside the timed region.
+  roofline   dominant kernel (PCGStep1 = J^T J p): algorithmic bytes / cudaEvent duration measured
+             live by the library's per-kernel timer, against MEASURED_PEAKS.json.
+  cpu_baseline  the CPU oracle (a port of the reference's backend_cpu/_mt path; the reference
+             itself is Terra and cannot be built here) timed on this box's host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+from opt_b200 import examples  # noqa: E402
+
+# name -> (builder, full-size args, solver kwargs, U, algorithmic bytes/site/PCG-iteration fp32,
+#          PCGStep1 bytes/site) ; byte figures from SURVEY.md section 8(d)
+WORKLOADS = {
+    "poisson_4096": dict(builder=examples.poisson_synthetic, args=(4096, 4096), kw=dict(n_iter=1, l_iter=100),
+                         U=4, bytes_iter=220, bytes_step1=(2 * 4 + 0 + 1) * 4,
+                         desc="poisson_image_editing 4096x4096 float4, GN 1x100 PCG, fp32"),
+    "image_warping_512": dict(builder=examples.image_warping_synthetic, args=(512, 512), kw=dict(n_iter=8, l_iter=400),
+                              U=3, bytes_iter=200, bytes_step1=(2 * 3 + 8 + 1) * 4,
+                              desc="image_warping 512x512, GN 8x400 PCG, fp32"),
+    "optical_flow_2048": dict(builder=examples.optical_flow_synthetic, args=(2048, 2048), kw=dict(n_iter=10, l_iter=50),
+                              U=2, bytes_iter=120, bytes_step1=(2 * 2 + 4) * 4,
+                              desc="optical_flow 2048x2048, GN 10x50 PCG, fp32"),
+    "volumetric_512": dict(builder=examples.volumetric_synthetic, args=(512, 512, 512), kw=dict(n_iter=2, l_iter=20),
+                           U=6, bytes_iter=348, bytes_step1=(2 * 6 + 9) * 4,
+                           desc="volumetric_mesh_deformation 512^3, GN 2x20 PCG, fp32"),
+    "volumetric_256": dict(builder=examples.volumetric_synthetic, args=(256, 256, 256), kw=dict(n_iter=2, l_iter=20),
+                           U=6, bytes_iter=348, bytes_step1=(2 * 6 + 9) * 4,
+                           desc="volumetric_mesh_deformation 256^3, GN 2x20 PCG, fp32"),
+    "arap_1m": dict(builder=examples.arap_synthetic, args=(1024, 1024), kw=dict(n_iter=2, l_iter=100),
+                    U=6, bytes_iter=396, bytes_step1=(2 * 6 + 9) * 4 + 48,
+                    desc="arap_mesh_deformation 1024x1024-vertex mesh (6.28M directed edges), GN 2x100 PCG, fp32"),
+}
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) >= 6 and r[2 + k] == "Active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def make_problem(name, size=None):
+    w = WORKLOADS[name]
+    args = tuple(size) if size else w["args"]
+    return w["builder"](*args, **w["kw"]), w
+
+
+def pcg_iterations(pr):
+    return int(pr.solver["nIterations"]) * int(pr.solver["lIterations"])
+
+
+# ------------------------------------------------------------------------------ CPU oracle legs
+def cpu_pcg_rate(pr, threads, budget_s=20.0):
+    """PCG iterations/s of the CPU oracle on the full-size workload.  Two bounded solves with L1 and
+    L2 PCG iterations are timed; the rate is (L2-L1)/(t2-t1), which removes the per-solve overhead
+    (cost evaluation, PCGInit1, update) that a 100-iteration solve would amortise."""
+    from oracle_api import OracleSolver
+
+    def timed(l_iter):
+        q = pr.clone()
+        o = OracleSolver(q.dims, q.energy, q.kind, double=q.double, threads=threads)
+        o.set_params(nIterations=1, lIterations=l_iter)
+        t = time.perf_counter()
+        o.solve(q.params)
+        dt = time.perf_counter() - t
+        o.close()
+        return dt
+
+    t1 = timed(1)
+    per_iter_guess = max(t1 / 4.0, 1e-4)
+    l2 = int(min(40, max(3, 1 + (budget_s - 2 * t1) / per_iter_guess)))
+    t2 = timed(l2)
+    rate = (l2 - 1) / max(t2 - t1, 1e-9)
+    sample = "full-size workload, 2 solves with lIterations=1 and %d (%.1fs + %.1fs); rate=(%d-1)/(t2-t1)" % (l2, t1, t2, l2)
+    return rate, sample, t1 + t2
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def run_reference(args, pr, w):
+    """--impl reference: the reference's CPU solver path on the host cores.  The reference is
+    Lua/Terra and cannot be built in this image, so this is the oracle port (kind "port")."""
+    threads = host_threads()
+    rates, samples = [], []
+    for _ in range(args.warmup):
+        pass                                            # nothing to warm on the CPU path
+    t0 = time.perf_counter()
+    for _ in range(max(1, args.steps)):
+        rate, sample, _ = cpu_pcg_rate(pr, threads, budget_s=max(4.0, 40.0 / max(1, args.steps)))
+        rates.append(rate)
+        samples.append(sample)
+    wall = time.perf_counter() - t0
+    rate = float(np.median(rates))
+    line = {
+        "impl": "reference", "metric": "pcg_iterations_per_second", "value": rate, "unit": "PCG iters/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1000.0 * pcg_iterations(pr) / rate, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": w["desc"], "dims": pr.dims, "timing": "host wall clock", "wall_s": wall},
+        "cpu_baseline": {"value": rate, "unit": "PCG iters/s", "cores": threads, "kind": "port", "sample": samples[0]},
+        "e2e": {"value": rate, "unit": "PCG iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------ GPU arm
+def run_ours(args, pr, w, rank, world):
+    import torch
+    import torch.distributed as dist
+    from opt_b200 import solver as S
+
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0)))
+    torch.cuda.set_device(dev)
+    img_idx = [i for i, p in enumerate(pr.params) if isinstance(p, np.ndarray)]
+    host = {i: torch.from_numpy(pr.params[i]).pin_memory() for i in img_idx}
+    devt = {i: host[i].to(dev, non_blocking=True) for i in img_idx}
+    pristine = {i: devt[i].clone() for i in pr.unknowns}
+    named = S.NamedParameters()
+    for i, p in enumerate(pr.params):
+        named.set("p%d" % i, devt[i] if i in devt else p)
+    sol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=pr.double, verbosity=0, timing=False)
+    sol.set_solver_parameters(pr.solver)
+    iters = pcg_iterations(pr)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        for i in pr.unknowns:
+            devt[i].copy_(pristine[i], non_blocking=True)
+        sol.init(named)
+        while sol.step():
+            pass
+        return sol.current_cost()
+
+    out_host = {i: torch.empty_like(host[i]).pin_memory() for i in pr.unknowns}
+
+    def step_e2e():
+        for i in img_idx:
+            devt[i].copy_(host[i], non_blocking=True)
+        sol.init(named)
+        while sol.step():
+            pass
+        for i in pr.unknowns:
+            out_host[i].copy_(devt[i], non_blocking=True)
+        torch.cuda.synchronize()
+        return sol.current_cost()
+
+    def timed(fn, steps, warmup, sample_clocks):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        clk = ClockSampler(dev.index or 0) if sample_clocks else None
+        if clk:
+            clk.start()
+        l0 = sol.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        cost = None
+        for _ in range(steps):
+            cost = fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, cost, (clk.stop() if clk else None), sol.launch_count() - l0
+
+    ms, cost, clocks, launches = timed(step_resident, args.steps, args.warmup, True)
+    ms_e2e, cost_e2e, _, _ = timed(step_e2e, max(1, min(args.steps, 3)), 1, False)
+    e2e_steps = max(1, min(args.steps, 3))
+    h2d = sum(host[i].numel() * host[i].element_size() for i in img_idx)
+    d2h = sum(out_host[i].numel() * out_host[i].element_size() for i in pr.unknowns) + 8
+
+    # per-kernel time of the dominant kernel, measured live with the library's cudaEvent timer
+    roof = None
+    if rank == 0:
+        tsol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=pr.double, verbosity=0, timing=True)
+        tsol.set_solver_parameters(pr.solver)
+        for rep in range(2):
+            for i in pr.unknowns:
+                devt[i].copy_(pristine[i])
+            tsol.reset_timing()
+            tsol.init(named)
+            while tsol.step():
+                pass
+        torch.cuda.synchronize()
+        kt = {k: tsol.kernel_time(k) for k in ("PCGStep1", "PCGStep1_Graph", "PCGStep2", "PCGStep3", "PCGInit1", "computeCost")}
+        n1, t1 = kt["PCGStep1"]
+        peak, peak_src = load_peaks()
+        N = sol.site_count()
+        if n1:
+            per_launch_ms = t1 / n1
+            alg = w["bytes_step1"] * N
+            ach = alg / (per_launch_ms * 1e-3) / 1e9
+            roof = {"bound": "hbm", "kernel": "PCGStep1", "achieved": ach, "peak": peak, "unit": "GB/s",
+                    "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": alg, "ms_per_launch": per_launch_ms,
+                    "kernel_ms": {k: (v[1] / v[0] if v[0] else None) for k, v in kt.items()},
+                    "iteration": {"algorithmic_bytes": w["bytes_iter"] * N,
+                                  "achieved": w["bytes_iter"] * N * (iters * args.steps / (ms * 1e-3)) / 1e9,
+                                  "frac": w["bytes_iter"] * N * (iters * args.steps / (ms * 1e-3)) / 1e9 / peak}}
+        tsol.close()
+
+    total_iters = iters * args.steps * world          # weak scaling: every rank solves its own slab/replica
+    value = total_iters / (ms * 1e-3) / (world if args.scaling_mode == "slab" else 1)
+    if rank != 0:
+        return
+    cpu = None
+    if not args.no_cpu and world == 1:
+        threads = host_threads()
+        rate, sample, _ = cpu_pcg_rate(pr, threads, budget_s=args.cpu_budget)
+        cpu = {"value": rate, "unit": "PCG iters/s", "cores": threads, "kind": "port", "sample": sample}
+    line = {
+        "metric": "pcg_iterations_per_second", "value": value, "unit": "PCG iters/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32" if not pr.double else "f64", "data": "synthetic",
+        "config": {"workload": w["desc"], "dims": pr.dims, "pcg_iterations_per_step": iters,
+                   "l2": "inputs larger than L2 (each solver vector is %.0f MB)" % (w["U"] * sol.site_count() * 4 / 1e6),
+                   "final_cost": cost, "parallelism": "1 GPU" if world == 1 else "%d ranks" % world},
+        "clocks": clocks,
+        "e2e": {"value": iters * e2e_steps * (world if args.scaling_mode != "slab" else 1) / (ms_e2e * 1e-3),
+                "unit": "PCG iters/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": ms_e2e / e2e_steps, "final_cost": cost_e2e},
+        "gpu_launches": launches,
+        "roofline": roof,
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="poisson_4096", choices=sorted(WORKLOADS))
+    ap.add_argument("--size", type=int, nargs="+", default=None, help="override the workload's grid size")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-budget", type=float, default=20.0)
+    ap.add_argument("--scaling-mode", default="replica", choices=["replica", "slab"])
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    pr, w = make_problem(args.workload, args.size)
+    if args.impl == "reference":
+        if rank == 0:
+            run_reference(args, pr, w)
+        return
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl")
+    run_ours(args, pr, w, rank, world)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -14,6 +14,10 @@ void OptB200_FreeState(Opt_State* state);
 
 /* Kernels launched by this plan since it was created (bench.py's "gpu_launches"). */
 long OptB200_PlanLaunchCount(Opt_Plan* plan);
+/* With collectPerKernelTimingInfo set: number of launches of `kernel` (the reference's kernel
+ * names, e.g. "PCGStep1") since the last reset and their summed cudaEvent duration in ms. */
+int  OptB200_PlanKernelTime(Opt_Plan* plan, const char* kernel, double* total_ms);
+void OptB200_PlanResetTiming(Opt_Plan* plan);
 int  OptB200_PlanUnknownChannels(Opt_Plan* plan);   /* U */
 long OptB200_PlanSiteCount(Opt_Plan* plan);         /* N */
 

@@ -87,6 +87,19 @@ struct OptK_Plan {
         kernel<<<grid, block, 0, stream>>>(args...);
         post_launch();
     }
+    // total milliseconds and launch count of all timed launches called `name` (timing must be on)
+    int kernel_time(const char* name, double* total_ms) {
+        OPTK_CUDA(cudaStreamSynchronize(stream));
+        int n = 0; double tot = 0;
+        for (auto& t : timed) if (!strcmp(t.name, name)) { float ms = 0; cudaEventElapsedTime(&ms, t.a, t.b); tot += ms; ++n; }
+        *total_ms = tot;
+        return n;
+    }
+    void reset_timing() {
+        OPTK_CUDA(cudaStreamSynchronize(stream));
+        for (auto& t : timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+        timed.clear();
+    }
     void print_timing() {                                    // backend_cuda.t:262-297
         if (!timing || timed.empty()) return;
         OPTK_CUDA(cudaStreamSynchronize(stream));

@@ -270,6 +270,10 @@ double Opt_ProblemCurrentCost(Opt_State* state, Opt_Plan* plan) { /* solver:2354
 
 /* ---- OptB200.h extensions (no counterpart in the reference) -------------------------------- */
 long OptB200_PlanLaunchCount(Opt_Plan* plan) { return optk_launch_count(plan->k); }
+int OptB200_PlanKernelTime(Opt_Plan* plan, const char* kernel, double* total_ms) {
+    return optk_kernel_time(plan->k, kernel, total_ms);
+}
+void OptB200_PlanResetTiming(Opt_Plan* plan) { optk_reset_timing(plan->k); }
 int OptB200_PlanUnknownChannels(Opt_Plan* plan) { return optk_unknown_channels(plan->k); }
 long OptB200_PlanSiteCount(Opt_Plan* plan) { return optk_site_count(plan->k); }
 int OptB200_DebugReadVector(Opt_Plan* plan, const char* name, void* host_out) {

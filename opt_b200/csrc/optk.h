@@ -41,6 +41,8 @@ void   optk_revert_update(OptK_Plan*);        /* revertUpdate (solver:864-869) *
 /* statistics and debugging */
 long   optk_launch_count(OptK_Plan*);         /* kernels launched since creation */
 void   optk_print_timing(OptK_Plan*);         /* Kernel | Count | Total | Average table (backend_cuda.t:152-297) */
+int    optk_kernel_time(OptK_Plan*, const char* kernel, double* total_ms);   /* returns launch count */
+void   optk_reset_timing(OptK_Plan*);
 int    optk_unknown_channels(OptK_Plan*);
 long   optk_site_count(OptK_Plan*);
 /* copies an internal solver vector ("delta","r","p","Ap","z","pre","CtC") to the host as AoS [site][U] of opt_float */

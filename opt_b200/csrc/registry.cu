@@ -59,6 +59,8 @@ void optk_linear_update(OptK_Plan* p) { p->linear_update(); }
 void optk_revert_update(OptK_Plan* p) { p->revert_update(); }
 long optk_launch_count(OptK_Plan* p) { return p->launches; }
 void optk_print_timing(OptK_Plan* p) { p->print_timing(); }
+int optk_kernel_time(OptK_Plan* p, const char* k, double* ms) { return p->kernel_time(k, ms); }
+void optk_reset_timing(OptK_Plan* p) { p->reset_timing(); }
 int optk_unknown_channels(OptK_Plan* p) { return p->unknown_channels(); }
 long optk_site_count(OptK_Plan* p) { return p->site_count(); }
 int optk_debug_read(OptK_Plan* p, const char* name, void* out) { return p->debug_read(name, out); }

@@ -124,7 +124,7 @@ def poisson_synthetic(W, H, seed=1234, n_iter=1, l_iter=100):
                    {"nIterations": n_iter, "lIterations": l_iter})
 
 
-def image_warping_synthetic(W, H, seed=1234, n_iter=2, l_iter=10):
+def image_warping_synthetic(W, H, seed=1234, n_iter=2, l_iter=10, noise=0.02):
     rng = np.random.default_rng(seed)
     ys, xs = np.mgrid[0:H, 0:W]
     mask = np.where(((xs - W / 2) ** 2 + (ys - H / 2) ** 2) < (0.45 * min(W, H)) ** 2, 0, 255).astype(np.uint8)
@@ -134,7 +134,7 @@ def image_warping_synthetic(W, H, seed=1234, n_iter=2, l_iter=10):
         cons.append([x, y, x + int(rng.integers(-5, 6)), y + int(rng.integers(-5, 6))])
     pr = image_warping(mask, cons, n_iter=n_iter, l_iter=l_iter)
     pr.params[1] = (0.05 * rng.standard_normal((H, W))).astype(np.float32)          # non-trivial angles
-    pr.params[0] = (pr.params[0] + 0.3 * rng.standard_normal((H, W, 2))).astype(np.float32)
+    pr.params[0] = (pr.params[0] + noise * rng.standard_normal((H, W, 2))).astype(np.float32)
     return pr
 
 

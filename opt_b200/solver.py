@@ -38,6 +38,9 @@ def load_library():
         _lib.OptB200_FreeState.argtypes = [P]
         _lib.OptB200_PlanLaunchCount.restype = C.c_long
         _lib.OptB200_PlanLaunchCount.argtypes = [P]
+        _lib.OptB200_PlanKernelTime.restype = C.c_int
+        _lib.OptB200_PlanKernelTime.argtypes = [P, C.c_char_p, C.POINTER(C.c_double)]
+        _lib.OptB200_PlanResetTiming.argtypes = [P]
         _lib.OptB200_PlanUnknownChannels.restype = C.c_int
         _lib.OptB200_PlanUnknownChannels.argtypes = [P]
         _lib.OptB200_PlanSiteCount.restype = C.c_long
@@ -149,6 +152,15 @@ class OptSolver:
     # --- OptB200.h extensions --------------------------------------------------------------------
     def launch_count(self):
         return self.lib.OptB200_PlanLaunchCount(self.plan)
+
+    def kernel_time(self, name):
+        """(launch count, total ms) of the kernels timed under `name` (needs timing=True)."""
+        ms = C.c_double(0.0)
+        n = self.lib.OptB200_PlanKernelTime(self.plan, name.encode(), C.byref(ms))
+        return n, ms.value
+
+    def reset_timing(self):
+        self.lib.OptB200_PlanResetTiming(self.plan)
 
     def unknown_channels(self):
         return self.lib.OptB200_PlanUnknownChannels(self.plan)

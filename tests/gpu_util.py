@@ -33,9 +33,9 @@ def run_oracle(pr, threads=4):
     return o.cost_history(), xs, o
 
 
-def assert_costs_close(gpu_costs, ref_costs, double):
+def assert_costs_close(gpu_costs, ref_costs, double, tol=None):
     assert len(gpu_costs) == len(ref_costs), (gpu_costs, ref_costs)
-    tol = COST_RTOL[double]
+    tol = COST_RTOL[double] if tol is None else tol
     for k, (a, b) in enumerate(zip(gpu_costs, ref_costs)):
         assert np.isfinite(a) and abs(a - b) <= tol * abs(b), "cost after step %d: gpu %r oracle %r" % (k, a, b)
 
