@@ -12,6 +12,21 @@ extern "C" {
 /* The reference never frees an Opt_State (createwrapper.t has no destructor); this one can be. */
 void OptB200_FreeState(Opt_State* state);
 
+/* ---- multi-GPU domain decomposition (new; the reference is single-device) ---------------------
+ * One process per GPU.  A 2-D / 3-D grid problem is cut into slabs along its slowest dimension
+ * (d1 for 2-D, d2 for 3-D).  Each rank plans its LOCAL slab: its owned rows/planes plus `halo`
+ * ghost rows/planes on every side that faces another rank, i.e. `dimensions` passed to
+ * Opt_ProblemPlan and every array in `problemparams` cover owned + ghost rows.  The caller fills
+ * all arrays (ghost rows included) before Opt_ProblemInit; afterwards the engine keeps the ghost
+ * rows of the unknown images current (NCCL send/recv after every update), exchanges the PCG
+ * search direction once per PCG iteration and all-reduces the PCG scalars and the costs.
+ * halo = 1 for every shipped grid example except shape_from_shading (2).
+ * Usage: rank 0 calls OptB200_GetNcclUniqueId and sends the 128 bytes to every rank (MPI,
+ * torch.distributed, a file ...); then EVERY rank calls OptB200_PlanSetSlab (collective) once,
+ * after Opt_ProblemPlan and before Opt_ProblemInit.  Returns 0 on success. */
+void OptB200_GetNcclUniqueId(void* out128);
+int  OptB200_PlanSetSlab(Opt_Plan* plan, int rank, int nranks, int halo, const void* nccl_unique_id);
+
 /* Kernels launched by this plan since it was created (bench.py's "gpu_launches"). */
 long OptB200_PlanLaunchCount(Opt_Plan* plan);
 /* With collectPerKernelTimingInfo set: number of launches of `kernel` (the reference's kernel

@@ -61,7 +61,7 @@ def build(verbose=False, oracle=True):
             if log:
                 sys.stderr.write(log)
     if _stale(LIB, objs):
-        cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-ccbin", HOST_CXX, "-lcudart"]
+        cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-ccbin", HOST_CXX, "-lcudart", "-lnccl"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed: %s\n%s" % (" ".join(cmd), r.stderr))

@@ -13,8 +13,20 @@
 #include <map>
 #include <string>
 #include <vector>
+#include <nccl.h>
 #include "common.cuh"
 #include "optk.h"
+
+#define OPTK_NCCL(call)                                                                        \
+    do {                                                                                       \
+        ncclResult_t r_ = (call);                                                              \
+        if (r_ != ncclSuccess) {                                                               \
+            printf("NCCL reported error %d: %s\nIn call: %s\nIn file: %s:%d\n", (int)r_,       \
+                   ncclGetErrorString(r_), #call, __FILE__, __LINE__);                         \
+            fflush(stdout);                                                                    \
+            exit(200 + (int)r_);                                                               \
+        }                                                                                      \
+    } while (0)
 
 // The C handle is the abstract base class of every Engine<F>.
 struct OptK_Plan {
@@ -35,6 +47,7 @@ struct OptK_Plan {
     virtual long site_count() const = 0;
     virtual int debug_read(const char* name, void* host_out) = 0;
     virtual void debug_apply_jtj(const void* host_p, void* host_out) = 0;
+    virtual int set_slab(int rank, int nranks, int halo, const void* nccl_unique_id) = 0;
 
     // ---- launch bookkeeping shared by all engines -------------------------------------------
     cudaStream_t stream = nullptr;
@@ -128,7 +141,10 @@ __device__ __forceinline__ bool thread_site(const F& f, int& x, int& y, int& z, 
     y = blockIdx.y * blockDim.y + threadIdx.y;
     z = blockIdx.z * blockDim.z + threadIdx.z;
     s = x + (long)f.W * (y + (long)f.H * z);
-    return x < f.W && y < f.H && z < f.D;
+    // slab mode: only rows (2-D) / planes (3-D) [o_lo, o_hi) are owned by this rank; the rest of the
+    // local array are ghost copies of the neighbours' boundary and are only ever read
+    const int slow = F::ND == 3 ? z : y;
+    return x < f.W && y < f.H && z < f.D && slow >= f.o_lo && slow < f.o_hi;
 }
 
 // ------------------------------------------------------------------------------ site kernels
@@ -479,6 +495,9 @@ struct Engine : OptK_Plan {
     double* h_scal = nullptr;    // pinned
     T radius = 0, min_diag = 0, max_diag = 0;
     dim3 sgrid, sblock;
+    // slab decomposition along the slowest dimension; nranks == 1: single GPU
+    int rank = 0, nranks = 1, halo = 0;
+    ncclComm_t comm = nullptr;
 
     Engine(const unsigned* dims, bool is_lm, bool collect_timing) : lm(is_lm) {
         base_init(collect_timing);
@@ -509,6 +528,7 @@ struct Engine : OptK_Plan {
     ~Engine() override {
         cudaStreamSynchronize(stream);
         f.free_temporaries();
+        if (comm) ncclCommDestroy(comm);
         cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal);
         base_destroy();
     }
@@ -521,6 +541,53 @@ struct Engine : OptK_Plan {
     long flat_vecs() const { return (long)U * Npad / VecIO<T>::W; }
     dim3 flat_grid() const { return dim3((unsigned)((flat_vecs() + 255) / 256)); }
     dim3 edge_grid() const { return dim3((unsigned)((E + 255) / 256)); }
+
+    // ---- multi-GPU: ownership, scalar all-reduce, halo exchange ---------------------------------
+    int set_slab(int rk, int nr, int h, const void* uid) override {
+        if (F::ND < 2 || GRAPH) { fprintf(stderr, "Opt: slab decomposition is only available for 2-D/3-D grid problems\n"); return -1; }
+        const int L = F::ND == 3 ? f.D : f.H;
+        rank = rk; nranks = nr; halo = h;
+        f.o_lo = rank > 0 ? halo : 0;
+        f.o_hi = rank < nranks - 1 ? L - halo : L;
+        if (f.o_hi - f.o_lo < halo) { fprintf(stderr, "Opt: slab thinner than its halo\n"); return -1; }
+        if (nranks > 1) {
+            ncclUniqueId id; memcpy(&id, uid, sizeof(id));
+            OPTK_NCCL(ncclCommInitRank(&comm, nranks, id, rank));
+        }
+        return 0;
+    }
+    void reduce(int slot, int count = 1) {                  // sum over ranks, in place, device-resident
+        if (nranks > 1) { OPTK_NCCL(ncclAllReduce(scal + slot, scal + slot, count, ncclDouble, ncclSum, comm, stream)); }
+    }
+    // ghost rows/planes of a contiguous array with `nplanes` planes of stride `pstride` elements,
+    // `rowsz` elements per row (2-D) or per plane (3-D) of the slowest dimension
+    template <class E_>
+    void exchange_raw(E_* base, int nplanes, size_t pstride, size_t rowsz) {
+        if (nranks <= 1) return;
+        const size_t cnt = rowsz * halo * sizeof(E_);
+        const int lo = f.o_lo, hi = f.o_hi;
+        OPTK_NCCL(ncclGroupStart());
+        for (int u = 0; u < nplanes; ++u) {
+            char* pl = (char*)(base + (size_t)u * pstride);
+            if (rank > 0) {
+                OPTK_NCCL(ncclSend(pl + (size_t)lo * rowsz * sizeof(E_), cnt, ncclChar, rank - 1, comm, stream));
+                OPTK_NCCL(ncclRecv(pl + (size_t)(lo - halo) * rowsz * sizeof(E_), cnt, ncclChar, rank - 1, comm, stream));
+            }
+            if (rank < nranks - 1) {
+                OPTK_NCCL(ncclSend(pl + (size_t)(hi - halo) * rowsz * sizeof(E_), cnt, ncclChar, rank + 1, comm, stream));
+                OPTK_NCCL(ncclRecv(pl + (size_t)hi * rowsz * sizeof(E_), cnt, ncclChar, rank + 1, comm, stream));
+            }
+        }
+        OPTK_NCCL(ncclGroupEnd());
+    }
+    size_t slow_rowsz() const { return F::ND == 3 ? (size_t)f.W * f.H : (size_t)f.W; }
+    void exchange(Vec<T> v) { exchange_raw(v.d, U, (size_t)v.plane, slow_rowsz()); }
+    void exchange_unknowns() {
+        if (nranks <= 1) return;
+        void* ptrs[8]; int ch[8];
+        const int n = f.unknown_images(ptrs, ch);
+        for (int i = 0; i < n; ++i) exchange_raw((T*)ptrs[i], 1, 0, slow_rowsz() * ch[i]);
+    }
 
     double read_scalar(int slot) {                          // blocking D2H (backend_cuda.t:353-355)
         OPTK_CUDA(cudaMemcpyAsync(h_scal, scal + slot, sizeof(double), cudaMemcpyDeviceToHost, stream));
@@ -535,12 +602,15 @@ struct Engine : OptK_Plan {
         OPTK_CUDA(cudaMemsetAsync(S(S_COST), 0, sizeof(double), stream));
         this->launch("computeCost", sgrid, dim3(sblock), k_cost<F>, f, S(S_COST));
         if (GRAPH) this->launch("computeCost_Graph", edge_grid(), dim3(256), k_graph_cost<F>, f, E, S(S_COST));
+        reduce(S_COST);
         return (double)(T)read_scalar(S_COST);
     }
     double model_cost() override {
+        exchange(delta);
         OPTK_CUDA(cudaMemsetAsync(S(S_MODEL), 0, sizeof(double), stream));
         this->launch("computeModelCost", sgrid, dim3(sblock), k_model_cost<F>, f, delta, S(S_MODEL));
         if (GRAPH) this->launch("computeModelCost_Graph", edge_grid(), dim3(256), k_graph_model_cost<F>, f, E, delta, S(S_MODEL));
+        reduce(S_MODEL);
         return (double)(T)read_scalar(S_MODEL);
     }
     double fetch_q() override { return (double)(T)read_scalar(S_Q); }
@@ -560,7 +630,10 @@ struct Engine : OptK_Plan {
             this->launch("PCGComputeCtC", sgrid, dim3(sblock), k_compute_ctc<F>, f, CtC, inv_radius);
             if (GRAPH) this->launch("PCGComputeCtC_Graph", edge_grid(), dim3(256), k_graph_ctc<F>, f, E, CtC, inv_radius);
             this->launch("PCGFinalizeDiagonal", sgrid, dim3(sblock), k_finalize_diagonal<F>, f, CtC, SSq, pre, r, b, p, delta, radius, min_diag, max_diag, S(S_RZ0), S(S_Q));
+            reduce(S_Q);
         }
+        reduce(S_RZ0);
+        exchange(p);                                        // Step1 reads p over the stencil
     }
 
     void apply_A(const char* name, const char* gname, Vec<T> dir, Vec<T> out, double* den, double* zero_slot) {
@@ -577,9 +650,11 @@ struct Engine : OptK_Plan {
         double* nextDen = S(S_ADEN0 + ((l + 1) & 1));
         // PCGStep1 also clears q for this iteration (solver:2090)
         apply_A("PCGStep1", "PCGStep1_Graph", p, Ap, aDen, lm ? S(S_Q) : nullptr);
+        reduce(int(aDen - scal));
         const long nv = flat_vecs();
         if (lm && reset) {
             this->launch("PCGStep2_1stHalf", flat_grid(), dim3(256), k_axpy_alpha<T>, nv, delta.d, p.d, aNum, aDen);
+            exchange(delta);
             apply_A("computeAdelta", "computeAdelta_Graph", delta, Adelta, S(S_DUMMY), nullptr);
             this->launch("PCGStep2_2ndHalf", flat_grid(), dim3(256), k_residual_reset<T, F::USE_PRE>, nv, delta.d, r.d, Adelta.d, pre.d, b.d, z.d, bNum, S(S_Q), nextDen);
         } else if (lm) {
@@ -587,15 +662,24 @@ struct Engine : OptK_Plan {
         } else {
             this->launch("PCGStep2", flat_grid(), dim3(256), k_pcg_step2<T, F::USE_PRE, false>, nv, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
         }
+        reduce(int(bNum - scal));
+        if (lm) reduce(S_Q);
         this->launch("PCGStep3", flat_grid(), dim3(256), k_pcg_step3<T>, nv, z.d, p.d, bNum, aNum, nextB);
+        exchange(p);
     }
     void pcg_run(int lIterations) override {
         for (int l = 0; l < lIterations; ++l) pcg_iter(l, 0);
     }
 
     void save_unknowns() override { this->launch("savePreviousUnknowns", sgrid, dim3(sblock), k_unknown_update<F, 1>, f, prevX); }
-    void linear_update() override { this->launch("PCGLinearUpdate", sgrid, dim3(sblock), k_unknown_update<F, 0>, f, delta); }
-    void revert_update() override { this->launch("revertUpdate", sgrid, dim3(sblock), k_unknown_update<F, 2>, f, prevX); }
+    void linear_update() override {
+        this->launch("PCGLinearUpdate", sgrid, dim3(sblock), k_unknown_update<F, 0>, f, delta);
+        exchange_unknowns();                                // neighbours read X over the stencil
+    }
+    void revert_update() override {
+        this->launch("revertUpdate", sgrid, dim3(sblock), k_unknown_update<F, 2>, f, prevX);
+        exchange_unknowns();
+    }
 
     Vec<T>* vec_by_name(const char* n) {
         struct { const char* n; Vec<T>* v; } tab[] = {{"delta", &delta}, {"r", &r}, {"p", &p}, {"Ap", &Ap}, {"z", &z},
@@ -632,6 +716,8 @@ struct FunctorDefaults {
     static constexpr bool HAS_PRECOMPUTE = false;
     static constexpr int GV = 0;
     int E = 0;
+    int o_lo = 0, o_hi = 0x7fffffff;                       // owned range along the slowest dimension (slab mode)
+    int unknown_images(void**, int*) const { return 0; }   // grid functors list their AoS unknown images (halo exchange)
     void alloc_temporaries(cudaStream_t) {}
     void free_temporaries() {}
     __device__ void precompute(int, int, int, long) const {}

@@ -23,6 +23,7 @@ struct ImageWarpingFunctor : FunctorDefaults<T> {
     }
     __device__ bool exclude(int, int, int, long s) const { return M[s] != T(0); }
     __device__ T* xptr(long s, int u) const { return u < 2 ? O + s * 2 + u : A + s; }
+    int unknown_images(void** ptrs, int* ch) const { ptrs[0] = O; ch[0] = 2; ptrs[1] = A; ch[1] = 1; return 2; }
 
     template <class Fn> __device__ __forceinline__ void neighbours(int x, int y, long s, Fn&& fn) const {
         const bool mi = M[s] == T(0);

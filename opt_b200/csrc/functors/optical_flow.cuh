@@ -23,6 +23,7 @@ struct OpticalFlowFunctor : FunctorDefaults<T> {
     }
     __device__ bool exclude(int, int, int, long) const { return false; }
     __device__ T* xptr(long s, int u) const { return X + s * 2 + u; }
+    int unknown_images(void** ptrs, int* ch) const { ptrs[0] = X; ch[0] = 2; return 1; }
 
     template <class Fn> __device__ __forceinline__ void neighbours(int x, int y, long s, Fn&& fn) const {
         if (x + 1 < W) fn(s + 1);

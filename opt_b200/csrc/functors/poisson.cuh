@@ -19,6 +19,7 @@ struct PoissonFunctor : FunctorDefaults<T> {
     void bind(void** pp) { X = (T*)pp[0]; Tm = (const T*)pp[1]; M = (const T*)pp[2]; }
     __device__ bool exclude(int, int, int, long s) const { return M[s] != T(0); }
     __device__ T* xptr(long s, int u) const { return X + s * 4 + u; }
+    int unknown_images(void** ptrs, int* ch) const { ptrs[0] = X; ch[0] = 4; return 1; }
 
     template <class Fn> __device__ __forceinline__ void neighbours(int x, int y, long s, Fn&& fn) const {
         if (x + 1 < W) fn(s + 1);

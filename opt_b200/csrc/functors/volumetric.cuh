@@ -24,6 +24,7 @@ struct VolumetricFunctor : FunctorDefaults<T> {
     }
     __device__ bool exclude(int, int, int, long) const { return false; }
     __device__ T* xptr(long s, int u) const { return u < 3 ? O + s * 3 + u : A + s * 3 + (u - 3); }
+    int unknown_images(void** ptrs, int* ch) const { ptrs[0] = O; ch[0] = 3; ptrs[1] = A; ch[1] = 3; return 2; }
 
     template <class Fn> __device__ __forceinline__ void neighbours(int x, int y, int z, long s, Fn&& fn) const {
         const long sy = W, sz = (long)W * H;

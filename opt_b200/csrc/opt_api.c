@@ -269,6 +269,10 @@ double Opt_ProblemCurrentCost(Opt_State* state, Opt_Plan* plan) { /* solver:2354
 }
 
 /* ---- OptB200.h extensions (no counterpart in the reference) -------------------------------- */
+void OptB200_GetNcclUniqueId(void* out128) { optk_nccl_unique_id(out128); }
+int OptB200_PlanSetSlab(Opt_Plan* plan, int rank, int nranks, int halo, const void* nccl_unique_id) {
+    return optk_set_slab(plan->k, rank, nranks, halo, nccl_unique_id);
+}
 long OptB200_PlanLaunchCount(Opt_Plan* plan) { return optk_launch_count(plan->k); }
 int OptB200_PlanKernelTime(Opt_Plan* plan, const char* kernel, double* total_ms) {
     return optk_kernel_time(plan->k, kernel, total_ms);

@@ -38,6 +38,12 @@ void   optk_save_unknowns(OptK_Plan*);        /* savePreviousUnknowns (solver:88
 void   optk_linear_update(OptK_Plan*);        /* PCGLinearUpdate (solver:854-859) */
 void   optk_revert_update(OptK_Plan*);        /* revertUpdate (solver:864-869) */
 
+/* Multi-GPU slab mode (one process per GPU).  The plan's dimensions are the LOCAL slab including
+ * `halo` ghost rows/planes on every interior side of the slowest dimension; `nccl_unique_id` is the
+ * 128-byte ncclUniqueId every rank received from rank 0.  Collective: every rank must call it. */
+int    optk_set_slab(OptK_Plan*, int rank, int nranks, int halo, const void* nccl_unique_id);
+void   optk_nccl_unique_id(void* out128);
+
 /* statistics and debugging */
 long   optk_launch_count(OptK_Plan*);         /* kernels launched since creation */
 void   optk_print_timing(OptK_Plan*);         /* Kernel | Count | Total | Average table (backend_cuda.t:152-297) */

@@ -57,6 +57,13 @@ double optk_model_cost(OptK_Plan* p) { return p->model_cost(); }
 void optk_save_unknowns(OptK_Plan* p) { p->save_unknowns(); }
 void optk_linear_update(OptK_Plan* p) { p->linear_update(); }
 void optk_revert_update(OptK_Plan* p) { p->revert_update(); }
+int optk_set_slab(OptK_Plan* p, int rank, int nranks, int halo, const void* uid) { return p->set_slab(rank, nranks, halo, uid); }
+void optk_nccl_unique_id(void* out128) {
+    ncclUniqueId id;
+    OPTK_NCCL(ncclGetUniqueId(&id));
+    static_assert(sizeof(id) == 128, "ncclUniqueId is 128 bytes");
+    memcpy(out128, &id, sizeof(id));
+}
 long optk_launch_count(OptK_Plan* p) { return p->launches; }
 void optk_print_timing(OptK_Plan* p) { p->print_timing(); }
 int optk_kernel_time(OptK_Plan* p, const char* k, double* ms) { return p->kernel_time(k, ms); }

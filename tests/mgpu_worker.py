@@ -1,0 +1,74 @@
+"""Worker for tests/test_multigpu.py (launched by torch.distributed.run, one rank per GPU): solves a
+grid problem slab-decomposed over all ranks and checks per-step costs and unknowns against the
+single-GPU solve of the undecomposed problem computed on rank 0."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from opt_b200 import examples, slab, solver as S  # noqa: E402
+
+CASES = {
+    "poisson": (lambda: examples.poisson_synthetic(64, 96, n_iter=2, l_iter=15), 1e-5),
+    "image_warping": (lambda: examples.image_warping_synthetic(48, 64, n_iter=3, l_iter=10), 1e-4),
+    "optical_flow_lm": (lambda: examples.optical_flow_synthetic(40, 60, n_iter=3, l_iter=12, kind="LMGPU"), 1e-4),
+    "volumetric": (lambda: examples.volumetric_synthetic(12, 10, 16, n_iter=2, l_iter=10), 1e-5),
+    "volumetric_lm_f64": (lambda: examples.volumetric_synthetic(8, 6, 12, n_iter=3, l_iter=12).as_double(), 1e-9),
+}
+
+
+def solve(pr, rank=0, world=1, halo=1):
+    named = S.upload(pr)
+    sol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=pr.double)
+    if world > 1:
+        slab.setup_slab(sol, rank, world, halo)
+    costs = []
+    sol.solve(pr.solver, named, costs)
+    torch.cuda.synchronize()
+    xs = [named.values[i].cpu().numpy() for i in pr.unknowns]
+    sol.close()
+    return costs, xs
+
+
+def main():
+    dist.init_process_group("nccl")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    failures = []
+    for name, (build, tol) in CASES.items():
+        pr = build()
+        if "lm" in name:
+            pr.kind = "LMGPU"
+        L = pr.dims[-1]
+        loc = slab.split_problem(pr, rank, world, 1)
+        costs, xs = solve(loc, rank, world)
+        owned = [slab.owned_rows(x, loc.dims[-1], rank, world, 1) for x in xs]
+        gathered = []
+        for o in owned:
+            lst = [None] * world
+            dist.all_gather_object(lst, o)
+            gathered.append(np.concatenate(lst, 0))
+        if rank == 0:
+            ref_costs, ref_xs = solve(pr)
+            ok = len(costs) == len(ref_costs) and all(abs(a - b) <= tol * abs(b) for a, b in zip(costs, ref_costs))
+            for g, rx in zip(gathered, ref_xs):
+                ref = rx.reshape(L, -1)
+                scale = np.abs(ref[np.isfinite(ref)]).max()
+                ok = ok and np.abs(g - ref).max() <= 10 * tol * scale
+            print("mgpu %-18s world=%d %s costs=%s ref=%s" % (name, world, "OK" if ok else "MISMATCH", costs, ref_costs), flush=True)
+            if not ok:
+                failures.append(name)
+        dist.barrier()
+    dist.destroy_process_group()
+    if failures:
+        sys.exit(1)
+
+
+if __name__ == "__main__":
+    main()
