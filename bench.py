@@ -101,10 +101,28 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def make_problem(name, size=None):
+SLAB = {   # workloads that run domain-decomposed at N > 1 (the others run as independent replicas)
+    "poisson_4096": "weak",       # N stacked 4096-row images: per-GPU work fixed
+    "volumetric_512": "strong",   # the 512^3 grid cut into N slabs of planes
+    "volumetric_256": "strong",
+}
+
+
+def make_problem(name, size=None, rank=0, world=1):
+    """Returns (local problem of this rank, workload record, slab mode or None)."""
+    from opt_b200 import slab
     w = WORKLOADS[name]
     args = tuple(size) if size else w["args"]
-    return w["builder"](*args, **w["kw"]), w
+    mode = SLAB.get(name) if world > 1 else None
+    if mode == "weak":
+        W, H = args
+        g0, g1, _, _ = slab.local_range(H * world, rank, world, 1)
+        return w["builder"](W, H * world, rows=(g0, g1), period=H, **w["kw"]), w, mode
+    if mode == "strong":
+        W, H, D = args
+        g0, g1, _, _ = slab.local_range(D, rank, world, 1)
+        return w["builder"](W, H, D, planes=(g0, g1), **w["kw"]), w, mode
+    return w["builder"](*args, **w["kw"]), w, None
 
 
 def pcg_iterations(pr):
@@ -172,7 +190,7 @@ def run_reference(args, pr, w):
 
 
 # ------------------------------------------------------------------------------ GPU arm
-def run_ours(args, pr, w, rank, world):
+def run_ours(args, pr, w, rank, world, mode):
     import torch
     import torch.distributed as dist
     from opt_b200 import solver as S
@@ -186,7 +204,10 @@ def run_ours(args, pr, w, rank, world):
     named = S.NamedParameters()
     for i, p in enumerate(pr.params):
         named.set("p%d" % i, devt[i] if i in devt else p)
+    from opt_b200 import slab
     sol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=pr.double, verbosity=0, timing=False)
+    if mode:
+        slab.setup_slab(sol, rank, world, 1)
     sol.set_solver_parameters(pr.solver)
     iters = pcg_iterations(pr)
 
@@ -246,8 +267,10 @@ def run_ours(args, pr, w, rank, world):
 
     # per-kernel time of the dominant kernel, measured live with the library's cudaEvent timer
     roof = None
-    if rank == 0:
+    if rank == 0 or mode:
         tsol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=pr.double, verbosity=0, timing=True)
+        if mode:
+            slab.setup_slab(tsol, rank, world, 1)
         tsol.set_solver_parameters(pr.solver)
         for rep in range(2):
             for i in pr.unknowns:
@@ -274,8 +297,10 @@ def run_ours(args, pr, w, rank, world):
                                   "frac": w["bytes_iter"] * N * (iters * args.steps / (ms * 1e-3)) / 1e9 / peak}}
         tsol.close()
 
-    total_iters = iters * args.steps * world          # weak scaling: every rank solves its own slab/replica
-    value = total_iters / (ms * 1e-3) / (world if args.scaling_mode == "slab" else 1)
+    # units: one PCG iteration over one single-GPU-sized grid.  weak slab / replicas: N such units per
+    # global iteration; strong slab: the global grid IS the single-GPU grid.
+    mult = 1 if mode == "strong" else world
+    value = mult * iters * args.steps / (ms * 1e-3)
     if rank != 0:
         return
     cpu = None
@@ -286,12 +311,15 @@ def run_ours(args, pr, w, rank, world):
     line = {
         "metric": "pcg_iterations_per_second", "value": value, "unit": "PCG iters/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32" if not pr.double else "f64", "data": "synthetic",
+        "scaling": "strong" if mode == "strong" else "weak", "vs_baseline": None,
+        "dtype": "f32" if not pr.double else "f64", "data": "synthetic",
         "config": {"workload": w["desc"], "dims": pr.dims, "pcg_iterations_per_step": iters,
                    "l2": "inputs larger than L2 (each solver vector is %.0f MB)" % (w["U"] * sol.site_count() * 4 / 1e6),
-                   "final_cost": cost, "parallelism": "1 GPU" if world == 1 else "%d ranks" % world},
+                   "final_cost": cost, "parallelism": "1 GPU" if world == 1 else ("%d ranks, %s" % (world, (
+                       "slab decomposition along the slowest dim (%s scaling), NCCL halo exchange + all-reduced PCG scalars" % mode)
+                       if mode else "independent replicas"))},
         "clocks": clocks,
-        "e2e": {"value": iters * e2e_steps * (world if args.scaling_mode != "slab" else 1) / (ms_e2e * 1e-3),
+        "e2e": {"value": mult * iters * e2e_steps / (ms_e2e * 1e-3),
                 "unit": "PCG iters/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / e2e_steps, "final_cost": cost_e2e},
         "gpu_launches": launches,
@@ -311,19 +339,21 @@ def main():
     ap.add_argument("--size", type=int, nargs="+", default=None, help="override the workload's grid size")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
-    ap.add_argument("--scaling-mode", default="replica", choices=["replica", "slab"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
-    pr, w = make_problem(args.workload, args.size)
     if args.impl == "reference":
         if rank == 0:
+            pr, w, _ = make_problem(args.workload, args.size)
             run_reference(args, pr, w)
         return
+    pr, w, mode = make_problem(args.workload, args.size, rank, world)
     if world > 1:
+        import torch
         import torch.distributed as dist
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
         dist.init_process_group("nccl")
-    run_ours(args, pr, w, rank, world)
+    run_ours(args, pr, w, rank, world, mode)
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()

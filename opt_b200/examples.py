@@ -107,20 +107,29 @@ def volumetric_golden(npz):
 
 # ---------------------------------------------------------------------------------------------
 # synthetic inputs of the BASELINE.json shapes, seed 1234
-def poisson_synthetic(W, H, seed=1234, n_iter=1, l_iter=100):
+def poisson_synthetic(W, H, seed=1234, n_iter=1, l_iter=100, rows=None, period=None):
     """X,T in U[0,255] (4 channels, w = 255), mask = 0 (unknown) inside a centred rectangle covering
     50 % of the area, 255 elsewhere (examples/poisson_image_editing/src/CombinedSolver.h:79-82,
-    main.cpp:102-106)."""
-    rng = np.random.default_rng(seed)
-    X = rng.uniform(0, 255, (H, W, 4)).astype(np.float32)
-    T = rng.uniform(0, 255, (H, W, 4)).astype(np.float32)
+    main.cpp:102-106).  Every global row y has its own RNG stream, so `rows=(y0,y1)` builds just
+    that band of the H-row image (multi-GPU slabs incl. ghost rows); with `period` the mask
+    rectangle repeats every `period` rows (weak scaling: one rectangle per rank)."""
+    y0, y1 = rows if rows else (0, H)
+    period = period or H
+    X = np.empty((y1 - y0, W, 4), dtype=np.float32)
+    T = np.empty((y1 - y0, W, 4), dtype=np.float32)
+    for y in range(y0, y1):
+        rng = np.random.default_rng([seed, y])
+        X[y - y0] = rng.uniform(0, 255, (W, 4))
+        T[y - y0] = rng.uniform(0, 255, (W, 4))
     X[..., 3] = 255
     T[..., 3] = 255
-    M = np.full((H, W), 255, dtype=np.float32)
-    rw, rh = int(round(W * np.sqrt(0.5))), int(round(H * np.sqrt(0.5)))
-    x0, y0 = (W - rw) // 2, (H - rh) // 2
-    M[y0:y0 + rh, x0:x0 + rw] = 0
-    return Problem("poisson_image_editing.t", [W, H], [X, T, M], [0],
+    rw, rh = int(round(W * np.sqrt(0.5))), int(round(period * np.sqrt(0.5)))
+    x0, r0 = (W - rw) // 2, (period - rh) // 2
+    yy = np.arange(y0, y1) % period
+    inside_y = (yy >= r0) & (yy < r0 + rh)
+    M = np.full((y1 - y0, W), 255, dtype=np.float32)
+    M[np.ix_(inside_y, np.arange(x0, x0 + rw))] = 0
+    return Problem("poisson_image_editing.t", [W, y1 - y0], [X, T, M], [0],
                    {"nIterations": n_iter, "lIterations": l_iter})
 
 
@@ -144,25 +153,31 @@ def image_warping_synthetic(W, H, seed=1234, n_iter=2, l_iter=10, noise=0.3, w_f
     return pr
 
 
-def volumetric_synthetic(W, H, D, seed=1234, n_iter=2, l_iter=10):
+def volumetric_synthetic(W, H, D, seed=1234, n_iter=2, l_iter=10, planes=None):
     """dims {W,H,D}; lattice in the unit-aspect box; plane d1==0 fixed, plane d1==H-1 rotated -90 deg
-    about z and shifted.  Angles get small random values in the test
-    variant so that the rotation derivatives are exercised."""
-    rng = np.random.default_rng(seed)
+    about z and shifted.  Offsets/angles get small random values so that
+    the rotation derivatives are exercised.  Every global d2-plane has its own RNG stream, so
+    `planes=(z0,z1)` builds just that slab of the D-plane volume."""
     f32 = np.float32
-    kk, jj, ii = np.meshgrid(np.arange(D), np.arange(H), np.arange(W), indexing="ij")   # d0 fastest
+    z0, z1 = planes if planes else (0, D)
+    nz = z1 - z0
+    kk, jj, ii = np.meshgrid(np.arange(z0, z1), np.arange(H), np.arange(W), indexing="ij")   # d0 fastest
     pos = np.stack([ii, jj, kk], -1).astype(f32) / f32(max(W, H, D) - 1)
     target = np.full(pos.shape, -np.inf, dtype=f32)
     target[:, 0] = pos[:, 0]
     R = np.array([[0, 1, 0], [-1, 0, 0], [0, 0, 1]], dtype=f32)
     mid = np.array([0.5 * (W - 1), H - 1, 0.5 * (D - 1)], dtype=f32) / f32(max(W, H, D) - 1)
     target[:, H - 1] = ((pos[:, H - 1] - mid) @ R.T + mid + np.array([0.25, -0.25, 0], dtype=f32)).astype(f32)
-    n = W * H * D
-    offset = (pos.reshape(n, 3) + 0.01 * rng.standard_normal((n, 3))).astype(f32)
-    angle = (0.05 * rng.standard_normal((n, 3))).astype(f32)
+    offset = np.empty((nz, H, W, 3), dtype=f32)
+    angle = np.empty((nz, H, W, 3), dtype=f32)
+    for z in range(z0, z1):
+        rng = np.random.default_rng([seed, z])
+        offset[z - z0] = pos[z - z0] + 0.01 * rng.standard_normal((H, W, 3), dtype=f32)
+        angle[z - z0] = 0.05 * rng.standard_normal((H, W, 3), dtype=f32)
+    n = W * H * nz
     w_fit, w_reg = np.sqrt(f32(1.0)), np.sqrt(f32(0.05))
-    return Problem("volumetric_mesh_deformation.t", [W, H, D],
-                   [offset, angle, pos.reshape(n, 3).copy(), target.reshape(n, 3), w_fit, w_reg], [0, 1],
+    return Problem("volumetric_mesh_deformation.t", [W, H, nz],
+                   [offset.reshape(n, 3), angle.reshape(n, 3), pos.reshape(n, 3).copy(), target.reshape(n, 3), w_fit, w_reg], [0, 1],
                    {"nIterations": n_iter, "lIterations": l_iter})
 
 
