@@ -10,6 +10,7 @@
 //   * reductions are block-level (warp shuffle -> smem -> one double atomicAdd per block) into
 //     device-resident double scalars that the next kernel reads (no host sync in the GN loop).
 #pragma once
+#include <algorithm>
 #include <map>
 #include <string>
 #include <vector>
@@ -184,6 +185,45 @@ __global__ void k_pcg_init1(F f, Vec<typename F::Scalar> delta, Vec<typename F::
         for (int u = 0; u < U; ++u) pre(u, s) = d[u];
     }
     if (F::GV == 0) block_accumulate(acc, aNum);
+}
+
+// Fused PCGStep3 + PCGStep1 (solver:814-845 + 607-632): the new search direction p' = z + beta p is
+// formed on the fly wherever the stencil reads it, written once at the thread's own site into the
+// OTHER p buffer (ping-pong: neighbours still read the old p), and Ap' = J^T J p' is produced in the
+// same pass.  Saves one read of p and one kernel per PCG iteration.
+template <class T>
+struct FusedDir {
+    Vec<T> z, p;
+    T beta;
+    __device__ __forceinline__ T operator()(int u, long s) const { return z(u, s) + beta * p(u, s); }
+};
+template <class F, bool LM>
+__global__ void k_apply_jtj_fused(F f, Vec<typename F::Scalar> z, Vec<typename F::Scalar> p_old,
+                                  Vec<typename F::Scalar> p_new, Vec<typename F::Scalar> out,
+                                  Vec<typename F::Scalar> CtC, const double* bNum, const double* aNum,
+                                  double* den, double* zero_a, double* zero_b) {
+    using T = typename F::Scalar;
+    constexpr int U = F::U;
+    int x, y, zc; long s;
+    double acc = 0.0;
+    FusedDir<T> dir{z, p_old, (T)(*bNum) / (T)(*aNum)};
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && linear_tid() == 0) {
+        if (zero_a) *zero_a = 0.0;
+        if (zero_b) *zero_b = 0.0;
+    }
+    if (thread_site(f, x, y, zc, s) && !f.exclude(x, y, zc, s)) {
+        T o[U];
+        f.applyJTJ(x, y, zc, s, dir, o);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            T pv = dir(u, s);
+            p_new(u, s) = pv;
+            if (LM) o[u] += CtC(u, s) * pv;
+            out(u, s) = o[u];
+            acc += (double)(pv * o[u]);
+        }
+    }
+    block_accumulate(acc, den);
 }
 
 // PCGStep1 / computeAdelta (solver:607-632, 873-878): out = (J^T J [+ CtC]) dir over non-excluded sites
@@ -366,8 +406,34 @@ __global__ void k_graph_ctc(F f, long E, Vec<typename F::Scalar> CtC, typename F
 // ------------------------------------------------------------------------------ flat streaming kernels
 // PCGStep2 (solver:665-731): alpha = aNum/aDen; delta += alpha p; r -= alpha Ap; z = M^-1 r;
 // betaNum += z.r ; LM: q += 0.5 delta.(r+b).   One 128-bit vector per thread and array.
+// Exclusion-aware streaming: `active4[g]` is nonzero iff any of the sites 4g..4g+3 is an unknown
+// (not excluded).  Groups without unknowns hold zeros in every solver vector and are skipped, so a
+// masked-out half of an image costs no HBM traffic (N/4 bytes of flags per plane pass instead).
+template <class T>
+__device__ __forceinline__ bool group_active(const unsigned char* active4, long i, long plane) {
+    if (!active4) return true;
+    const long e = (i * VecIO<T>::W) % plane;
+    return active4[e >> 2] != 0;
+}
+template <class F>
+__global__ void k_active4(F f, long ngroups, unsigned char* active4) {
+    const long g = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (g >= ngroups) return;
+    const long N = (long)f.W * f.H * f.D;
+    unsigned char a = 0;
+    for (int j = 0; j < 4; ++j) {
+        const long s = g * 4 + j;
+        if (s < N) {
+            const int x = (int)(s % f.W), y = (int)((s / f.W) % f.H), z = (int)(s / ((long)f.W * f.H));
+            if (!f.exclude(x, y, z, s)) a = 1;
+        }
+    }
+    active4[g] = a;
+}
+
 template <class T, bool USE_PRE, bool LM>
-__global__ void __launch_bounds__(256) k_pcg_step2(long nvec, T* __restrict__ delta, const T* __restrict__ p,
+__global__ void __launch_bounds__(256) k_pcg_step2(long nvec, const unsigned char* __restrict__ active4, long plane,
+                                                   T* __restrict__ delta, const T* __restrict__ p,
                                                    T* __restrict__ r, const T* __restrict__ Ap,
                                                    const T* __restrict__ pre, const T* __restrict__ b,
                                                    T* __restrict__ z, const double* aNum, const double* aDen,
@@ -378,7 +444,7 @@ __global__ void __launch_bounds__(256) k_pcg_step2(long nvec, T* __restrict__ de
     const T alpha = (T)(*aNum) / (T)(*aDen);
     if (i == 0 && zero_slot) *zero_slot = 0.0;
     double bacc = 0.0, qacc = 0.0;
-    if (i < nvec) {
+    if (i < nvec && group_active<T>(active4, i, plane)) {
         V d = reinterpret_cast<const V*>(delta)[i];
         V pv = reinterpret_cast<const V*>(p)[i];
         V rv = reinterpret_cast<const V*>(r)[i];
@@ -410,14 +476,15 @@ __global__ void __launch_bounds__(256) k_pcg_step2(long nvec, T* __restrict__ de
 
 // PCGStep3 (solver:814-845): beta = bNum/aNum; p = z + beta p
 template <class T>
-__global__ void __launch_bounds__(256) k_pcg_step3(long nvec, const T* __restrict__ z, T* __restrict__ p,
+__global__ void __launch_bounds__(256) k_pcg_step3(long nvec, const unsigned char* __restrict__ active4, long plane,
+                                                   const T* __restrict__ z, T* __restrict__ p,
                                                    const double* bNum, const double* aNum, double* zero_slot) {
     using V = typename VecIO<T>::V;
     constexpr int VW = VecIO<T>::W;
     const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
     const T beta = (T)(*bNum) / (T)(*aNum);
     if (i == 0 && zero_slot) *zero_slot = 0.0;
-    if (i < nvec) {
+    if (i < nvec && group_active<T>(active4, i, plane)) {
         V zv = reinterpret_cast<const V*>(z)[i];
         V pv = reinterpret_cast<const V*>(p)[i];
 #pragma unroll
@@ -428,13 +495,14 @@ __global__ void __launch_bounds__(256) k_pcg_step3(long nvec, const T* __restric
 
 // PCGStep2_1stHalf (solver:738-762): delta += alpha p
 template <class T>
-__global__ void __launch_bounds__(256) k_axpy_alpha(long nvec, T* __restrict__ delta, const T* __restrict__ p,
+__global__ void __launch_bounds__(256) k_axpy_alpha(long nvec, const unsigned char* __restrict__ active4, long plane,
+                                                    T* __restrict__ delta, const T* __restrict__ p,
                                                     const double* aNum, const double* aDen) {
     using V = typename VecIO<T>::V;
     constexpr int VW = VecIO<T>::W;
     const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
     const T alpha = (T)(*aNum) / (T)(*aDen);
-    if (i < nvec) {
+    if (i < nvec && group_active<T>(active4, i, plane)) {
         V d = reinterpret_cast<const V*>(delta)[i];
         V pv = reinterpret_cast<const V*>(p)[i];
 #pragma unroll
@@ -445,7 +513,8 @@ __global__ void __launch_bounds__(256) k_axpy_alpha(long nvec, T* __restrict__ d
 
 // PCGStep2_2ndHalf (solver:766-799): r = b - A delta; z = M^-1 r; betaNum += z.r; q += 0.5 delta.(r+b)
 template <class T, bool USE_PRE>
-__global__ void __launch_bounds__(256) k_residual_reset(long nvec, const T* __restrict__ delta, T* __restrict__ r,
+__global__ void __launch_bounds__(256) k_residual_reset(long nvec, const unsigned char* __restrict__ active4, long plane,
+                                                        const T* __restrict__ delta, T* __restrict__ r,
                                                         const T* __restrict__ Adelta, const T* __restrict__ pre,
                                                         const T* __restrict__ b, T* __restrict__ z,
                                                         double* bNum, double* q, double* zero_slot) {
@@ -454,7 +523,7 @@ __global__ void __launch_bounds__(256) k_residual_reset(long nvec, const T* __re
     const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
     if (i == 0 && zero_slot) *zero_slot = 0.0;
     double bacc = 0.0, qacc = 0.0;
-    if (i < nvec) {
+    if (i < nvec && group_active<T>(active4, i, plane)) {
         V d = reinterpret_cast<const V*>(delta)[i];
         V av = reinterpret_cast<const V*>(Adelta)[i];
         V bv = reinterpret_cast<const V*>(b)[i];
@@ -491,6 +560,9 @@ struct Engine : OptK_Plan {
     long N, Npad, E;
     T* pool = nullptr;
     Vec<T> delta, r, b, Adelta, z, p, Ap, CtC, pre, SSq, prevX;
+    Vec<T> p_alt;                                           // second p buffer of the fused Step3+Step1 kernel
+    unsigned char* active4 = nullptr;                       // 1 flag per 4 sites (HAS_EXCLUDE functors only)
+    bool fuse = true;                                       // fused PCGStep3+PCGStep1 (single rank)
     double* scal = nullptr;
     double* h_scal = nullptr;    // pinned
     T radius = 0, min_diag = 0, max_diag = 0;
@@ -505,16 +577,21 @@ struct Engine : OptK_Plan {
         N = (long)f.W * f.H * f.D;
         E = GRAPH ? (long)f.E : 0;
         Npad = round_up(N, 64);
-        const int nvec = lm ? 11 : 7;
+        const int nvec = lm ? 12 : 8;
         size_t bytes = (size_t)nvec * U * Npad * sizeof(T);
         OPTK_CUDA(cudaMalloc(&pool, bytes));
         OPTK_CUDA(cudaMemsetAsync(pool, 0, bytes, stream));
-        Vec<T>* vs[11] = {&delta, &r, &z, &p, &Ap, &pre, &prevX, &b, &Adelta, &CtC, &SSq};
-        for (int i = 0; i < 11; ++i) {
+        Vec<T>* vs[12] = {&delta, &r, &z, &p, &Ap, &pre, &prevX, &p_alt, &b, &Adelta, &CtC, &SSq};
+        for (int i = 0; i < 12; ++i) {
             vs[i]->plane = Npad;
             vs[i]->d = i < nvec ? pool + (size_t)i * U * Npad : nullptr;
         }
         if (!F::USE_PRE) z = r;                             // M^-1 = 1: z aliases r (solver:705-711)
+        if (F::HAS_EXCLUDE) {
+            OPTK_CUDA(cudaMalloc(&active4, Npad / 4));
+            OPTK_CUDA(cudaMemsetAsync(active4, 0, Npad / 4, stream));
+        }
+        if (getenv("OPTB200_NO_FUSE")) fuse = false;
         OPTK_CUDA(cudaMalloc(&scal, S_COUNT * sizeof(double)));
         OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
         OPTK_CUDA(cudaMallocHost(&h_scal, S_COUNT * sizeof(double)));
@@ -529,7 +606,7 @@ struct Engine : OptK_Plan {
         cudaStreamSynchronize(stream);
         f.free_temporaries();
         if (comm) ncclCommDestroy(comm);
-        cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal);
+        cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFree(active4);
         base_destroy();
     }
     int unknown_channels() const override { return U; }
@@ -547,6 +624,7 @@ struct Engine : OptK_Plan {
         if (F::ND < 2 || GRAPH) { fprintf(stderr, "Opt: slab decomposition is only available for 2-D/3-D grid problems\n"); return -1; }
         const int L = F::ND == 3 ? f.D : f.H;
         rank = rk; nranks = nr; halo = h;
+        if (nranks > 1) fuse = false;                       // ghost rows of p are refreshed after PCGStep3
         f.o_lo = rank > 0 ? halo : 0;
         f.o_hi = rank < nranks - 1 ? L - halo : L;
         if (f.o_hi - f.o_lo < halo) { fprintf(stderr, "Opt: slab thinner than its halo\n"); return -1; }
@@ -617,6 +695,8 @@ struct Engine : OptK_Plan {
 
     void pcg_begin(int nIter) override {
         OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
+        if (F::HAS_EXCLUDE)                                 // Exclude() may read inputs the caller changed
+            this->launch("activeGroups", dim3((unsigned)((Npad / 4 + 255) / 256)), dim3(256), k_active4<F>, f, Npad / 4, active4);
         this->launch("PCGInit1", sgrid, dim3(sblock), k_pcg_init1<F>, f, delta, r, p, pre, S(S_RZ0));
         if (GRAPH) {
             this->launch("PCGInit1_Graph", edge_grid(), dim3(256), k_graph_jtf<F>, f, E, r, pre);
@@ -637,6 +717,13 @@ struct Engine : OptK_Plan {
     }
 
     void apply_A(const char* name, const char* gname, Vec<T> dir, Vec<T> out, double* den, double* zero_slot) {
+        if constexpr (F::HAS_FAST_APPLY) {
+            if (f.fast_ok()) {
+                if (lm) this->launch(name, f.fast_grid(), f.fast_block(), F::template fast_kernel<false, true>(), f, dir, dir, dir, out, CtC, (const unsigned char*)active4, (const double*)nullptr, (const double*)nullptr, den, zero_slot, (double*)nullptr);
+                else    this->launch(name, f.fast_grid(), f.fast_block(), F::template fast_kernel<false, false>(), f, dir, dir, dir, out, CtC, (const unsigned char*)active4, (const double*)nullptr, (const double*)nullptr, den, zero_slot, (double*)nullptr);
+                return;
+            }
+        }
         if (lm) this->launch(name, sgrid, dim3(sblock), k_apply_jtj<F, true>, f, dir, out, CtC, den, zero_slot);
         else    this->launch(name, sgrid, dim3(sblock), k_apply_jtj<F, false>, f, dir, out, CtC, den, zero_slot);
         if (GRAPH) this->launch(gname, edge_grid(), dim3(256), k_graph_jtj<F>, f, E, dir, out, den);
@@ -648,24 +735,47 @@ struct Engine : OptK_Plan {
         double* nextB = S(S_RZ0 + (l + 2) % 3);
         double* aDen = S(S_ADEN0 + (l & 1));
         double* nextDen = S(S_ADEN0 + ((l + 1) & 1));
-        // PCGStep1 also clears q for this iteration (solver:2090)
-        apply_A("PCGStep1", "PCGStep1_Graph", p, Ap, aDen, lm ? S(S_Q) : nullptr);
-        reduce(int(aDen - scal));
         const long nv = flat_vecs();
+        const unsigned char* act = active4;
+        // PCGStep1 also clears q for this iteration (solver:2090)
+        if (fuse && l > 0) {
+            // p' = z + beta p with beta = RZ[l%3] / RZ[(l-1)%3] (the PCGStep3 of iteration l-1), then Ap'
+            double* prevA = S(S_RZ0 + (l + 2) % 3);
+            if constexpr (F::HAS_FAST_APPLY) {
+                if (f.fast_ok()) {
+                    if (lm) this->launch("PCGStep3+1", f.fast_grid(), f.fast_block(), F::template fast_kernel<true, true>(), f, z, p, p_alt, Ap, CtC, (const unsigned char*)active4, (const double*)aNum, (const double*)prevA, aDen, bNum, S(S_Q));
+                    else    this->launch("PCGStep3+1", f.fast_grid(), f.fast_block(), F::template fast_kernel<true, false>(), f, z, p, p_alt, Ap, CtC, (const unsigned char*)active4, (const double*)aNum, (const double*)prevA, aDen, bNum, (double*)nullptr);
+                    std::swap(p.d, p_alt.d);
+                    goto applied;
+                }
+            }
+            if (lm) this->launch("PCGStep3+1", sgrid, dim3(sblock), k_apply_jtj_fused<F, true>, f, z, p, p_alt, Ap, CtC, aNum, prevA, aDen, bNum, S(S_Q));
+            else    this->launch("PCGStep3+1", sgrid, dim3(sblock), k_apply_jtj_fused<F, false>, f, z, p, p_alt, Ap, CtC, aNum, prevA, aDen, bNum, (double*)nullptr);
+            std::swap(p.d, p_alt.d);
+            if (GRAPH) this->launch("PCGStep1_Graph", edge_grid(), dim3(256), k_graph_jtj<F>, f, E, p, Ap, aDen);
+        } else {
+            apply_A("PCGStep1", "PCGStep1_Graph", p, Ap, aDen, lm ? S(S_Q) : nullptr);
+        }
+    applied:
+        reduce(int(aDen - scal));
         if (lm && reset) {
-            this->launch("PCGStep2_1stHalf", flat_grid(), dim3(256), k_axpy_alpha<T>, nv, delta.d, p.d, aNum, aDen);
+            this->launch("PCGStep2_1stHalf", flat_grid(), dim3(256), k_axpy_alpha<T>, nv, act, Npad, delta.d, p.d, aNum, aDen);
             exchange(delta);
             apply_A("computeAdelta", "computeAdelta_Graph", delta, Adelta, S(S_DUMMY), nullptr);
-            this->launch("PCGStep2_2ndHalf", flat_grid(), dim3(256), k_residual_reset<T, F::USE_PRE>, nv, delta.d, r.d, Adelta.d, pre.d, b.d, z.d, bNum, S(S_Q), nextDen);
+            this->launch("PCGStep2_2ndHalf", flat_grid(), dim3(256), k_residual_reset<T, F::USE_PRE>, nv, act, Npad, delta.d, r.d, Adelta.d, pre.d, b.d, z.d, bNum, S(S_Q), nextDen);
         } else if (lm) {
-            this->launch("PCGStep2", flat_grid(), dim3(256), k_pcg_step2<T, F::USE_PRE, true>, nv, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
+            this->launch("PCGStep2", flat_grid(), dim3(256), k_pcg_step2<T, F::USE_PRE, true>, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
         } else {
-            this->launch("PCGStep2", flat_grid(), dim3(256), k_pcg_step2<T, F::USE_PRE, false>, nv, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
+            this->launch("PCGStep2", flat_grid(), dim3(256), k_pcg_step2<T, F::USE_PRE, false>, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
         }
         reduce(int(bNum - scal));
         if (lm) reduce(S_Q);
-        this->launch("PCGStep3", flat_grid(), dim3(256), k_pcg_step3<T>, nv, z.d, p.d, bNum, aNum, nextB);
-        exchange(p);
+        if (!fuse) {
+            this->launch("PCGStep3", flat_grid(), dim3(256), k_pcg_step3<T>, nv, act, Npad, z.d, p.d, bNum, aNum, nextB);
+            exchange(p);
+        }
+        // fused mode: PCGStep3 of this iteration happens inside the next iteration's first kernel; after
+        // the last iteration its result (the next search direction) is never used (solver:2203-2227)
     }
     void pcg_run(int lIterations) override {
         for (int l = 0; l < lIterations; ++l) pcg_iter(l, 0);
@@ -704,6 +814,8 @@ struct Engine : OptK_Plan {
         OPTK_CUDA(cudaMemcpy(p.d, tmp.data(), tmp.size() * sizeof(T), cudaMemcpyHostToDevice));
         OPTK_CUDA(cudaMemsetAsync(Ap.d, 0, tmp.size() * sizeof(T), stream));
         bool saved = lm; lm = false;
+        if (F::HAS_EXCLUDE)
+            this->launch("activeGroups", dim3((unsigned)((Npad / 4 + 255) / 256)), dim3(256), k_active4<F>, f, Npad / 4, active4);
         apply_A("PCGStep1", "PCGStep1_Graph", p, Ap, S(S_DUMMY), nullptr);
         lm = saved;
         debug_read("Ap", host_out);
@@ -714,6 +826,9 @@ struct Engine : OptK_Plan {
 template <class T>
 struct FunctorDefaults {
     static constexpr bool HAS_PRECOMPUTE = false;
+    static constexpr bool HAS_EXCLUDE = false;           // functors with an Exclude() override this
+    static constexpr bool HAS_FAST_APPLY = false;        // functors with a specialised J^T J kernel override this
+    bool fast_ok() const { return false; }
     static constexpr int GV = 0;
     int E = 0;
     int o_lo = 0, o_hi = 0x7fffffff;                       // owned range along the slowest dimension (slab mode)

@@ -43,7 +43,7 @@ struct ArapFunctor : FunctorDefaults<T> {
             for (int k = 0; k < 3; ++k) { g[k] += wf2 * (O[s * 3 + k] - Cn[s * 3 + k]); d[k] += wf2; }
         }
     }
-    __device__ void applyJTJ(int, int, int, long s, const Vec<T>& p, T* out) const {
+    template <class P> __device__ void applyJTJ(int, int, int, long s, const P& p, T* out) const {
         const T vf = fit_valid(s) ? w_fit * w_fit : T(0);
 #pragma unroll
         for (int k = 0; k < 3; ++k) { out[k] = vf * p(k, s); out[3 + k] = T(0); }

@@ -12,6 +12,7 @@ template <class T>
 struct ImageWarpingFunctor : FunctorDefaults<T> {
     using Scalar = T;
     static constexpr int U = 3, ND = 2;
+    static constexpr bool HAS_EXCLUDE = true;
     static constexpr bool USE_PRE = true;
     int W, H, D;
     T* O; T* A; const T* Ur; const T* Cn; const T* M;
@@ -71,7 +72,7 @@ struct ImageWarpingFunctor : FunctorDefaults<T> {
             d[2] += wr2 * (Dv[0] * Dv[0] + Dv[1] * Dv[1]);
         });
     }
-    __device__ void applyJTJ(int x, int y, int, long s, const Vec<T>& p, T* out) const {
+    template <class P> __device__ void applyJTJ(int x, int y, int, long s, const P& p, T* out) const {
         T ui[2], ci[2]; load2(Ur + s * 2, ui); load2(Cn + s * 2, ci);
         T sa, ca; sincos_t(A[s], sa, ca);
         const T wf2 = w_fit * w_fit, wr2 = w_reg * w_reg;

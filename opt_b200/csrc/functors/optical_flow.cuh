@@ -68,7 +68,7 @@ struct OpticalFlowFunctor : FunctorDefaults<T> {
             d[0] += T(2) * wr2; d[1] += T(2) * wr2;
         });
     }
-    __device__ void applyJTJ(int x, int y, int, long s, const Vec<T>& p, T* out) const {
+    template <class P> __device__ void applyJTJ(int x, int y, int, long s, const P& p, T* out) const {
         T xi[2]; load2(X + s * 2, xi);
         const T px = (T)x + xi[0], py = (T)y + xi[1];
         const T wf2 = w_fit * w_fit, wr2 = w_reg * w_reg;

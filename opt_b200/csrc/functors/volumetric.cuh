@@ -78,7 +78,7 @@ struct VolumetricFunctor : FunctorDefaults<T> {
             }
         });
     }
-    __device__ void applyJTJ(int x, int y, int z, long s, const Vec<T>& p, T* out) const {
+    template <class P> __device__ void applyJTJ(int x, int y, int z, long s, const P& p, T* out) const {
         T ui[3], ai[3]; load3(Ur + s * 3, ui); load3(A + s * 3, ai);
         Rot3<T> R; R.set(ai);
         const T wf2 = w_fit * w_fit, wr2 = w_reg * w_reg;
