@@ -34,26 +34,30 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
 
 from opt_b200 import examples  # noqa: E402
 
-# name -> (builder, full-size args, solver kwargs, U, algorithmic bytes/site/PCG-iteration fp32,
-#          PCGStep1 bytes/site) ; byte figures from SURVEY.md section 8(d)
+# Algorithmic bytes follow SURVEY.md section 8(d): per PCG iteration s*(13U + I_JTJ + 3 I_excl) per site
+# (+ `extra` bytes per vertex of index traffic for graphs); PCGStep1 alone s*(2U + I_JTJ + I_excl).
+# ijtj = input channels the J^T J functor needs, iexcl = channels Exclude() reads, mask = index of the
+# exclude mask in problemparams.  The unknown-vector terms are counted for ACTIVE (non-excluded) sites
+# only -- excluded pixels are not unknowns and hold no data -- the exclude reads for all sites; the
+# all-sites figure of the SURVEY table is reported next to it as `survey_formula`.
 WORKLOADS = {
     "poisson_4096": dict(builder=examples.poisson_synthetic, args=(4096, 4096), kw=dict(n_iter=1, l_iter=100),
-                         U=4, bytes_iter=220, bytes_step1=(2 * 4 + 0 + 1) * 4,
+                         U=4, ijtj=0, iexcl=1, extra=0, mask=2,
                          desc="poisson_image_editing 4096x4096 float4, GN 1x100 PCG, fp32"),
     "image_warping_512": dict(builder=examples.image_warping_synthetic, args=(512, 512), kw=dict(n_iter=8, l_iter=400),
-                              U=3, bytes_iter=200, bytes_step1=(2 * 3 + 8 + 1) * 4,
+                              U=3, ijtj=8, iexcl=1, extra=0, mask=4,
                               desc="image_warping 512x512, GN 8x400 PCG, fp32"),
     "optical_flow_2048": dict(builder=examples.optical_flow_synthetic, args=(2048, 2048), kw=dict(n_iter=10, l_iter=50),
-                              U=2, bytes_iter=120, bytes_step1=(2 * 2 + 4) * 4,
+                              U=2, ijtj=4, iexcl=0, extra=0, mask=None,
                               desc="optical_flow 2048x2048, GN 10x50 PCG, fp32"),
     "volumetric_512": dict(builder=examples.volumetric_synthetic, args=(512, 512, 512), kw=dict(n_iter=2, l_iter=20),
-                           U=6, bytes_iter=348, bytes_step1=(2 * 6 + 9) * 4,
+                           U=6, ijtj=9, iexcl=0, extra=0, mask=None,
                            desc="volumetric_mesh_deformation 512^3, GN 2x20 PCG, fp32"),
     "volumetric_256": dict(builder=examples.volumetric_synthetic, args=(256, 256, 256), kw=dict(n_iter=2, l_iter=20),
-                           U=6, bytes_iter=348, bytes_step1=(2 * 6 + 9) * 4,
+                           U=6, ijtj=9, iexcl=0, extra=0, mask=None,
                            desc="volumetric_mesh_deformation 256^3, GN 2x20 PCG, fp32"),
     "arap_1m": dict(builder=examples.arap_synthetic, args=(1024, 1024), kw=dict(n_iter=2, l_iter=100),
-                    U=6, bytes_iter=396, bytes_step1=(2 * 6 + 9) * 4 + 48,
+                    U=6, ijtj=9, iexcl=0, extra=48, mask=None,
                     desc="arap_mesh_deformation 1024x1024-vertex mesh (6.28M directed edges), GN 2x100 PCG, fp32"),
 }
 
@@ -286,17 +290,30 @@ def run_ours(args, pr, w, rank, world, mode):
         fused = kt["PCGStep3+1"][0] > 0
         peak, peak_src = load_peaks()
         N = sol.site_count()
+        m = w["mask"]
+        n_act = int((pr.params[m] == 0).sum()) if m is not None else N
+        sz, U = (8 if pr.double else 4), w["U"]
+
+        def alg_bytes(per_active, per_site):
+            return sz * (n_act * per_active + N * per_site)
+
+        step1_words = 2 * U + w["ijtj"] + (3 * U if fused else 0)      # fused kernel also does PCGStep3's 3U words
+        iter_words = 13 * U + w["ijtj"]
         if n1:
             per_launch_ms = t1 / n1
-            alg = (w["bytes_step1"] + (3 * w["U"] * 4 if fused else 0)) * N      # fused kernel also does PCGStep3's 3U words
+            alg = alg_bytes(step1_words, w["iexcl"]) + w["extra"] * N
             ach = alg / (per_launch_ms * 1e-3) / 1e9
-            roof = {"bound": "hbm", "kernel": "PCGStep3+PCGStep1 (fused)" if fused else "PCGStep1", "achieved": ach, "peak": peak, "unit": "GB/s",
-                    "frac": ach / peak, "traffic": None, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": alg, "ms_per_launch": per_launch_ms,
+            it_alg = alg_bytes(iter_words, 3 * w["iexcl"]) + w["extra"] * N
+            it_rate = iters * args.steps / (ms * 1e-3)
+            it_survey = sz * N * (iter_words + 3 * w["iexcl"]) + w["extra"] * N
+            roof = {"bound": "hbm", "kernel": "PCGStep3+PCGStep1 (fused)" if fused else "PCGStep1",
+                    "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                    "peak_source": peak_src, "algorithmic_bytes_per_launch": alg, "ms_per_launch": per_launch_ms,
+                    "active_sites": n_act, "sites": N,
                     "kernel_ms": {k: (v[1] / v[0] if v[0] else None) for k, v in kt.items()},
-                    "iteration": {"algorithmic_bytes": w["bytes_iter"] * N,
-                                  "achieved": w["bytes_iter"] * N * (iters * args.steps / (ms * 1e-3)) / 1e9,
-                                  "frac": w["bytes_iter"] * N * (iters * args.steps / (ms * 1e-3)) / 1e9 / peak}}
+                    "iteration": {"algorithmic_bytes": it_alg, "achieved": it_alg * it_rate / 1e9,
+                                  "frac": it_alg * it_rate / 1e9 / peak,
+                                  "survey_formula": {"algorithmic_bytes": it_survey, "frac": it_survey * it_rate / 1e9 / peak}}}
         tsol.close()
 
     # units: one PCG iteration over one single-GPU-sized grid.  weak slab / replicas: N such units per

@@ -114,6 +114,30 @@ struct OptK_Plan {
         for (auto& t : timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
         timed.clear();
     }
+    // persistent kernels: as many CTAs as can be co-resident (occupancy x SM count), never more than
+    // there are tiles -- a larger grid would run in waves and leave a tail
+    int n_sm = 0;
+    std::map<const void*, int> occ_cache;
+    template <class... KA>
+    dim3 persistent_grid(void (*kernel)(KA...), int threads, long ntiles) {
+        if (!n_sm) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev); }
+        auto it = occ_cache.find((const void*)kernel);
+        int nb;
+        if (it == occ_cache.end()) {
+            nb = 1;
+            OPTK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, threads, 0));
+            if (nb < 1) nb = 1;
+            occ_cache[(const void*)kernel] = nb;
+        } else nb = it->second;
+        long g = (long)n_sm * nb;
+        if (g > ntiles) g = ntiles;
+        if (g < 1) g = 1;
+        return dim3((unsigned)g);
+    }
+    template <class... KA, class... A>
+    void launch_tiles(const char* name, long ntiles, dim3 block, void (*kernel)(KA...), A... args) {
+        launch(name, persistent_grid(kernel, (int)(block.x * block.y * block.z), ntiles), block, kernel, args...);
+    }
     void print_timing() {                                    // backend_cuda.t:262-297
         if (!timing || timed.empty()) return;
         OPTK_CUDA(cudaStreamSynchronize(stream));
@@ -136,11 +160,22 @@ struct OptK_Plan {
 namespace optk {
 
 // ------------------------------------------------------------------------------ site mapping
+// Site kernels are persistent: a fixed grid (a few CTAs per SM) loops over the virtual tiles of the
+// index space, so a kernel does one reduction atomic per resident CTA instead of one per tile (65 536
+// same-address atomics per launch on a 4096^2 image otherwise) and pays no CTA-dispatch cost for
+// tiles that are entirely masked out.
+struct TileGrid {
+    int gx, gy, gz;     // tiles per dimension
+    long n;             // gx*gy*gz
+};
+#define OPTK_TILE_LOOP(tg) for (long tile_ = blockIdx.x; tile_ < (tg).n; tile_ += gridDim.x)
+
 template <class F>
-__device__ __forceinline__ bool thread_site(const F& f, int& x, int& y, int& z, long& s) {
-    x = blockIdx.x * blockDim.x + threadIdx.x;
-    y = blockIdx.y * blockDim.y + threadIdx.y;
-    z = blockIdx.z * blockDim.z + threadIdx.z;
+__device__ __forceinline__ bool thread_site(const F& f, const TileGrid& tg, long tile, int& x, int& y, int& z, long& s) {
+    const int bx = (int)(tile % tg.gx), by = (int)((tile / tg.gx) % tg.gy), bz = (int)(tile / ((long)tg.gx * tg.gy));
+    x = bx * blockDim.x + threadIdx.x;
+    y = by * blockDim.y + threadIdx.y;
+    z = bz * blockDim.z + threadIdx.z;
     s = x + (long)f.W * (y + (long)f.H * z);
     // slab mode: only rows (2-D) / planes (3-D) [o_lo, o_hi) are owned by this rank; the rest of the
     // local array are ghost copies of the neighbours' boundary and are only ever read
@@ -151,13 +186,14 @@ __device__ __forceinline__ bool thread_site(const F& f, int& x, int& y, int& z, 
 // ------------------------------------------------------------------------------ site kernels
 // PCGInit1 (solver:521-563).  For graph problems the raw diagonal is stored and inverted later.
 template <class F>
-__global__ void k_pcg_init1(F f, Vec<typename F::Scalar> delta, Vec<typename F::Scalar> r,
+__global__ void k_pcg_init1(F f, TileGrid tg, Vec<typename F::Scalar> delta, Vec<typename F::Scalar> r,
                             Vec<typename F::Scalar> p, Vec<typename F::Scalar> pre, double* aNum) {
     using T = typename F::Scalar;
     constexpr int U = F::U;
     int x, y, z; long s;
     double acc = 0.0;
-    if (thread_site(f, x, y, z, s)) {
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, z, s)) {
         T g[U], d[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) g[u] = d[u] = T(0);
@@ -198,7 +234,7 @@ struct FusedDir {
     __device__ __forceinline__ T operator()(int u, long s) const { return z(u, s) + beta * p(u, s); }
 };
 template <class F, bool LM>
-__global__ void k_apply_jtj_fused(F f, Vec<typename F::Scalar> z, Vec<typename F::Scalar> p_old,
+__global__ void k_apply_jtj_fused(F f, TileGrid tg, Vec<typename F::Scalar> z, Vec<typename F::Scalar> p_old,
                                   Vec<typename F::Scalar> p_new, Vec<typename F::Scalar> out,
                                   Vec<typename F::Scalar> CtC, const double* bNum, const double* aNum,
                                   double* den, double* zero_a, double* zero_b) {
@@ -211,7 +247,8 @@ __global__ void k_apply_jtj_fused(F f, Vec<typename F::Scalar> z, Vec<typename F
         if (zero_a) *zero_a = 0.0;
         if (zero_b) *zero_b = 0.0;
     }
-    if (thread_site(f, x, y, zc, s) && !f.exclude(x, y, zc, s)) {
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, zc, s) && !f.exclude(x, y, zc, s)) {
         T o[U];
         f.applyJTJ(x, y, zc, s, dir, o);
 #pragma unroll
@@ -228,14 +265,15 @@ __global__ void k_apply_jtj_fused(F f, Vec<typename F::Scalar> z, Vec<typename F
 
 // PCGStep1 / computeAdelta (solver:607-632, 873-878): out = (J^T J [+ CtC]) dir over non-excluded sites
 template <class F, bool LM>
-__global__ void k_apply_jtj(F f, Vec<typename F::Scalar> dir, Vec<typename F::Scalar> out,
+__global__ void k_apply_jtj(F f, TileGrid tg, Vec<typename F::Scalar> dir, Vec<typename F::Scalar> out,
                             Vec<typename F::Scalar> CtC, double* den, double* zero_slot) {
     using T = typename F::Scalar;
     constexpr int U = F::U;
     int x, y, z; long s;
     double acc = 0.0;
     if (zero_slot && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && linear_tid() == 0) *zero_slot = 0.0;
-    if (thread_site(f, x, y, z, s) && !f.exclude(x, y, z, s)) {
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, z, s) && !f.exclude(x, y, z, s)) {
         T o[U];
         f.applyJTJ(x, y, z, s, dir, o);
 #pragma unroll
@@ -251,31 +289,34 @@ __global__ void k_apply_jtj(F f, Vec<typename F::Scalar> dir, Vec<typename F::Sc
 
 // computeCost (solver:971-997)
 template <class F>
-__global__ void k_cost(F f, double* target) {
+__global__ void k_cost(F f, TileGrid tg, double* target) {
     using T = typename F::Scalar;
     int x, y, z; long s;
     double acc = 0.0;
-    if (thread_site(f, x, y, z, s) && !f.exclude(x, y, z, s)) acc = (double)(T)(0.5 * (double)f.cost(x, y, z, s));
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, z, s) && !f.exclude(x, y, z, s)) acc += (double)(T)(0.5 * (double)f.cost(x, y, z, s));
     block_accumulate(acc, target);
 }
 
 // computeModelCost (solver:1105-1118)
 template <class F>
-__global__ void k_model_cost(F f, Vec<typename F::Scalar> delta, double* target) {
+__global__ void k_model_cost(F f, TileGrid tg, Vec<typename F::Scalar> delta, double* target) {
     using T = typename F::Scalar;
     int x, y, z; long s;
     double acc = 0.0;
-    if (thread_site(f, x, y, z, s) && !f.exclude(x, y, z, s)) acc = (double)(T(0.5) * f.modelCost(x, y, z, s, delta));
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, z, s) && !f.exclude(x, y, z, s)) acc += (double)(T(0.5) * f.modelCost(x, y, z, s, delta));
     block_accumulate(acc, target);
 }
 
 // PCGComputeCtC (solver:1042-1048): CtC = diag(J^T J) / radius
 template <class F>
-__global__ void k_compute_ctc(F f, Vec<typename F::Scalar> CtC, typename F::Scalar inv_radius) {
+__global__ void k_compute_ctc(F f, TileGrid tg, Vec<typename F::Scalar> CtC, typename F::Scalar inv_radius) {
     using T = typename F::Scalar;
     constexpr int U = F::U;
     int x, y, z; long s;
-    if (thread_site(f, x, y, z, s) && !f.exclude(x, y, z, s)) {
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, z, s) && !f.exclude(x, y, z, s)) {
         T g[U], d[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) g[u] = d[u] = T(0);
@@ -287,7 +328,7 @@ __global__ void k_compute_ctc(F f, Vec<typename F::Scalar> CtC, typename F::Scal
 
 // PCGFinalizeDiagonal (solver:1061-1099)
 template <class F>
-__global__ void k_finalize_diagonal(F f, Vec<typename F::Scalar> CtC, Vec<typename F::Scalar> SSq,
+__global__ void k_finalize_diagonal(F f, TileGrid tg, Vec<typename F::Scalar> CtC, Vec<typename F::Scalar> SSq,
                                     Vec<typename F::Scalar> pre, Vec<typename F::Scalar> r,
                                     Vec<typename F::Scalar> b, Vec<typename F::Scalar> p,
                                     Vec<typename F::Scalar> delta, typename F::Scalar radius,
@@ -297,7 +338,8 @@ __global__ void k_finalize_diagonal(F f, Vec<typename F::Scalar> CtC, Vec<typena
     constexpr int U = F::U;
     int x, y, z; long s;
     double acc = 0.0, qacc = 0.0;
-    if (thread_site(f, x, y, z, s) && !f.exclude(x, y, z, s)) {
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, z, s) && !f.exclude(x, y, z, s)) {
         T qq = T(0);
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -315,7 +357,7 @@ __global__ void k_finalize_diagonal(F f, Vec<typename F::Scalar> CtC, Vec<typena
             acc += (double)(res * pp);
             qq += delta(u, s) * (res + res);
         }
-        qacc = (double)(T(0.5) * qq);
+        qacc += (double)(T(0.5) * qq);
     }
     block_accumulate(acc, aNum);
     block_accumulate(qacc, q);
@@ -324,10 +366,11 @@ __global__ void k_finalize_diagonal(F f, Vec<typename F::Scalar> CtC, Vec<typena
 // PCGLinearUpdate / savePreviousUnknowns / revertUpdate (solver:854-887); MODE 0: X += delta,
 // 1: prevX = X, 2: X = prevX
 template <class F, int MODE>
-__global__ void k_unknown_update(F f, Vec<typename F::Scalar> v) {
+__global__ void k_unknown_update(F f, TileGrid tg, Vec<typename F::Scalar> v) {
     constexpr int U = F::U;
     int x, y, z; long s;
-    if (thread_site(f, x, y, z, s) && !f.exclude(x, y, z, s)) {
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, z, s) && !f.exclude(x, y, z, s)) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             typename F::Scalar* xp = f.xptr(s, u);
@@ -339,9 +382,10 @@ __global__ void k_unknown_update(F f, Vec<typename F::Scalar> v) {
 }
 
 template <class F>
-__global__ void k_precompute(F f) {
+__global__ void k_precompute(F f, TileGrid tg) {
     int x, y, z; long s;
-    if (thread_site(f, x, y, z, s)) f.precompute(x, y, z, s);
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, z, s)) f.precompute(x, y, z, s);
 }
 
 // ------------------------------------------------------------------------------ graph kernels
@@ -353,13 +397,14 @@ __global__ void k_graph_jtf(F f, long E, Vec<typename F::Scalar> r, Vec<typename
 }
 // PCGInit1_Finish (solver:570-598): no exclude test
 template <class F>
-__global__ void k_pcg_init1_finish(F f, Vec<typename F::Scalar> r, Vec<typename F::Scalar> pre,
+__global__ void k_pcg_init1_finish(F f, TileGrid tg, Vec<typename F::Scalar> r, Vec<typename F::Scalar> pre,
                                    Vec<typename F::Scalar> p, double* aNum) {
     using T = typename F::Scalar;
     constexpr int U = F::U;
     int x, y, z; long s;
     double acc = 0.0;
-    if (thread_site(f, x, y, z, s)) {
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, z, s)) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             T res = r(u, s);
@@ -440,11 +485,12 @@ __global__ void __launch_bounds__(256) k_pcg_step2(long nvec, const unsigned cha
                                                    double* bNum, double* q, double* zero_slot) {
     using V = typename VecIO<T>::V;
     constexpr int VW = VecIO<T>::W;
-    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    const long i0 = blockIdx.x * (long)blockDim.x + threadIdx.x, istride = (long)gridDim.x * blockDim.x;
     const T alpha = (T)(*aNum) / (T)(*aDen);
-    if (i == 0 && zero_slot) *zero_slot = 0.0;
+    if (i0 == 0 && zero_slot) *zero_slot = 0.0;
     double bacc = 0.0, qacc = 0.0;
-    if (i < nvec && group_active<T>(active4, i, plane)) {
+    for (long i = i0; i < nvec; i += istride)
+    if (group_active<T>(active4, i, plane)) {
         V d = reinterpret_cast<const V*>(delta)[i];
         V pv = reinterpret_cast<const V*>(p)[i];
         V rv = reinterpret_cast<const V*>(r)[i];
@@ -467,8 +513,8 @@ __global__ void __launch_bounds__(256) k_pcg_step2(long nvec, const unsigned cha
         reinterpret_cast<V*>(delta)[i] = d;
         reinterpret_cast<V*>(r)[i] = rv;
         if (USE_PRE) reinterpret_cast<V*>(z)[i] = zv;
-        bacc = (double)bsum;
-        qacc = (double)(T(0.5) * qsum);
+        bacc += (double)bsum;
+        qacc += (double)(T(0.5) * qsum);
     }
     block_accumulate(bacc, bNum);
     if (LM) block_accumulate(qacc, q);
@@ -481,10 +527,11 @@ __global__ void __launch_bounds__(256) k_pcg_step3(long nvec, const unsigned cha
                                                    const double* bNum, const double* aNum, double* zero_slot) {
     using V = typename VecIO<T>::V;
     constexpr int VW = VecIO<T>::W;
-    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    const long i0 = blockIdx.x * (long)blockDim.x + threadIdx.x, istride = (long)gridDim.x * blockDim.x;
     const T beta = (T)(*bNum) / (T)(*aNum);
-    if (i == 0 && zero_slot) *zero_slot = 0.0;
-    if (i < nvec && group_active<T>(active4, i, plane)) {
+    if (i0 == 0 && zero_slot) *zero_slot = 0.0;
+    for (long i = i0; i < nvec; i += istride)
+    if (group_active<T>(active4, i, plane)) {
         V zv = reinterpret_cast<const V*>(z)[i];
         V pv = reinterpret_cast<const V*>(p)[i];
 #pragma unroll
@@ -500,9 +547,10 @@ __global__ void __launch_bounds__(256) k_axpy_alpha(long nvec, const unsigned ch
                                                     const double* aNum, const double* aDen) {
     using V = typename VecIO<T>::V;
     constexpr int VW = VecIO<T>::W;
-    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    const long i0 = blockIdx.x * (long)blockDim.x + threadIdx.x, istride = (long)gridDim.x * blockDim.x;
     const T alpha = (T)(*aNum) / (T)(*aDen);
-    if (i < nvec && group_active<T>(active4, i, plane)) {
+    for (long i = i0; i < nvec; i += istride)
+    if (group_active<T>(active4, i, plane)) {
         V d = reinterpret_cast<const V*>(delta)[i];
         V pv = reinterpret_cast<const V*>(p)[i];
 #pragma unroll
@@ -520,10 +568,11 @@ __global__ void __launch_bounds__(256) k_residual_reset(long nvec, const unsigne
                                                         double* bNum, double* q, double* zero_slot) {
     using V = typename VecIO<T>::V;
     constexpr int VW = VecIO<T>::W;
-    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
-    if (i == 0 && zero_slot) *zero_slot = 0.0;
+    const long i0 = blockIdx.x * (long)blockDim.x + threadIdx.x, istride = (long)gridDim.x * blockDim.x;
+    if (i0 == 0 && zero_slot) *zero_slot = 0.0;
     double bacc = 0.0, qacc = 0.0;
-    if (i < nvec && group_active<T>(active4, i, plane)) {
+    for (long i = i0; i < nvec; i += istride)
+    if (group_active<T>(active4, i, plane)) {
         V d = reinterpret_cast<const V*>(delta)[i];
         V av = reinterpret_cast<const V*>(Adelta)[i];
         V bv = reinterpret_cast<const V*>(b)[i];
@@ -541,8 +590,8 @@ __global__ void __launch_bounds__(256) k_residual_reset(long nvec, const unsigne
         }
         reinterpret_cast<V*>(r)[i] = rv;
         if (USE_PRE) reinterpret_cast<V*>(z)[i] = zv;
-        bacc = (double)bsum;
-        qacc = (double)(T(0.5) * qsum);
+        bacc += (double)bsum;
+        qacc += (double)(T(0.5) * qsum);
     }
     block_accumulate(bacc, bNum);
     block_accumulate(qacc, q);
@@ -567,6 +616,8 @@ struct Engine : OptK_Plan {
     double* h_scal = nullptr;    // pinned
     T radius = 0, min_diag = 0, max_diag = 0;
     dim3 sgrid, sblock;
+    TileGrid tg;
+    int nsm = 148;
     // slab decomposition along the slowest dimension; nranks == 1: single GPU
     int rank = 0, nranks = 1, halo = 0;
     ncclComm_t comm = nullptr;
@@ -591,14 +642,17 @@ struct Engine : OptK_Plan {
             OPTK_CUDA(cudaMalloc(&active4, Npad / 4));
             OPTK_CUDA(cudaMemsetAsync(active4, 0, Npad / 4, stream));
         }
-        if (getenv("OPTB200_NO_FUSE")) fuse = false;
+        if (getenv("OPTB200_NO_FUSE") || !F::FUSE_STEP3) fuse = false;
         OPTK_CUDA(cudaMalloc(&scal, S_COUNT * sizeof(double)));
         OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
         OPTK_CUDA(cudaMallocHost(&h_scal, S_COUNT * sizeof(double)));
         if (F::ND == 1) { sblock = dim3(256, 1, 1); }
         else if (F::ND == 2) { sblock = dim3(32, 8, 1); }
         else { sblock = dim3(32, 4, 2); }
-        sgrid = dim3((f.W + sblock.x - 1) / sblock.x, (f.H + sblock.y - 1) / sblock.y, (f.D + sblock.z - 1) / sblock.z);
+        tg.gx = (f.W + sblock.x - 1) / sblock.x; tg.gy = (f.H + sblock.y - 1) / sblock.y; tg.gz = (f.D + sblock.z - 1) / sblock.z;
+        tg.n = (long)tg.gx * tg.gy * tg.gz;
+        { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev); }
+        sgrid = dim3((unsigned)std::min<long>(tg.n, (long)nsm * 8));        // persistent: <= 8 CTAs of 256 threads per SM
         f.alloc_temporaries(stream);
         OPTK_CUDA(cudaStreamSynchronize(stream));
     }
@@ -616,7 +670,7 @@ struct Engine : OptK_Plan {
 
     double* S(int slot) const { return scal + slot; }
     long flat_vecs() const { return (long)U * Npad / VecIO<T>::W; }
-    dim3 flat_grid() const { return dim3((unsigned)((flat_vecs() + 255) / 256)); }
+    dim3 flat_grid() const { return dim3((unsigned)std::min<long>((flat_vecs() + 255) / 256, (long)nsm * 8)); }
     dim3 edge_grid() const { return dim3((unsigned)((E + 255) / 256)); }
 
     // ---- multi-GPU: ownership, scalar all-reduce, halo exchange ---------------------------------
@@ -674,11 +728,11 @@ struct Engine : OptK_Plan {
     }
 
     void precompute() override {
-        if (F::HAS_PRECOMPUTE) this->launch("precompute", sgrid, dim3(sblock), k_precompute<F>, f);
+        if (F::HAS_PRECOMPUTE) this->launch_tiles("precompute", tg.n, sblock, k_precompute<F>, f, tg);
     }
     double cost() override {
         OPTK_CUDA(cudaMemsetAsync(S(S_COST), 0, sizeof(double), stream));
-        this->launch("computeCost", sgrid, dim3(sblock), k_cost<F>, f, S(S_COST));
+        this->launch_tiles("computeCost", tg.n, sblock, k_cost<F>, f, tg, S(S_COST));
         if (GRAPH) this->launch("computeCost_Graph", edge_grid(), dim3(256), k_graph_cost<F>, f, E, S(S_COST));
         reduce(S_COST);
         return (double)(T)read_scalar(S_COST);
@@ -686,7 +740,7 @@ struct Engine : OptK_Plan {
     double model_cost() override {
         exchange(delta);
         OPTK_CUDA(cudaMemsetAsync(S(S_MODEL), 0, sizeof(double), stream));
-        this->launch("computeModelCost", sgrid, dim3(sblock), k_model_cost<F>, f, delta, S(S_MODEL));
+        this->launch_tiles("computeModelCost", tg.n, sblock, k_model_cost<F>, f, tg, delta, S(S_MODEL));
         if (GRAPH) this->launch("computeModelCost_Graph", edge_grid(), dim3(256), k_graph_model_cost<F>, f, E, delta, S(S_MODEL));
         reduce(S_MODEL);
         return (double)(T)read_scalar(S_MODEL);
@@ -697,19 +751,19 @@ struct Engine : OptK_Plan {
         OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
         if (F::HAS_EXCLUDE)                                 // Exclude() may read inputs the caller changed
             this->launch("activeGroups", dim3((unsigned)((Npad / 4 + 255) / 256)), dim3(256), k_active4<F>, f, Npad / 4, active4);
-        this->launch("PCGInit1", sgrid, dim3(sblock), k_pcg_init1<F>, f, delta, r, p, pre, S(S_RZ0));
+        this->launch_tiles("PCGInit1", tg.n, sblock, k_pcg_init1<F>, f, tg, delta, r, p, pre, S(S_RZ0));
         if (GRAPH) {
             this->launch("PCGInit1_Graph", edge_grid(), dim3(256), k_graph_jtf<F>, f, E, r, pre);
-            this->launch("PCGInit1_Finish", sgrid, dim3(sblock), k_pcg_init1_finish<F>, f, r, pre, p, S(S_RZ0));
+            this->launch_tiles("PCGInit1_Finish", tg.n, sblock, k_pcg_init1_finish<F>, f, tg, r, pre, p, S(S_RZ0));
         }
         if (lm) {
             OPTK_CUDA(cudaMemsetAsync(S(S_RZ0), 0, sizeof(double), stream));
             if (nIter == 0)                                  // PCGSaveSSq (solver:1052-1057), flat copy
                 OPTK_CUDA(cudaMemcpyAsync(SSq.d, pre.d, (size_t)U * Npad * sizeof(T), cudaMemcpyDeviceToDevice, stream));
             const T inv_radius = T(1) / radius;
-            this->launch("PCGComputeCtC", sgrid, dim3(sblock), k_compute_ctc<F>, f, CtC, inv_radius);
+            this->launch_tiles("PCGComputeCtC", tg.n, sblock, k_compute_ctc<F>, f, tg, CtC, inv_radius);
             if (GRAPH) this->launch("PCGComputeCtC_Graph", edge_grid(), dim3(256), k_graph_ctc<F>, f, E, CtC, inv_radius);
-            this->launch("PCGFinalizeDiagonal", sgrid, dim3(sblock), k_finalize_diagonal<F>, f, CtC, SSq, pre, r, b, p, delta, radius, min_diag, max_diag, S(S_RZ0), S(S_Q));
+            this->launch_tiles("PCGFinalizeDiagonal", tg.n, sblock, k_finalize_diagonal<F>, f, tg, CtC, SSq, pre, r, b, p, delta, radius, min_diag, max_diag, S(S_RZ0), S(S_Q));
             reduce(S_Q);
         }
         reduce(S_RZ0);
@@ -719,13 +773,13 @@ struct Engine : OptK_Plan {
     void apply_A(const char* name, const char* gname, Vec<T> dir, Vec<T> out, double* den, double* zero_slot) {
         if constexpr (F::HAS_FAST_APPLY) {
             if (f.fast_ok()) {
-                if (lm) this->launch(name, f.fast_grid(), f.fast_block(), F::template fast_kernel<false, true>(), f, dir, dir, dir, out, CtC, (const unsigned char*)active4, (const double*)nullptr, (const double*)nullptr, den, zero_slot, (double*)nullptr);
-                else    this->launch(name, f.fast_grid(), f.fast_block(), F::template fast_kernel<false, false>(), f, dir, dir, dir, out, CtC, (const unsigned char*)active4, (const double*)nullptr, (const double*)nullptr, den, zero_slot, (double*)nullptr);
+                if (lm) this->launch_tiles(name, f.fast_tiles(), f.fast_block(), F::template fast_kernel<false, true>(), f, dir, dir, dir, out, CtC, (const unsigned char*)active4, (const double*)nullptr, (const double*)nullptr, den, zero_slot, (double*)nullptr);
+                else    this->launch_tiles(name, f.fast_tiles(), f.fast_block(), F::template fast_kernel<false, false>(), f, dir, dir, dir, out, CtC, (const unsigned char*)active4, (const double*)nullptr, (const double*)nullptr, den, zero_slot, (double*)nullptr);
                 return;
             }
         }
-        if (lm) this->launch(name, sgrid, dim3(sblock), k_apply_jtj<F, true>, f, dir, out, CtC, den, zero_slot);
-        else    this->launch(name, sgrid, dim3(sblock), k_apply_jtj<F, false>, f, dir, out, CtC, den, zero_slot);
+        if (lm) this->launch_tiles(name, tg.n, sblock, k_apply_jtj<F, true>, f, tg, dir, out, CtC, den, zero_slot);
+        else    this->launch_tiles(name, tg.n, sblock, k_apply_jtj<F, false>, f, tg, dir, out, CtC, den, zero_slot);
         if (GRAPH) this->launch(gname, edge_grid(), dim3(256), k_graph_jtj<F>, f, E, dir, out, den);
     }
 
@@ -743,14 +797,14 @@ struct Engine : OptK_Plan {
             double* prevA = S(S_RZ0 + (l + 2) % 3);
             if constexpr (F::HAS_FAST_APPLY) {
                 if (f.fast_ok()) {
-                    if (lm) this->launch("PCGStep3+1", f.fast_grid(), f.fast_block(), F::template fast_kernel<true, true>(), f, z, p, p_alt, Ap, CtC, (const unsigned char*)active4, (const double*)aNum, (const double*)prevA, aDen, bNum, S(S_Q));
-                    else    this->launch("PCGStep3+1", f.fast_grid(), f.fast_block(), F::template fast_kernel<true, false>(), f, z, p, p_alt, Ap, CtC, (const unsigned char*)active4, (const double*)aNum, (const double*)prevA, aDen, bNum, (double*)nullptr);
+                    if (lm) this->launch_tiles("PCGStep3+1", f.fast_tiles(), f.fast_block(), F::template fast_kernel<true, true>(), f, z, p, p_alt, Ap, CtC, (const unsigned char*)active4, (const double*)aNum, (const double*)prevA, aDen, bNum, S(S_Q));
+                    else    this->launch_tiles("PCGStep3+1", f.fast_tiles(), f.fast_block(), F::template fast_kernel<true, false>(), f, z, p, p_alt, Ap, CtC, (const unsigned char*)active4, (const double*)aNum, (const double*)prevA, aDen, bNum, (double*)nullptr);
                     std::swap(p.d, p_alt.d);
                     goto applied;
                 }
             }
-            if (lm) this->launch("PCGStep3+1", sgrid, dim3(sblock), k_apply_jtj_fused<F, true>, f, z, p, p_alt, Ap, CtC, aNum, prevA, aDen, bNum, S(S_Q));
-            else    this->launch("PCGStep3+1", sgrid, dim3(sblock), k_apply_jtj_fused<F, false>, f, z, p, p_alt, Ap, CtC, aNum, prevA, aDen, bNum, (double*)nullptr);
+            if (lm) this->launch_tiles("PCGStep3+1", tg.n, sblock, k_apply_jtj_fused<F, true>, f, tg, z, p, p_alt, Ap, CtC, aNum, prevA, aDen, bNum, S(S_Q));
+            else    this->launch_tiles("PCGStep3+1", tg.n, sblock, k_apply_jtj_fused<F, false>, f, tg, z, p, p_alt, Ap, CtC, aNum, prevA, aDen, bNum, (double*)nullptr);
             std::swap(p.d, p_alt.d);
             if (GRAPH) this->launch("PCGStep1_Graph", edge_grid(), dim3(256), k_graph_jtj<F>, f, E, p, Ap, aDen);
         } else {
@@ -759,19 +813,19 @@ struct Engine : OptK_Plan {
     applied:
         reduce(int(aDen - scal));
         if (lm && reset) {
-            this->launch("PCGStep2_1stHalf", flat_grid(), dim3(256), k_axpy_alpha<T>, nv, act, Npad, delta.d, p.d, aNum, aDen);
+            this->launch_tiles("PCGStep2_1stHalf", (flat_vecs() + 255) / 256, dim3(256), k_axpy_alpha<T>, nv, act, Npad, delta.d, p.d, aNum, aDen);
             exchange(delta);
             apply_A("computeAdelta", "computeAdelta_Graph", delta, Adelta, S(S_DUMMY), nullptr);
-            this->launch("PCGStep2_2ndHalf", flat_grid(), dim3(256), k_residual_reset<T, F::USE_PRE>, nv, act, Npad, delta.d, r.d, Adelta.d, pre.d, b.d, z.d, bNum, S(S_Q), nextDen);
+            this->launch_tiles("PCGStep2_2ndHalf", (flat_vecs() + 255) / 256, dim3(256), k_residual_reset<T, F::USE_PRE>, nv, act, Npad, delta.d, r.d, Adelta.d, pre.d, b.d, z.d, bNum, S(S_Q), nextDen);
         } else if (lm) {
-            this->launch("PCGStep2", flat_grid(), dim3(256), k_pcg_step2<T, F::USE_PRE, true>, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
+            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, true>, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
         } else {
-            this->launch("PCGStep2", flat_grid(), dim3(256), k_pcg_step2<T, F::USE_PRE, false>, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
+            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, false>, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
         }
         reduce(int(bNum - scal));
         if (lm) reduce(S_Q);
         if (!fuse) {
-            this->launch("PCGStep3", flat_grid(), dim3(256), k_pcg_step3<T>, nv, act, Npad, z.d, p.d, bNum, aNum, nextB);
+            this->launch_tiles("PCGStep3", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step3<T>, nv, act, Npad, z.d, p.d, bNum, aNum, nextB);
             exchange(p);
         }
         // fused mode: PCGStep3 of this iteration happens inside the next iteration's first kernel; after
@@ -781,13 +835,13 @@ struct Engine : OptK_Plan {
         for (int l = 0; l < lIterations; ++l) pcg_iter(l, 0);
     }
 
-    void save_unknowns() override { this->launch("savePreviousUnknowns", sgrid, dim3(sblock), k_unknown_update<F, 1>, f, prevX); }
+    void save_unknowns() override { this->launch_tiles("savePreviousUnknowns", tg.n, sblock, k_unknown_update<F, 1>, f, tg, prevX); }
     void linear_update() override {
-        this->launch("PCGLinearUpdate", sgrid, dim3(sblock), k_unknown_update<F, 0>, f, delta);
+        this->launch_tiles("PCGLinearUpdate", tg.n, sblock, k_unknown_update<F, 0>, f, tg, delta);
         exchange_unknowns();                                // neighbours read X over the stencil
     }
     void revert_update() override {
-        this->launch("revertUpdate", sgrid, dim3(sblock), k_unknown_update<F, 2>, f, prevX);
+        this->launch_tiles("revertUpdate", tg.n, sblock, k_unknown_update<F, 2>, f, tg, prevX);
         exchange_unknowns();
     }
 
@@ -828,6 +882,7 @@ struct FunctorDefaults {
     static constexpr bool HAS_PRECOMPUTE = false;
     static constexpr bool HAS_EXCLUDE = false;           // functors with an Exclude() override this
     static constexpr bool HAS_FAST_APPLY = false;        // functors with a specialised J^T J kernel override this
+    static constexpr bool FUSE_STEP3 = true;             // form p' = z + beta p inside the J^T J kernel (engine.cuh, FusedDir)
     bool fast_ok() const { return false; }
     static constexpr int GV = 0;
     int E = 0;

@@ -24,7 +24,7 @@ struct PoissonFunctor : FunctorDefaults<T> {
     // vectorised / fused J^T J apply (k_poisson_apply below); needs rows that are a multiple of 4 pixels
     static constexpr bool HAS_FAST_APPLY = true;
     bool fast_ok() const { return W % 4 == 0; }
-    dim3 fast_grid() const { return dim3((W / 4 + 31) / 32, (H + 7) / 8, 1); }
+    long fast_tiles() const { return (long)((W / 4 + 31) / 32) * ((H + 7) / 8); }
     dim3 fast_block() const { return dim3(32, 8, 1); }
     template <bool FUSED, bool LM> static auto fast_kernel();
 
@@ -102,18 +102,22 @@ __global__ void __launch_bounds__(256) k_poisson_apply(PoissonFunctor<T> f, Vec<
                                                        const double* bNum, const double* aNum, double* den,
                                                        double* zero_a, double* zero_b) {
     const int W = f.W, H = f.H;
-    const int gx = (blockIdx.x * 32 + threadIdx.x) * 4;
-    const int y = blockIdx.y * 8 + threadIdx.y;
-    const bool in_img = gx < W && y < H;
-    const bool own = in_img && y >= f.o_lo && y < f.o_hi;
-    const long s = (long)y * W + gx;
+    const int tiles_x = (W / 4 + 31) / 32;
+    const long ntiles = (long)tiles_x * ((H + 7) / 8);
     const int lane = threadIdx.x;
     T beta = T(0);
     if (FUSED) beta = (T)(*bNum) / (T)(*aNum);
-    if (blockIdx.x == 0 && blockIdx.y == 0 && linear_tid() == 0) {
+    if (blockIdx.x == 0 && linear_tid() == 0) {
         if (zero_a) *zero_a = 0.0;
         if (zero_b) *zero_b = 0.0;
     }
+    double acc = 0.0;
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {      // persistent CTAs over 128x8-pixel tiles
+    const int gx = ((int)(tile % tiles_x) * 32 + threadIdx.x) * 4;
+    const int y = (int)(tile / tiles_x) * 8 + threadIdx.y;
+    const bool in_img = gx < W && y < H;
+    const bool own = in_img && y >= f.o_lo && y < f.o_hi;
+    const long s = (long)y * W + gx;
     // a quad takes part in loads if it is inside the image and holds at least one unknown
     const bool act = in_img && active4[s >> 2] != 0;
     bool ex[4] = {true, true, true, true};
@@ -123,7 +127,6 @@ __global__ void __launch_bounds__(256) k_poisson_apply(PoissonFunctor<T> f, Vec<
         for (int j = 0; j < 4; ++j) ex[j] = m[j] != T(0);
     }
     const bool up = y > 0, dn = y + 1 < H;
-    double acc = 0.0;
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
         const T* pc = p.d + (long)c * p.plane;
@@ -174,6 +177,7 @@ __global__ void __launch_bounds__(256) k_poisson_apply(PoissonFunctor<T> f, Vec<
             st4v(out.d + (long)c * out.plane + s, o);
         }
     }
+    }   // tile loop
     block_accumulate(acc, den);
 }
 
