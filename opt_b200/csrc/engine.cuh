@@ -381,9 +381,12 @@ __global__ void k_unknown_update(F f, TileGrid tg, Vec<typename F::Scalar> v) {
     }
 }
 
+// precompute (solver:1028-1039) runs over EVERY local site, ghost rows included: the per-site tables are
+// read over the stencil, and the ghost unknowns were refreshed by the halo exchange just before
 template <class F>
 __global__ void k_precompute(F f, TileGrid tg) {
     int x, y, z; long s;
+    f.o_lo = 0; f.o_hi = 0x7fffffff;
     OPTK_TILE_LOOP(tg)
     if (thread_site(f, tg, tile_, x, y, z, s)) f.precompute(x, y, z, s);
 }
@@ -728,7 +731,11 @@ struct Engine : OptK_Plan {
     }
 
     void precompute() override {
-        if (F::HAS_PRECOMPUTE) this->launch_tiles("precompute", tg.n, sblock, k_precompute<F>, f, tg);
+        if constexpr (F::HAS_CUSTOM_PRECOMPUTE) {           // functor owns a table in its own layout
+            this->pre_launch("precompute");
+            f.custom_precompute(stream, nsm);
+            this->post_launch();
+        } else if (F::HAS_PRECOMPUTE) this->launch_tiles("precompute", tg.n, sblock, k_precompute<F>, f, tg);
     }
     double cost() override {
         OPTK_CUDA(cudaMemsetAsync(S(S_COST), 0, sizeof(double), stream));
@@ -880,6 +887,7 @@ struct Engine : OptK_Plan {
 template <class T>
 struct FunctorDefaults {
     static constexpr bool HAS_PRECOMPUTE = false;
+    static constexpr bool HAS_CUSTOM_PRECOMPUTE = false; // precompute is a functor-launched kernel (own table layout)
     static constexpr bool HAS_EXCLUDE = false;           // functors with an Exclude() override this
     static constexpr bool HAS_FAST_APPLY = false;        // functors with a specialised J^T J kernel override this
     static constexpr bool FUSE_STEP3 = true;             // form p' = z + beta p inside the J^T J kernel (engine.cuh, FusedDir)

@@ -20,7 +20,38 @@ struct VolumetricFunctor : FunctorDefaults<T> {
     int W, H, D;
     T* O; T* A; const T* Ur; const T* Cn;
     T w_fit, w_reg;
+    // Table refreshed by precompute (once per nonlinear iteration, like the reference's ComputedArrays,
+    // o.t:3131-3153): sin/cos of the three Euler angles, UrShape and the fit-term predicate of every site,
+    // stored in the tile order of the J^T J kernel below: one record per 30 x FTY x 1 tile, laid out
+    // [plane 10][ty][32 lanes], where lanes 0 and 31 DUPLICATE the x-neighbours of the tile.  A warp row
+    // is therefore one aligned 128-byte line per plane and every table access of a thread is
+    // (one pointer) + (compile-time offset).  The kernel reads ONLY this table and p inside the PCG loop:
+    // no sincos, no 12-byte-strided AoS loads.  Planes: sa ca sb cb sg cg ux uy uz fit.
+    T* tab = nullptr;
+    static constexpr int NP = 10;
+    static constexpr bool HAS_PRECOMPUTE = true, HAS_CUSTOM_PRECOMPUTE = true;
+    static constexpr bool HAS_FAST_APPLY = true;
+    static constexpr int FTY = 8, FTZ = 1, FTX = 30, FNT = 32 * FTY * FTZ;
+    static constexpr int ZC = 32;                               // planes one warp marches through per work unit
+    static constexpr long REC = (long)NP * FNT;                 // elements per tile record
     void plan(const unsigned* d) { W = d[0]; H = d[1]; D = d[2]; }
+    __host__ __device__ int ntx() const { return (W + FTX - 1) / FTX; }
+    __host__ __device__ int nty() const { return (H + FTY - 1) / FTY; }
+    __host__ __device__ int ntz() const { return (D + FTZ - 1) / FTZ; }
+    void alloc_temporaries(cudaStream_t) {
+        OPTK_CUDA(cudaMalloc(&tab, (size_t)ntx() * nty() * ntz() * REC * sizeof(T)));
+    }
+    void free_temporaries() { cudaFree(tab); tab = nullptr; }
+    __device__ void precompute(int, int, int, long) const {}   // table is written by custom_precompute
+    void custom_precompute(cudaStream_t stream, int n_sm) const;
+    bool fast_ok() const { return getenv("OPTB200_GENERIC_JTJ") == nullptr; }
+    // a slab rank marches through its owned planes only
+    __host__ __device__ int z_lo() const { return this->o_lo; }
+    __host__ __device__ int z_hi() const { return this->o_hi < D ? this->o_hi : D; }
+    __host__ __device__ int nseg() const { return (z_hi() - z_lo() + ZC - 1) / ZC; }
+    long fast_tiles() const { return (long)ntx() * nty() * nseg(); }
+    dim3 fast_block() const { return dim3(32, FTY, FTZ); }
+    template <bool FUSED, bool LM> static auto fast_kernel();
     void bind(void** pp) {
         O = (T*)pp[0]; A = (T*)pp[1]; Ur = (const T*)pp[2]; Cn = (const T*)pp[3];
         w_fit = (T) * (const float*)pp[4]; w_reg = (T) * (const float*)pp[5];
@@ -136,5 +167,292 @@ struct VolumetricFunctor : FunctorDefaults<T> {
         return sum;
     }
 };
+
+
+// ---------------------------------------------------------------------------------------------
+// Marching J^T J apply for the 3-D ARAP energy.
+//
+// With M_a = sum_j pA_a[j] dR/da_j(A_a) (3x3, one per site) and u = U_i - U_n, the J p of the regularisation
+// residual centred at i toward n is  jp_in = (pO_i - pO_n) - M_i u, and
+//     Ap_O(i) = vf pO_i + w_r^2 sum_n (jp_in - jp_ni)
+//     Ap_A(i)[j] = -w_r^2 < dR/da_j(A_i), S_i >_F ,   S_i = sum_n jp_in u^T
+// (SURVEY.md App. D rearranged: D_in pA_i = -M_i u, D_ni pA_n = +M_n u).  A warp is one x-row of 32 sites (the
+// outer two lanes are halo lanes that only produce the jp toward the interior, so no lane diverges) and
+// marches through ZC consecutive z-planes.  jp_ni comes from the neighbour lane by shuffle along x, from the
+// thread's own previous / next step along z (registers), and is recomputed from the neighbour's table entry
+// along y.  No shared memory and no barrier: warps are independent and prefetch their next plane.  The
+// generic functor kernel needed 21 sincos and ~1850 instructions per site (profiles/r1_e); this needs none.
+template <class T>
+struct RotM {
+    T R[3][3], B[3][3];         // R = Rotate3D(a) (lib.t:84-98), B = dR/dbeta
+    __device__ __forceinline__ void set(const T* t) {   // t = sa ca sb cb sg cg
+        const T sa = t[0], ca = t[1], sb = t[2], cb = t[3], sg = t[4], cg = t[5];
+        const T cgsb = cg * sb, sgsb = sg * sb;
+        R[0][0] = cg * cb; R[0][1] = cgsb * sa - sg * ca; R[0][2] = cgsb * ca + sg * sa;
+        R[1][0] = sg * cb; R[1][1] = sgsb * sa + cg * ca; R[1][2] = sgsb * ca - cg * sa;
+        R[2][0] = -sb;     R[2][1] = cb * sa;             R[2][2] = cb * ca;
+        B[0][0] = -cgsb;   B[0][1] = R[0][0] * sa;        B[0][2] = R[0][0] * ca;
+        B[1][0] = -sgsb;   B[1][1] = R[1][0] * sa;        B[1][2] = R[1][0] * ca;
+        B[2][0] = -cb;     B[2][1] = -sb * sa;            B[2][2] = -sb * ca;
+    }
+    // M = pa dR/dalpha + pb dR/dbeta + pg dR/dgamma, with dR/dalpha = [0 | R[:,2] | -R[:,1]] and
+    // dR/dgamma = [-R[1,:]; R[0,:]; 0]
+    __device__ __forceinline__ void combine(T pa, T pb, T pg, T M[3][3]) const {
+        M[0][0] = pb * B[0][0] - pg * R[1][0];
+        M[0][1] = pa * R[0][2] + pb * B[0][1] - pg * R[1][1];
+        M[0][2] = pb * B[0][2] - pa * R[0][1] - pg * R[1][2];
+        M[1][0] = pb * B[1][0] + pg * R[0][0];
+        M[1][1] = pa * R[1][2] + pb * B[1][1] + pg * R[0][1];
+        M[1][2] = pb * B[1][2] - pa * R[1][1] + pg * R[0][2];
+        M[2][0] = pb * B[2][0];
+        M[2][1] = pa * R[2][2] + pb * B[2][1];
+        M[2][2] = pb * B[2][2] - pa * R[2][1];
+    }
+    // -< dR/da_j, S >_F for j = alpha, beta, gamma
+    __device__ __forceinline__ void project(const T S[3][3], T* o) const {
+        T a = T(0), b = T(0), g = T(0);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            a += R[k][2] * S[k][1] - R[k][1] * S[k][2];
+            b += B[k][0] * S[k][0] + B[k][1] * S[k][1] + B[k][2] * S[k][2];
+            g += R[0][k] * S[1][k] - R[1][k] * S[0][k];
+        }
+        o[0] = -a; o[1] = -b; o[2] = -g;
+    }
+};
+
+
+// Writes the tile-ordered table (same thread <-> site mapping as k_volumetric_apply; slots outside the
+// grid are zero-filled so that the apply kernel can read them unconditionally).
+template <class T>
+__global__ void __launch_bounds__(VolumetricFunctor<T>::FNT) k_volumetric_table(VolumetricFunctor<T> f) {
+    using F = VolumetricFunctor<T>;
+    constexpr int TX = F::FTX, TY = F::FTY, TZ = F::FTZ, NT = F::FNT;
+    const int W = f.W, H = f.H, D = f.D;
+    const int ntx = f.ntx(), nty = f.nty();
+    const int ntiles = ntx * nty * f.ntz();
+    const int lane = threadIdx.x, tid = linear_tid();
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int bx = tile % ntx, by = (tile / ntx) % nty, bz = tile / (ntx * nty);
+        const int x = bx * TX + lane - 1, y = by * TY + (int)threadIdx.y, z = bz * TZ + (int)threadIdx.z;
+        T v[F::NP];
+#pragma unroll
+        for (int k = 0; k < F::NP; ++k) v[k] = T(0);
+        if (x >= 0 && x < W && y < H && z < D) {
+            const long s = x + (long)W * (y + (long)H * z);
+            T a[3]; load3(f.A + s * 3, a); load3(f.Ur + s * 3, v + 6);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) sincos_t(a[k], v[2 * k], v[2 * k + 1]);
+            v[9] = f.Cn[s * 3] >= T(-999999.9) ? T(1) : T(0);
+        }
+        T* rec = f.tab + (long)tile * F::REC + tid;
+#pragma unroll
+        for (int k = 0; k < F::NP; ++k) rec[k * NT] = v[k];
+    }
+}
+template <class T> void VolumetricFunctor<T>::custom_precompute(cudaStream_t stream, int n_sm) const {
+    const long ntiles = (long)ntx() * nty() * ntz();
+    const unsigned grid = (unsigned)(ntiles < (long)n_sm * 4 ? ntiles : (long)n_sm * 4);
+    k_volumetric_table<T><<<grid, dim3(32, FTY, FTZ), 0, stream>>>(*this);
+}
+
+
+template <class T, bool FUSED, bool LM>
+__global__ void __launch_bounds__(VolumetricFunctor<T>::FNT, sizeof(T) == 4 ? 2 : 1)
+k_volumetric_apply(VolumetricFunctor<T> f, Vec<T> zv, Vec<T> p, Vec<T> p_new, Vec<T> out, Vec<T> CtC,
+                   const unsigned char* __restrict__, const double* bNum, const double* aNum, double* den,
+                   double* zero_a, double* zero_b) {
+    using F = VolumetricFunctor<T>;
+    constexpr int TX = F::FTX, TY = F::FTY, NT = F::FNT, ZC = F::ZC;
+    const int W = f.W, H = f.H, D = f.D;
+    const int sy = W;
+    const long sz = (long)W * H, pp = p.plane, op = out.plane;
+    const int zlo = f.z_lo(), zhi = f.z_hi();
+    const int ntx = f.ntx(), nty = f.nty();
+    const int nunits = ntx * nty * f.nseg();
+    const int lane = threadIdx.x, ty = threadIdx.y, tid = linear_tid();
+    const T wr2 = f.w_reg * f.w_reg, wf2 = f.w_fit * f.w_fit;
+    // table: record of (bx, by, z) = [plane][ty][lane]; the y neighbours are in this record or in the facing
+    // row of the adjacent one (warp-uniform choice), the z neighbours one z-stride away
+    const long rec_y = (long)ntx * F::REC, rec_z = (long)ntx * nty * F::REC;
+    const long oyp = ty + 1 < TY ? 32 : rec_y - (TY - 1) * 32, oym = ty > 0 ? -32 : -rec_y + (TY - 1) * 32;
+    if (blockIdx.x == 0 && tid == 0) {
+        if (zero_a) *zero_a = 0.0;
+        if (zero_b) *zero_b = 0.0;
+    }
+    double dot = 0.0;
+    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
+        const int bx = unit % ntx, by = (unit / ntx) % nty, seg = unit / (ntx * nty);
+        const int x = bx * TX + lane - 1, y = by * TY + ty;
+        const int z0 = zlo + seg * ZC, z1 = z0 + ZC < zhi ? z0 + ZC : zhi;
+        if (y >= H) continue;                                          // warp-uniform
+        const bool inside = x >= 0 && x < W;
+        const bool inner = inside && lane >= 1 && lane <= TX;          // not a halo lane
+        const bool hasR = inside && lane < 31 && x + 1 < W, hasL = inside && lane > 0 && x > 0;
+        const bool eyp = y + 1 < H, eym = y > 0;
+        long s = x + (long)sy * y + sz * z0;
+        const T* __restrict__ ts = f.tab + ((long)(z0 * nty + by) * ntx + bx) * F::REC + tid;
+        const T* __restrict__ ps = p.d + s;
+        // ---- prologue: centre data of plane z0; jp of the plane below toward it --------------------------
+        T tr[6], pc[6], uc[3], fit;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) { tr[k] = ts[k * NT]; pc[k] = inside ? ps[k * pp] : T(0); }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) uc[k] = ts[(6 + k) * NT];
+        fit = ts[9 * NT];
+        // state of the plane below (pending its jp from above): its UrShape, pO, accumulated Ap_O, fit flag,
+        // and jp_{below -> here}
+        T ucP[3] = {T(0), T(0), T(0)}, pOP[3] = {T(0), T(0), T(0)}, accP[3] = {T(0), T(0), T(0)}, fitP = T(0);
+        T jpP[3] = {T(0), T(0), T(0)};
+        bool havePrev = z0 > 0, writePrev = false;
+        if (havePrev) {
+            const T* __restrict__ tn = ts - rec_z;
+            const T* __restrict__ pn = ps - sz;
+            T t6[6], Mn[3][3];
+#pragma unroll
+            for (int k = 0; k < 6; ++k) t6[k] = tn[k * NT];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { ucP[k] = tn[(6 + k) * NT]; pOP[k] = inside ? pn[k * pp] : T(0); }
+            RotM<T> rn; rn.set(t6);
+            rn.combine(inside ? pn[3 * pp] : T(0), inside ? pn[4 * pp] : T(0), inside ? pn[5 * pp] : T(0), Mn);
+            T u[3] = {ucP[0] - uc[0], ucP[1] - uc[1], ucP[2] - uc[2]};
+#pragma unroll
+            for (int k = 0; k < 3; ++k) jpP[k] = (pOP[k] - pc[k]) - (Mn[k][0] * u[0] + Mn[k][1] * u[1] + Mn[k][2] * u[2]);
+        }
+        for (int z = z0; z <= z1; ++z) {
+            // at z == z1 only the jp toward the pending plane z1-1 is produced (nothing of plane z1 is written)
+            const bool last = z == z1;
+            if (last && z1 >= D) break;
+            const bool hasNext = !last && z + 1 < D;
+            // prefetch the centre data of the plane above
+            T trN[6], pcN[6], ucN[3], fitN = T(0);
+            if (hasNext) {
+                const T* __restrict__ tn = ts + rec_z;
+                const T* __restrict__ pn = ps + sz;
+#pragma unroll
+                for (int k = 0; k < 6; ++k) { trN[k] = tn[k * NT]; pcN[k] = inside ? pn[k * pp] : T(0); }
+#pragma unroll
+                for (int k = 0; k < 3; ++k) ucN[k] = tn[(6 + k) * NT];
+                fitN = tn[9 * NT];
+            }
+            RotM<T> rm; rm.set(tr);
+            T M[3][3]; rm.combine(pc[3], pc[4], pc[5], M);
+            T S[3][3] = {{T(0), T(0), T(0)}, {T(0), T(0), T(0)}, {T(0), T(0), T(0)}}, accO[3] = {T(0), T(0), T(0)};
+            auto edge = [&](const T* un, const T* pn, T* u, T* q, T* jp) {
+#pragma unroll
+                for (int k = 0; k < 3; ++k) { u[k] = uc[k] - un[k]; q[k] = pc[k] - pn[k]; }
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    jp[k] = q[k] - (M[k][0] * u[0] + M[k][1] * u[1] + M[k][2] * u[2]);
+                    accO[k] += jp[k];
+                    S[k][0] += jp[k] * u[0]; S[k][1] += jp[k] * u[1]; S[k][2] += jp[k] * u[2];
+                }
+            };
+            // ---- z-: toward the pending plane below; completes it --------------------------------------
+            if (havePrev) {
+                T u[3], q[3], jd[3];
+                edge(ucP, pOP, u, q, jd);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) accO[k] -= jpP[k];
+                if (writePrev && inner) {
+                    const long sp = s - sz;
+                    T dsum = T(0);
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) {
+                        T o = fitP * wf2 * pOP[k] + wr2 * (accP[k] - jd[k]);
+                        if (LM) o += CtC.d[k * CtC.plane + sp] * pOP[k];
+                        out.d[k * op + sp] = o;
+                        dsum += pOP[k] * o;
+                    }
+                    dot += (double)dsum;
+                }
+            }
+            if (last) break;
+            // ---- x: both directions through shuffles -------------------------------------------------
+            {
+                T unr[3], unl[3], pnr[3], pnl[3];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    unr[k] = __shfl_down_sync(0xffffffffu, uc[k], 1); unl[k] = __shfl_up_sync(0xffffffffu, uc[k], 1);
+                    pnr[k] = __shfl_down_sync(0xffffffffu, pc[k], 1); pnl[k] = __shfl_up_sync(0xffffffffu, pc[k], 1);
+                }
+                T u[3], q[3], jr[3] = {T(0), T(0), T(0)}, jl[3] = {T(0), T(0), T(0)};
+                if (hasR) edge(unr, pnr, u, q, jr);
+                if (hasL) edge(unl, pnl, u, q, jl);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const T fromR = __shfl_down_sync(0xffffffffu, jl[k], 1);   // the right neighbour's jp toward me
+                    const T fromL = __shfl_up_sync(0xffffffffu, jr[k], 1);
+                    if (hasR) accO[k] -= fromR;
+                    if (hasL) accO[k] -= fromL;
+                }
+            }
+            // ---- y: the neighbour's jp toward me is recomputed from its table entry --------------------
+            auto yside = [&](bool exists, long toff, long poff) {
+                if (inner && exists) {
+                    const T* __restrict__ tn = ts + toff;
+                    const T* __restrict__ pn_ = ps + poff;
+                    T un[3], pn[3], u[3], q[3], jp[3], t6[6], Mn[3][3];
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) { un[k] = tn[(6 + k) * NT]; pn[k] = pn_[k * pp]; }
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) t6[k] = tn[k * NT];
+                    edge(un, pn, u, q, jp);
+                    RotM<T> rn; rn.set(t6);
+                    rn.combine(pn_[3 * pp], pn_[4 * pp], pn_[5 * pp], Mn);
+#pragma unroll
+                    for (int k = 0; k < 3; ++k)                       // jp_ni = -q + M_n u
+                        accO[k] -= (Mn[k][0] * u[0] + Mn[k][1] * u[1] + Mn[k][2] * u[2]) - q[k];
+                }
+            };
+            yside(eyp, oyp, sy);
+            yside(eym, oym, -sy);
+            // ---- z+: toward the plane above (its jp toward me arrives in the next step) -----------------
+            T jn[3] = {T(0), T(0), T(0)};
+            if (hasNext) { T u[3], q[3]; edge(ucN, pcN, u, q, jn); }
+            // ---- the angle block of this plane is complete ------------------------------------------
+            if (inner) {
+                T oA[3];
+                rm.project(S, oA);
+                T dsum = T(0);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    T o = wr2 * oA[k];
+                    if (LM) o += CtC.d[(3 + k) * CtC.plane + s] * pc[3 + k];
+                    out.d[(3 + k) * op + s] = o;
+                    dsum += pc[3 + k] * o;
+                }
+                dot += (double)dsum;
+            }
+            // ---- shift: this plane becomes the pending one -------------------------------------------
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { ucP[k] = uc[k]; pOP[k] = pc[k]; accP[k] = accO[k]; uc[k] = ucN[k]; }
+            fitP = fit; fit = fitN;
+            // jp_{this -> above} as seen from above is "jp of the plane below toward it"
+#pragma unroll
+            for (int k = 0; k < 3; ++k) jpP[k] = jn[k];
+#pragma unroll
+            for (int k = 0; k < 6; ++k) { tr[k] = trN[k]; pc[k] = pcN[k]; }
+            havePrev = true; writePrev = true;
+            s += sz; ts += rec_z; ps += sz;
+        }
+        // the top plane of the grid has nothing above it
+        if (z1 >= D && writePrev && inner) {
+            const long sp = s - sz;
+            T dsum = T(0);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                T o = fitP * wf2 * pOP[k] + wr2 * accP[k];
+                if (LM) o += CtC.d[k * CtC.plane + sp] * pOP[k];
+                out.d[k * op + sp] = o;
+                dsum += pOP[k] * o;
+            }
+            dot += (double)dsum;
+        }
+    }
+    block_accumulate(dot, den);
+}
+
+template <class T> template <bool FUSED, bool LM> auto VolumetricFunctor<T>::fast_kernel() { return &k_volumetric_apply<T, FUSED, LM>; }
 
 }  // namespace optk

@@ -15,6 +15,8 @@ CASES = {
     "poisson_aligned": (examples.poisson_synthetic, (128, 64), dict(n_iter=1, l_iter=20)),
     "image_warping": (examples.image_warping_synthetic, (61, 47), dict(n_iter=3, l_iter=10)),
     "volumetric": (examples.volumetric_synthetic, (11, 9, 7), dict(n_iter=3, l_iter=10)),
+    # several 30x4x4 (fp32) / 30x4x2 (fp64) tiles of the tiled J^T J kernel per dimension, ragged edges
+    "volumetric_tiles": (examples.volumetric_synthetic, (67, 10, 9), dict(n_iter=2, l_iter=8)),
     "optical_flow": (examples.optical_flow_synthetic, (53, 38), dict(n_iter=3, l_iter=10)),
     "arap": (examples.arap_synthetic, (13, 11), dict(n_iter=3, l_iter=10)),
 }
@@ -66,6 +68,25 @@ def test_jtf_and_jtj_match_oracle(built, case, double):
     ap_gpu = sol.debug_apply_jtj(named, p)
     ap_ref = o.apply_jtj(pr.params, p)
     assert np.abs(ap_gpu - ap_ref).max() <= tol * np.abs(ap_ref).max()
+
+
+@pytest.mark.parametrize("double", [False, True])
+def test_volumetric_tiled_jtj_equals_generic(built, double, monkeypatch):
+    """The tiled kernel (precomputed trig table, shared-memory exchange of J p) against the generic
+    one-thread-per-site functor kernel: two different derivations of the same operator."""
+    from opt_b200 import solver as S
+    pr = make("volumetric_tiles", double=double)
+    named = S.upload(pr)
+    dt = np.float64 if double else np.float32
+    rng = np.random.default_rng(11)
+    N = int(np.prod(pr.dims))
+    p = rng.standard_normal((N, 6)).astype(dt)
+    sol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=double)
+    fast = sol.debug_apply_jtj(named, p)
+    monkeypatch.setenv("OPTB200_GENERIC_JTJ", "1")
+    generic = sol.debug_apply_jtj(named, p)
+    assert not np.array_equal(fast, generic)          # really two code paths
+    assert np.abs(fast - generic).max() <= OP_RTOL[double] * np.abs(generic).max()
 
 
 GOLDEN = [("image_warping_cat512.npz", examples.image_warping_golden),
