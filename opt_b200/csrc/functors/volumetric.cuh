@@ -180,8 +180,10 @@ struct VolumetricFunctor : FunctorDefaults<T> {
 // outer two lanes are halo lanes that only produce the jp toward the interior, so no lane diverges) and
 // marches through ZC consecutive z-planes.  jp_ni comes from the neighbour lane by shuffle along x, from the
 // thread's own previous / next step along z (registers), and is recomputed from the neighbour's table entry
-// along y.  No shared memory and no barrier: warps are independent and prefetch their next plane.  The
-// generic functor kernel needed 21 sincos and ~1850 instructions per site (profiles/r1_e); this needs none.
+// along y.  No shared memory and no barrier: warps are independent and prefetch their next plane (a variant
+// that exchanged the y direction through shared memory executed 23 % fewer instructions but was slower: the
+// per-plane barrier put every warp's loads in lockstep, profiles/r1_e).  The generic functor kernel needed
+// 21 sincos and ~1850 instructions per site; this needs no sincos and ~40 % of the instructions.
 template <class T>
 struct RotM {
     T R[3][3], B[3][3];         // R = Rotate3D(a) (lib.t:84-98), B = dR/dbeta
@@ -257,6 +259,17 @@ template <class T> void VolumetricFunctor<T>::custom_precompute(cudaStream_t str
 }
 
 
+
+__device__ __forceinline__ float nfma(float a, float b, float c) { return fmaf(-a, b, c); }     // c - a b
+__device__ __forceinline__ double nfma(double a, double b, double c) { return fma(-a, b, c); }
+
+template <class T>
+struct VolSite {                 // what a thread keeps of one plane while it is the next / current / pending one
+    T tr[6], pc[6], uc[3], fit;  // table entry and direction p
+    T acc[3];                    // sum_n (jp_in - jp_ni) collected so far
+    T jn[3];                     // jp toward the plane above
+};
+
 template <class T, bool FUSED, bool LM>
 __global__ void __launch_bounds__(VolumetricFunctor<T>::FNT, sizeof(T) == 4 ? 2 : 1)
 k_volumetric_apply(VolumetricFunctor<T> f, Vec<T> zv, Vec<T> p, Vec<T> p_new, Vec<T> out, Vec<T> CtC,
@@ -275,7 +288,8 @@ k_volumetric_apply(VolumetricFunctor<T> f, Vec<T> zv, Vec<T> p, Vec<T> p_new, Ve
     // table: record of (bx, by, z) = [plane][ty][lane]; the y neighbours are in this record or in the facing
     // row of the adjacent one (warp-uniform choice), the z neighbours one z-stride away
     const long rec_y = (long)ntx * F::REC, rec_z = (long)ntx * nty * F::REC;
-    const long oyp = ty + 1 < TY ? 32 : rec_y - (TY - 1) * 32, oym = ty > 0 ? -32 : -rec_y + (TY - 1) * 32;
+    const bool typ = ty + 1 < TY, tym = ty > 0;
+    const long oyp = typ ? 32 : rec_y - (TY - 1) * 32, oym = tym ? -32 : -rec_y + (TY - 1) * 32;
     if (blockIdx.x == 0 && tid == 0) {
         if (zero_a) *zero_a = 0.0;
         if (zero_b) *zero_b = 0.0;
@@ -285,96 +299,79 @@ k_volumetric_apply(VolumetricFunctor<T> f, Vec<T> zv, Vec<T> p, Vec<T> p_new, Ve
         const int bx = unit % ntx, by = (unit / ntx) % nty, seg = unit / (ntx * nty);
         const int x = bx * TX + lane - 1, y = by * TY + ty;
         const int z0 = zlo + seg * ZC, z1 = z0 + ZC < zhi ? z0 + ZC : zhi;
-        if (y >= H) continue;                                          // warp-uniform
-        const bool inside = x >= 0 && x < W;
+        const bool inside = x >= 0 && x < W && y < H;
         const bool inner = inside && lane >= 1 && lane <= TX;          // not a halo lane
         const bool hasR = inside && lane < 31 && x + 1 < W, hasL = inside && lane > 0 && x > 0;
-        const bool eyp = y + 1 < H, eym = y > 0;
+        const bool eyp = inner && y + 1 < H, eym = inner && y > 0;
         long s = x + (long)sy * y + sz * z0;
         const T* __restrict__ ts = f.tab + ((long)(z0 * nty + by) * ntx + bx) * F::REC + tid;
         const T* __restrict__ ps = p.d + s;
-        // ---- prologue: centre data of plane z0; jp of the plane below toward it --------------------------
-        T tr[6], pc[6], uc[3], fit;
-#pragma unroll
-        for (int k = 0; k < 6; ++k) { tr[k] = ts[k * NT]; pc[k] = inside ? ps[k * pp] : T(0); }
-#pragma unroll
-        for (int k = 0; k < 3; ++k) uc[k] = ts[(6 + k) * NT];
-        fit = ts[9 * NT];
-        // state of the plane below (pending its jp from above): its UrShape, pO, accumulated Ap_O, fit flag,
-        // and jp_{below -> here}
-        T ucP[3] = {T(0), T(0), T(0)}, pOP[3] = {T(0), T(0), T(0)}, accP[3] = {T(0), T(0), T(0)}, fitP = T(0);
-        T jpP[3] = {T(0), T(0), T(0)};
         bool havePrev = z0 > 0, writePrev = false;
-        if (havePrev) {
-            const T* __restrict__ tn = ts - rec_z;
-            const T* __restrict__ pn = ps - sz;
-            T t6[6], Mn[3][3];
+
+        auto load_site = [&](VolSite<T>& c, const T* __restrict__ tn, const T* __restrict__ pn) {
 #pragma unroll
-            for (int k = 0; k < 6; ++k) t6[k] = tn[k * NT];
+            for (int k = 0; k < 6; ++k) { c.tr[k] = tn[k * NT]; c.pc[k] = inside ? pn[k * pp] : T(0); }
 #pragma unroll
-            for (int k = 0; k < 3; ++k) { ucP[k] = tn[(6 + k) * NT]; pOP[k] = inside ? pn[k * pp] : T(0); }
-            RotM<T> rn; rn.set(t6);
-            rn.combine(inside ? pn[3 * pp] : T(0), inside ? pn[4 * pp] : T(0), inside ? pn[5 * pp] : T(0), Mn);
-            T u[3] = {ucP[0] - uc[0], ucP[1] - uc[1], ucP[2] - uc[2]};
+            for (int k = 0; k < 3; ++k) c.uc[k] = tn[(6 + k) * NT];
+            c.fit = tn[9 * NT];
+        };
+        // Ap_O of a completed plane (all six jp_in and jp_ni collected in acc)
+        auto write_O = [&](const VolSite<T>& c, const T* acc, long sp) {
+            T dsum = T(0);
 #pragma unroll
-            for (int k = 0; k < 3; ++k) jpP[k] = (pOP[k] - pc[k]) - (Mn[k][0] * u[0] + Mn[k][1] * u[1] + Mn[k][2] * u[2]);
-        }
-        for (int z = z0; z <= z1; ++z) {
-            // at z == z1 only the jp toward the pending plane z1-1 is produced (nothing of plane z1 is written)
-            const bool last = z == z1;
-            if (last && z1 >= D) break;
-            const bool hasNext = !last && z + 1 < D;
-            // prefetch the centre data of the plane above
-            T trN[6], pcN[6], ucN[3], fitN = T(0);
-            if (hasNext) {
-                const T* __restrict__ tn = ts + rec_z;
-                const T* __restrict__ pn = ps + sz;
-#pragma unroll
-                for (int k = 0; k < 6; ++k) { trN[k] = tn[k * NT]; pcN[k] = inside ? pn[k * pp] : T(0); }
-#pragma unroll
-                for (int k = 0; k < 3; ++k) ucN[k] = tn[(6 + k) * NT];
-                fitN = tn[9 * NT];
+            for (int k = 0; k < 3; ++k) {
+                T o = (c.fit * wf2) * c.pc[k] + wr2 * acc[k];
+                if (LM) o += CtC.d[k * CtC.plane + sp] * c.pc[k];
+                out.d[k * op + sp] = o;
+                dsum += c.pc[k] * o;
             }
-            RotM<T> rm; rm.set(tr);
-            T M[3][3]; rm.combine(pc[3], pc[4], pc[5], M);
-            T S[3][3] = {{T(0), T(0), T(0)}, {T(0), T(0), T(0)}, {T(0), T(0), T(0)}}, accO[3] = {T(0), T(0), T(0)};
+            dot += (double)dsum;
+        };
+        // one plane: P = pending plane below, C = this plane, N = plane above (filled here).  Returns false
+        // after the step that only completes the pending plane.
+        auto step = [&](VolSite<T>& P, VolSite<T>& C, VolSite<T>& N, int z) -> bool {
+            const bool last = z == z1;
+            if (last && z1 >= D) {                                    // top plane of the grid: nothing above it
+                if (writePrev && inner) write_O(P, P.acc, s - sz);
+                return false;
+            }
+            const bool hasNext = !last && z + 1 < D;
+            if (hasNext) load_site(N, ts + rec_z, ps + sz);           // prefetch the plane above
+            RotM<T> rm; rm.set(C.tr);
+            T M[3][3]; rm.combine(C.pc[3], C.pc[4], C.pc[5], M);
+            T S[3][3] = {{T(0), T(0), T(0)}, {T(0), T(0), T(0)}, {T(0), T(0), T(0)}};
+#pragma unroll
+            for (int k = 0; k < 3; ++k) C.acc[k] = T(0);
+            // jp of the residual centred here toward a neighbour with UrShape un and direction pn
             auto edge = [&](const T* un, const T* pn, T* u, T* q, T* jp) {
 #pragma unroll
-                for (int k = 0; k < 3; ++k) { u[k] = uc[k] - un[k]; q[k] = pc[k] - pn[k]; }
+                for (int k = 0; k < 3; ++k) { u[k] = C.uc[k] - un[k]; q[k] = C.pc[k] - pn[k]; }
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
-                    jp[k] = q[k] - (M[k][0] * u[0] + M[k][1] * u[1] + M[k][2] * u[2]);
-                    accO[k] += jp[k];
-                    S[k][0] += jp[k] * u[0]; S[k][1] += jp[k] * u[1]; S[k][2] += jp[k] * u[2];
+                    jp[k] = nfma(M[k][0], u[0], nfma(M[k][1], u[1], nfma(M[k][2], u[2], q[k])));
+                    C.acc[k] += jp[k];
+                    S[k][0] = fma(jp[k], u[0], S[k][0]); S[k][1] = fma(jp[k], u[1], S[k][1]); S[k][2] = fma(jp[k], u[2], S[k][2]);
                 }
             };
             // ---- z-: toward the pending plane below; completes it --------------------------------------
             if (havePrev) {
                 T u[3], q[3], jd[3];
-                edge(ucP, pOP, u, q, jd);
+                edge(P.uc, P.pc, u, q, jd);
 #pragma unroll
-                for (int k = 0; k < 3; ++k) accO[k] -= jpP[k];
+                for (int k = 0; k < 3; ++k) C.acc[k] -= P.jn[k];
                 if (writePrev && inner) {
-                    const long sp = s - sz;
-                    T dsum = T(0);
-#pragma unroll
-                    for (int k = 0; k < 3; ++k) {
-                        T o = fitP * wf2 * pOP[k] + wr2 * (accP[k] - jd[k]);
-                        if (LM) o += CtC.d[k * CtC.plane + sp] * pOP[k];
-                        out.d[k * op + sp] = o;
-                        dsum += pOP[k] * o;
-                    }
-                    dot += (double)dsum;
+                    T a[3] = {P.acc[0] - jd[0], P.acc[1] - jd[1], P.acc[2] - jd[2]};
+                    write_O(P, a, s - sz);
                 }
             }
-            if (last) break;
+            if (last) return false;
             // ---- x: both directions through shuffles -------------------------------------------------
             {
                 T unr[3], unl[3], pnr[3], pnl[3];
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
-                    unr[k] = __shfl_down_sync(0xffffffffu, uc[k], 1); unl[k] = __shfl_up_sync(0xffffffffu, uc[k], 1);
-                    pnr[k] = __shfl_down_sync(0xffffffffu, pc[k], 1); pnl[k] = __shfl_up_sync(0xffffffffu, pc[k], 1);
+                    unr[k] = __shfl_down_sync(0xffffffffu, C.uc[k], 1); unl[k] = __shfl_up_sync(0xffffffffu, C.uc[k], 1);
+                    pnr[k] = __shfl_down_sync(0xffffffffu, C.pc[k], 1); pnl[k] = __shfl_up_sync(0xffffffffu, C.pc[k], 1);
                 }
                 T u[3], q[3], jr[3] = {T(0), T(0), T(0)}, jl[3] = {T(0), T(0), T(0)};
                 if (hasR) edge(unr, pnr, u, q, jr);
@@ -383,33 +380,38 @@ k_volumetric_apply(VolumetricFunctor<T> f, Vec<T> zv, Vec<T> p, Vec<T> p_new, Ve
                 for (int k = 0; k < 3; ++k) {
                     const T fromR = __shfl_down_sync(0xffffffffu, jl[k], 1);   // the right neighbour's jp toward me
                     const T fromL = __shfl_up_sync(0xffffffffu, jr[k], 1);
-                    if (hasR) accO[k] -= fromR;
-                    if (hasL) accO[k] -= fromL;
+                    if (hasR) C.acc[k] -= fromR;
+                    if (hasL) C.acc[k] -= fromL;
                 }
             }
-            // ---- y: the neighbour's jp toward me is recomputed from its table entry --------------------
+            // ---- y: own jp into the exchange slot; a neighbour row of another CTA is recomputed ----------
             auto yside = [&](bool exists, long toff, long poff) {
-                if (inner && exists) {
+                if (exists) {
+                    T jp[3];
                     const T* __restrict__ tn = ts + toff;
                     const T* __restrict__ pn_ = ps + poff;
-                    T un[3], pn[3], u[3], q[3], jp[3], t6[6], Mn[3][3];
+                    T un[3], pn[3], u[3], q[3];
 #pragma unroll
                     for (int k = 0; k < 3; ++k) { un[k] = tn[(6 + k) * NT]; pn[k] = pn_[k * pp]; }
-#pragma unroll
-                    for (int k = 0; k < 6; ++k) t6[k] = tn[k * NT];
                     edge(un, pn, u, q, jp);
-                    RotM<T> rn; rn.set(t6);
-                    rn.combine(pn_[3 * pp], pn_[4 * pp], pn_[5 * pp], Mn);
+                    {
+                        T t6[6], Mn[3][3];
 #pragma unroll
-                    for (int k = 0; k < 3; ++k)                       // jp_ni = -q + M_n u
-                        accO[k] -= (Mn[k][0] * u[0] + Mn[k][1] * u[1] + Mn[k][2] * u[2]) - q[k];
+                        for (int k = 0; k < 6; ++k) t6[k] = tn[k * NT];
+                        RotM<T> rn; rn.set(t6);
+                        rn.combine(pn_[3 * pp], pn_[4 * pp], pn_[5 * pp], Mn);
+#pragma unroll
+                        for (int k = 0; k < 3; ++k)                   // acc -= jp_ni, jp_ni = M_n u - q
+                            C.acc[k] = nfma(Mn[k][0], u[0], nfma(Mn[k][1], u[1], nfma(Mn[k][2], u[2], C.acc[k] + q[k])));
+                    }
                 }
             };
             yside(eyp, oyp, sy);
             yside(eym, oym, -sy);
             // ---- z+: toward the plane above (its jp toward me arrives in the next step) -----------------
-            T jn[3] = {T(0), T(0), T(0)};
-            if (hasNext) { T u[3], q[3]; edge(ucN, pcN, u, q, jn); }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) C.jn[k] = T(0);
+            if (hasNext) { T u[3], q[3]; edge(N.uc, N.pc, u, q, C.jn); }
             // ---- the angle block of this plane is complete ------------------------------------------
             if (inner) {
                 T oA[3];
@@ -418,36 +420,32 @@ k_volumetric_apply(VolumetricFunctor<T> f, Vec<T> zv, Vec<T> p, Vec<T> p_new, Ve
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
                     T o = wr2 * oA[k];
-                    if (LM) o += CtC.d[(3 + k) * CtC.plane + s] * pc[3 + k];
+                    if (LM) o += CtC.d[(3 + k) * CtC.plane + s] * C.pc[3 + k];
                     out.d[(3 + k) * op + s] = o;
-                    dsum += pc[3 + k] * o;
+                    dsum += C.pc[3 + k] * o;
                 }
                 dot += (double)dsum;
             }
-            // ---- shift: this plane becomes the pending one -------------------------------------------
-#pragma unroll
-            for (int k = 0; k < 3; ++k) { ucP[k] = uc[k]; pOP[k] = pc[k]; accP[k] = accO[k]; uc[k] = ucN[k]; }
-            fitP = fit; fit = fitN;
-            // jp_{this -> above} as seen from above is "jp of the plane below toward it"
-#pragma unroll
-            for (int k = 0; k < 3; ++k) jpP[k] = jn[k];
-#pragma unroll
-            for (int k = 0; k < 6; ++k) { tr[k] = trN[k]; pc[k] = pcN[k]; }
             havePrev = true; writePrev = true;
             s += sz; ts += rec_z; ps += sz;
-        }
-        // the top plane of the grid has nothing above it
-        if (z1 >= D && writePrev && inner) {
-            const long sp = s - sz;
-            T dsum = T(0);
+            return true;
+        };
+
+        VolSite<T> A, B, C;
+        load_site(A, ts, ps);
+        if (havePrev) {                                               // jp of the plane below toward plane z0
+            load_site(C, ts - rec_z, ps - sz);
+            RotM<T> rn; rn.set(C.tr);
+            T Mn[3][3]; rn.combine(C.pc[3], C.pc[4], C.pc[5], Mn);
+            const T u[3] = {C.uc[0] - A.uc[0], C.uc[1] - A.uc[1], C.uc[2] - A.uc[2]};
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                T o = fitP * wf2 * pOP[k] + wr2 * accP[k];
-                if (LM) o += CtC.d[k * CtC.plane + sp] * pOP[k];
-                out.d[k * op + sp] = o;
-                dsum += pOP[k] * o;
-            }
-            dot += (double)dsum;
+            for (int k = 0; k < 3; ++k)
+                C.jn[k] = nfma(Mn[k][0], u[0], nfma(Mn[k][1], u[1], nfma(Mn[k][2], u[2], C.pc[k] - A.pc[k])));
+        }
+        for (int z = z0;; z += 3) {                                   // roles rotate: no register shuffling
+            if (!step(C, A, B, z)) break;
+            if (!step(A, B, C, z + 1)) break;
+            if (!step(B, C, A, z + 2)) break;
         }
     }
     block_accumulate(dot, den);
