@@ -15,6 +15,7 @@
 #include <string>
 #include <vector>
 #include <nccl.h>
+#include <cub/device/device_radix_sort.cuh>
 #include "common.cuh"
 #include "optk.h"
 
@@ -451,6 +452,52 @@ __global__ void k_graph_ctc(F f, long E, Vec<typename F::Scalar> CtC, typename F
     if (e < E) f.graphCtC(e, CtC, inv_radius);
 }
 
+// ------------------------------------------------------------------------------ graph terms as a gather
+// Instead of one global atomicAdd per edge and channel (the reference, o.t:2586-2600), J^T J p over the
+// graph domain is gathered per vertex: at Init the engine sorts every (edge, slot) incidence by
+// (vertex, slot) -- a segmented, deterministic adjacency -- and a functor with HAS_GATHER then evaluates,
+// for its own vertex, the contribution of every incident edge.  No atomics, no memset of Ap, Ap is written
+// once, and alphaDen = <p, Ap> comes out of the same kernel.
+template <class F>
+__global__ void k_incidence_keys(F f, long n, unsigned* keys, unsigned* vals) {
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long e = i / F::GV; const int slot = (int)(i % F::GV);
+    keys[i] = (unsigned)f.graph_vertex(e, slot) * F::GV + slot;
+    vals[i] = f.incidence_payload(e, slot);
+}
+// off[k] = first position whose key is >= k, for k in [0, nkeys]
+static __global__ void k_incidence_offsets(const unsigned* __restrict__ keys, long n, long nkeys, int* off) {
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (i > n) return;
+    const long lo = i == 0 ? 0 : (long)keys[i - 1] + 1;
+    const long hi = i == n ? nkeys : (long)keys[i];
+    for (long k = lo; k <= hi; ++k) off[k] = (int)i;
+}
+template <class F, bool LM>
+__global__ void __launch_bounds__(128) k_gather_jtj(F f, long N, const int* __restrict__ off, const unsigned* __restrict__ inc,
+                                                    Vec<typename F::Scalar> dir, Vec<typename F::Scalar> out,
+                                                    Vec<typename F::Scalar> CtC, double* den, double* zero_slot) {
+    using T = typename F::Scalar;
+    constexpr int U = F::U;
+    double acc = 0.0;
+    if (zero_slot && blockIdx.x == 0 && threadIdx.x == 0) *zero_slot = 0.0;
+    for (long v = blockIdx.x * (long)blockDim.x + threadIdx.x; v < N; v += (long)gridDim.x * blockDim.x) {
+        T o[U];
+        f.gatherJTJ(v, off + v * F::GV, inc, dir, o);
+        T dsum = T(0);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const T pv = dir(u, v);
+            if (LM) o[u] += CtC(u, v) * pv;
+            out(u, v) = o[u];
+            dsum += pv * o[u];
+        }
+        acc += (double)dsum;
+    }
+    block_accumulate(acc, den);
+}
+
 // ------------------------------------------------------------------------------ flat streaming kernels
 // PCGStep2 (solver:665-731): alpha = aNum/aDen; delta += alpha p; r -= alpha Ap; z = M^-1 r;
 // betaNum += z.r ; LM: q += 0.5 delta.(r+b).   One 128-bit vector per thread and array.
@@ -614,6 +661,10 @@ struct Engine : OptK_Plan {
     Vec<T> delta, r, b, Adelta, z, p, Ap, CtC, pre, SSq, prevX;
     Vec<T> p_alt;                                           // second p buffer of the fused Step3+Step1 kernel
     unsigned char* active4 = nullptr;                       // 1 flag per 4 sites (HAS_EXCLUDE functors only)
+    unsigned* inc = nullptr;                                // HAS_GATHER: incidence payloads sorted by (vertex, slot)
+    int* inc_off = nullptr;                                 //             N*GV + 1 segment offsets
+    void* sort_tmp = nullptr; size_t sort_tmp_bytes = 0;
+    unsigned *key_a = nullptr, *key_b = nullptr, *val_a = nullptr;
     bool fuse = true;                                       // fused PCGStep3+PCGStep1 (single rank)
     double* scal = nullptr;
     double* h_scal = nullptr;    // pinned
@@ -645,7 +696,7 @@ struct Engine : OptK_Plan {
             OPTK_CUDA(cudaMalloc(&active4, Npad / 4));
             OPTK_CUDA(cudaMemsetAsync(active4, 0, Npad / 4, stream));
         }
-        if (getenv("OPTB200_NO_FUSE") || !F::FUSE_STEP3) fuse = false;
+        if (getenv("OPTB200_NO_FUSE") || !F::FUSE_STEP3 || use_gather()) fuse = false;
         OPTK_CUDA(cudaMalloc(&scal, S_COUNT * sizeof(double)));
         OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
         OPTK_CUDA(cudaMallocHost(&h_scal, S_COUNT * sizeof(double)));
@@ -664,6 +715,7 @@ struct Engine : OptK_Plan {
         f.free_temporaries();
         if (comm) ncclCommDestroy(comm);
         cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFree(active4);
+        cudaFree(inc); cudaFree(inc_off); cudaFree(sort_tmp); cudaFree(key_a); cudaFree(key_b); cudaFree(val_a);
         base_destroy();
     }
     int unknown_channels() const override { return U; }
@@ -730,6 +782,33 @@ struct Engine : OptK_Plan {
         return h_scal[0];
     }
 
+    // (vertex, slot)-sorted incidence lists of the graph (HAS_GATHER functors); rebuilt at the first
+    // nonlinear iteration of every solve because the index arrays belong to the caller
+    void build_incidence() {
+        if constexpr (F::HAS_GATHER) {
+            const long n = E * F::GV, nkeys = N * F::GV;
+            if (!inc) {
+                OPTK_CUDA(cudaMalloc(&inc, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
+                OPTK_CUDA(cudaMalloc(&inc_off, (size_t)(nkeys + 1) * sizeof(int)));
+                OPTK_CUDA(cudaMalloc(&key_a, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
+                OPTK_CUDA(cudaMalloc(&key_b, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
+                OPTK_CUDA(cudaMalloc(&val_a, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
+                cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp_bytes, key_a, key_b, val_a, inc, (int)n);
+                OPTK_CUDA(cudaMalloc(&sort_tmp, sort_tmp_bytes));
+            }
+            int bits = 1;
+            while ((1L << bits) < nkeys) ++bits;
+            if (n > 0) {
+                this->launch("graphIncidenceKeys", dim3((unsigned)((n + 255) / 256)), dim3(256), k_incidence_keys<F>, f, n, key_a, val_a);
+                this->pre_launch("graphIncidenceSort");
+                cub::DeviceRadixSort::SortPairs(sort_tmp, sort_tmp_bytes, key_a, key_b, val_a, inc, (int)n, 0, bits, stream);
+                this->post_launch();
+            }
+            this->launch("graphIncidenceOffsets", dim3((unsigned)((n + 1 + 255) / 256)), dim3(256), k_incidence_offsets, (const unsigned*)key_b, n, nkeys, inc_off);
+        }
+    }
+    bool use_gather() const { return F::HAS_GATHER && getenv("OPTB200_GRAPH_ATOMICS") == nullptr; }
+
     void precompute() override {
         if constexpr (F::HAS_CUSTOM_PRECOMPUTE) {           // functor owns a table in its own layout
             this->pre_launch("precompute");
@@ -756,6 +835,7 @@ struct Engine : OptK_Plan {
 
     void pcg_begin(int nIter) override {
         OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
+        if (nIter == 0 && use_gather()) build_incidence();
         if (F::HAS_EXCLUDE)                                 // Exclude() may read inputs the caller changed
             this->launch("activeGroups", dim3((unsigned)((Npad / 4 + 255) / 256)), dim3(256), k_active4<F>, f, Npad / 4, active4);
         this->launch_tiles("PCGInit1", tg.n, sblock, k_pcg_init1<F>, f, tg, delta, r, p, pre, S(S_RZ0));
@@ -778,6 +858,14 @@ struct Engine : OptK_Plan {
     }
 
     void apply_A(const char* name, const char* gname, Vec<T> dir, Vec<T> out, double* den, double* zero_slot) {
+        if constexpr (F::HAS_GATHER) {
+            if (use_gather()) {
+                const long nb = (N + 127) / 128;
+                if (lm) this->launch_tiles(name, nb, dim3(128), k_gather_jtj<F, true>, f, N, (const int*)inc_off, (const unsigned*)inc, dir, out, CtC, den, zero_slot);
+                else    this->launch_tiles(name, nb, dim3(128), k_gather_jtj<F, false>, f, N, (const int*)inc_off, (const unsigned*)inc, dir, out, CtC, den, zero_slot);
+                return;
+            }
+        }
         if constexpr (F::HAS_FAST_APPLY) {
             if (f.fast_ok()) {
                 if (lm) this->launch_tiles(name, f.fast_tiles(), f.fast_block(), F::template fast_kernel<false, true>(), f, dir, dir, dir, out, CtC, (const unsigned char*)active4, (const double*)nullptr, (const double*)nullptr, den, zero_slot, (double*)nullptr);
@@ -875,6 +963,7 @@ struct Engine : OptK_Plan {
         OPTK_CUDA(cudaMemcpy(p.d, tmp.data(), tmp.size() * sizeof(T), cudaMemcpyHostToDevice));
         OPTK_CUDA(cudaMemsetAsync(Ap.d, 0, tmp.size() * sizeof(T), stream));
         bool saved = lm; lm = false;
+        if (use_gather()) build_incidence();
         if (F::HAS_EXCLUDE)
             this->launch("activeGroups", dim3((unsigned)((Npad / 4 + 255) / 256)), dim3(256), k_active4<F>, f, Npad / 4, active4);
         apply_A("PCGStep1", "PCGStep1_Graph", p, Ap, S(S_DUMMY), nullptr);
@@ -890,6 +979,7 @@ struct FunctorDefaults {
     static constexpr bool HAS_CUSTOM_PRECOMPUTE = false; // precompute is a functor-launched kernel (own table layout)
     static constexpr bool HAS_EXCLUDE = false;           // functors with an Exclude() override this
     static constexpr bool HAS_FAST_APPLY = false;        // functors with a specialised J^T J kernel override this
+    static constexpr bool HAS_GATHER = false;            // graph functors with a per-vertex gather form of J^T J p
     static constexpr bool FUSE_STEP3 = true;             // form p' = z + beta p inside the J^T J kernel (engine.cuh, FusedDir)
     bool fast_ok() const { return false; }
     static constexpr int GV = 0;

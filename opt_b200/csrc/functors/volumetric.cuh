@@ -184,46 +184,6 @@ struct VolumetricFunctor : FunctorDefaults<T> {
 // that exchanged the y direction through shared memory executed 23 % fewer instructions but was slower: the
 // per-plane barrier put every warp's loads in lockstep, profiles/r1_e).  The generic functor kernel needed
 // 21 sincos and ~1850 instructions per site; this needs no sincos and ~40 % of the instructions.
-template <class T>
-struct RotM {
-    T R[3][3], B[3][3];         // R = Rotate3D(a) (lib.t:84-98), B = dR/dbeta
-    __device__ __forceinline__ void set(const T* t) {   // t = sa ca sb cb sg cg
-        const T sa = t[0], ca = t[1], sb = t[2], cb = t[3], sg = t[4], cg = t[5];
-        const T cgsb = cg * sb, sgsb = sg * sb;
-        R[0][0] = cg * cb; R[0][1] = cgsb * sa - sg * ca; R[0][2] = cgsb * ca + sg * sa;
-        R[1][0] = sg * cb; R[1][1] = sgsb * sa + cg * ca; R[1][2] = sgsb * ca - cg * sa;
-        R[2][0] = -sb;     R[2][1] = cb * sa;             R[2][2] = cb * ca;
-        B[0][0] = -cgsb;   B[0][1] = R[0][0] * sa;        B[0][2] = R[0][0] * ca;
-        B[1][0] = -sgsb;   B[1][1] = R[1][0] * sa;        B[1][2] = R[1][0] * ca;
-        B[2][0] = -cb;     B[2][1] = -sb * sa;            B[2][2] = -sb * ca;
-    }
-    // M = pa dR/dalpha + pb dR/dbeta + pg dR/dgamma, with dR/dalpha = [0 | R[:,2] | -R[:,1]] and
-    // dR/dgamma = [-R[1,:]; R[0,:]; 0]
-    __device__ __forceinline__ void combine(T pa, T pb, T pg, T M[3][3]) const {
-        M[0][0] = pb * B[0][0] - pg * R[1][0];
-        M[0][1] = pa * R[0][2] + pb * B[0][1] - pg * R[1][1];
-        M[0][2] = pb * B[0][2] - pa * R[0][1] - pg * R[1][2];
-        M[1][0] = pb * B[1][0] + pg * R[0][0];
-        M[1][1] = pa * R[1][2] + pb * B[1][1] + pg * R[0][1];
-        M[1][2] = pb * B[1][2] - pa * R[1][1] + pg * R[0][2];
-        M[2][0] = pb * B[2][0];
-        M[2][1] = pa * R[2][2] + pb * B[2][1];
-        M[2][2] = pb * B[2][2] - pa * R[2][1];
-    }
-    // -< dR/da_j, S >_F for j = alpha, beta, gamma
-    __device__ __forceinline__ void project(const T S[3][3], T* o) const {
-        T a = T(0), b = T(0), g = T(0);
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            a += R[k][2] * S[k][1] - R[k][1] * S[k][2];
-            b += B[k][0] * S[k][0] + B[k][1] * S[k][1] + B[k][2] * S[k][2];
-            g += R[0][k] * S[1][k] - R[1][k] * S[0][k];
-        }
-        o[0] = -a; o[1] = -b; o[2] = -g;
-    }
-};
-
-
 // Writes the tile-ordered table (same thread <-> site mapping as k_volumetric_apply; slots outside the
 // grid are zero-filled so that the apply kernel can read them unconditionally).
 template <class T>
@@ -260,8 +220,6 @@ template <class T> void VolumetricFunctor<T>::custom_precompute(cudaStream_t str
 
 
 
-__device__ __forceinline__ float nfma(float a, float b, float c) { return fmaf(-a, b, c); }     // c - a b
-__device__ __forceinline__ double nfma(double a, double b, double c) { return fma(-a, b, c); }
 
 template <class T>
 struct VolSite {                 // what a thread keeps of one plane while it is the next / current / pending one
