@@ -50,6 +50,9 @@ WORKLOADS = {
     "optical_flow_2048": dict(builder=examples.optical_flow_synthetic, args=(2048, 2048), kw=dict(n_iter=10, l_iter=50),
                               U=2, ijtj=4, iexcl=0, extra=0, mask=None,
                               desc="optical_flow 2048x2048, GN 10x50 PCG, fp32"),
+    "sfs_2048": dict(builder=examples.sfs_synthetic, args=(2048, 2048), kw=dict(n_iter=10, l_iter=10, holes=False),
+                     U=1, ijtj=5.5, iexcl=1, extra=0, mask=None,
+                     desc="shape_from_shading 2048x2048, GN 10x10 PCG, fp32"),
     "volumetric_512": dict(builder=examples.volumetric_synthetic, args=(512, 512, 512), kw=dict(n_iter=2, l_iter=20),
                            U=6, ijtj=9, iexcl=0, extra=0, mask=None,
                            desc="volumetric_mesh_deformation 512^3, GN 2x20 PCG, fp32"),

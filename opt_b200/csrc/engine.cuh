@@ -730,7 +730,7 @@ struct Engine : OptK_Plan {
 
     // ---- multi-GPU: ownership, scalar all-reduce, halo exchange ---------------------------------
     int set_slab(int rk, int nr, int h, const void* uid) override {
-        if (F::ND < 2 || GRAPH) { fprintf(stderr, "Opt: slab decomposition is only available for 2-D/3-D grid problems\n"); return -1; }
+        if (F::ND < 2 || GRAPH || !F::SLAB_OK) { fprintf(stderr, "Opt: slab decomposition is not available for this energy\n"); return -1; }
         const int L = F::ND == 3 ? f.D : f.H;
         rank = rk; nranks = nr; halo = h;
         if (nranks > 1) fuse = false;                       // ghost rows of p are refreshed after PCGStep3
@@ -979,6 +979,7 @@ struct FunctorDefaults {
     static constexpr bool HAS_CUSTOM_PRECOMPUTE = false; // precompute is a functor-launched kernel (own table layout)
     static constexpr bool HAS_EXCLUDE = false;           // functors with an Exclude() override this
     static constexpr bool HAS_FAST_APPLY = false;        // functors with a specialised J^T J kernel override this
+    static constexpr bool SLAB_OK = true;                // grid functors whose bounds predicates survive a slab cut
     static constexpr bool HAS_GATHER = false;            // graph functors with a per-vertex gather form of J^T J p
     static constexpr bool FUSE_STEP3 = true;             // form p' = z + beta p inside the J^T J kernel (engine.cuh, FusedDir)
     bool fast_ok() const { return false; }

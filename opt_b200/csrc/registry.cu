@@ -10,6 +10,7 @@ OPTK_DECL(image_warping)
 OPTK_DECL(volumetric_mesh_deformation)
 OPTK_DECL(optical_flow)
 OPTK_DECL(arap_mesh_deformation)
+OPTK_DECL(shape_from_shading)
 #undef OPTK_DECL
 }
 
@@ -21,6 +22,7 @@ const Entry kTable[] = {
     {"volumetric_mesh_deformation", optk_make_volumetric_mesh_deformation},
     {"optical_flow", optk_make_optical_flow},
     {"arap_mesh_deformation", optk_make_arap_mesh_deformation},
+    {"shape_from_shading", optk_make_shape_from_shading},
 };
 const Entry* find(const char* energy) {
     for (const Entry& e : kTable) if (!strcmp(e.name, energy)) return &e;

@@ -213,6 +213,37 @@ def optical_flow_synthetic(W, H, seed=1234, n_iter=3, l_iter=20, kind="gaussNewt
                    {"nIterations": n_iter, "lIterations": l_iter}, kind=kind)
 
 
+# lighting coefficients / intrinsics of examples/data/shape_from_shading/default.SFSSolverParameters
+# (layout: shape_from_shading/src/TerraSolverParameters.h:7-31)
+SFS_L = [0.6908317804336548, 0.044598858803510666, 0.01812959648668766, -0.1773163229227066, -0.04067882522940636,
+         0.14467650651931763, 0.02393525093793869, -0.24658696353435516, 0.005797004792839289]
+
+
+def sfs_synthetic(W, H, seed=1234, n_iter=3, l_iter=10, kind="gaussNewtonGPU", holes=True):
+    """shape_from_shading: D_i = 1 + smooth field, X = D_i + small noise, Im = smooth
+    intensity in [0,1], uint8 edge masks, pinhole intrinsics scaled from the 640x480 default
+    (f = 0.897 W, principal point at the image centre), weights w_p, w_s, w_g = 100, 100, 1 and lighting from
+    default.SFSSolverParameters.  `holes` punches invalid-depth pixels (D_i <= 0 -> Exclude)."""
+    rng = np.random.default_rng(seed)
+    f32 = np.float32
+    ys, xs = np.mgrid[0:H, 0:W].astype(np.float64)
+    smooth = np.sin(2 * np.pi * (0.7 * xs / W + 0.2)) * np.cos(2 * np.pi * (0.6 * ys / H))
+    D = (1.0 + 0.03 * smooth).astype(f32)
+    if holes:
+        k = max(1, (W * H) // 200)
+        D.reshape(-1)[rng.choice(W * H, k, replace=False)] = 0.0
+        D[H // 3:H // 3 + 2, W // 4:W // 4 + 3] = -1.0
+    X = (D + 0.002 * rng.standard_normal((H, W))).astype(f32)
+    Im = (0.5 + 0.3 * np.cos(2 * np.pi * (0.9 * xs / W)) * np.sin(2 * np.pi * (0.8 * ys / H + 0.1))
+          + 0.01 * rng.standard_normal((H, W))).astype(f32)
+    mR = (rng.random((H, W)) > 0.1).astype(np.uint8)
+    mC = (rng.random((H, W)) > 0.1).astype(np.uint8)
+    fx = f32(574.0528564453125 / 640.0 * W)
+    scal = [f32(100.0), f32(100.0), f32(1.0), fx, fx, f32(W / 2), f32(H / 2)] + [f32(v) for v in SFS_L]
+    return Problem("shape_from_shading.t", [W, H], scal + [X, D, Im, mR, mC], [16],
+                   {"nIterations": n_iter, "lIterations": l_iter}, kind=kind)
+
+
 def grid_mesh_edges(nx, ny):
     """Directed edges of a regular height-field triangulation, both directions of every mesh
     edge, sorted by head vertex (the order examples/shared/OptGraph.h:78-89 produces)."""

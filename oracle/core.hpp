@@ -56,6 +56,7 @@ struct SpecBase {
 template <class T, class S> struct Seeder;
 template <class T> struct Seeder<T, T> {
     static T make(T v, int, T) { return v; }
+    static void add(T&, int, T, T) {}
 };
 template <class T, int N> struct Seeder<T, Dual<T, N>> {
     // tangent slot `slot` (or -1) gets 1; the last tangent carries the direction (J*dir)
@@ -64,6 +65,11 @@ template <class T, int N> struct Seeder<T, Dual<T, N>> {
         if (slot >= 0) r.d[slot] = T(1);
         r.d[N - 1] = dirv;
         return r;
+    }
+    // chain rule through a stored gradient image: d/d(unknown in `slot`) += g, J*dir += g * dir(unknown)
+    static void add(Dual<T, N>& r, int slot, T g, T dirv) {
+        if (slot >= 0) r.d[slot] += g;
+        r.d[N - 1] += g * dirv;
     }
 };
 
@@ -100,6 +106,19 @@ struct CenterCtx {
         int x = cx + ox, y = cy + oy;
         if (!dir || !sp.inside(x, y, cz)) return T(0);
         return dir[sp.lin(x, y, cz) * Spec::U + sp.img[im].uoff + ch];
+    }
+    // ComputedArray access (o.t:1551-1563): the value image at (ox,oy) [0 out of bounds], differentiated through
+    // its stored gradient images: image j holds d value / d X_{im,ch}(. + goff[j]) (ImageAccess:gradient)
+    S computed(const T* val, int ng, const T* const* grad, const int (*goff)[2], int im, int ch, int ox, int oy) const {
+        int x = cx + ox, y = cy + oy;
+        if (!sp.inside(x, y, cz)) return S(T(0));
+        long q = sp.lin(x, y, cz);
+        S r(val[q]);
+        for (int j = 0; j < ng; ++j) {
+            int ux = ox + goff[j][0], uy = oy + goff[j][1];
+            Seeder<T, S>::add(r, slot_of(im, ch, ux, uy), grad[j][q], dir_of(im, ch, ux, uy));
+        }
+        return r;
     }
     template <class A>
     A arr(const A* p, int nch, int ch, int ox = 0, int oy = 0, int oz = 0) const {

@@ -246,7 +246,10 @@ struct ArapMeshDeformation : SpecBase<T> {
 
 }  // namespace oracle
 
+#include "energies_sfs.hpp"
+
 #define ORACLE_ENERGY_LIST(X)      \
+    X(oracle::ShapeFromShading)    \
     X(oracle::PoissonImageEditing) \
     X(oracle::ImageWarping)        \
     X(oracle::VolumetricMeshDeformation) \

@@ -75,3 +75,38 @@ def test_oracle_jtj_is_symmetric_psd(built):
     Ap, Aq = s.apply_jtj(pr.params, p), s.apply_jtj(pr.params, q)
     assert abs(q @ Ap - p @ Aq) < 1e-9 * abs(q @ Ap)
     assert p @ Ap >= 0
+
+
+def test_oracle_sfs_jtf_is_gradient_of_cost(built):
+    """shape_from_shading has no golden in the reference (test_final_cost.py:63 holds -1), so the oracle's
+    ComputedArray machinery (value + gradient images, o.t:1686-1719) is pinned by a property instead: with fresh
+    gradient images, -r = J^T F must be the central finite-difference gradient of the oracle's own cost."""
+    pr = examples.sfs_synthetic(24, 18).as_double()
+    s = OracleSolver(pr.dims, pr.energy, double=True, threads=2)
+    r, _ = s.eval_jtf(pr.params, np.float64)
+    X, D = pr.params[16], pr.params[17]
+    W = pr.dims[0]
+    h = 1e-6
+    checked = 0
+    for (y, x) in [(5, 7), (9, 12), (3, 3), (10, 20), (16, 22), (1, 1), (8, 8), (0, 5), (17, 23)]:
+        if D[y, x] <= 0:
+            continue
+        X[y, x] += h
+        cp = s.init(pr.params)
+        X[y, x] -= 2 * h
+        cm = s.init(pr.params)
+        X[y, x] += h
+        fd = (cp - cm) / (2 * h)
+        assert abs(fd + r[y * W + x]) <= 1e-6 * max(1.0, abs(fd)), (x, y, fd, r[y * W + x])
+        checked += 1
+    assert checked >= 6
+
+
+@pytest.mark.parametrize("kind", ["gaussNewtonGPU", "LMGPU"])
+def test_oracle_sfs_converges(built, kind):
+    pr = examples.sfs_synthetic(24, 18).as_double()
+    s = OracleSolver(pr.dims, pr.energy, kind, double=True, threads=2)
+    s.set_params(nIterations=5, lIterations=10)
+    s.solve(pr.params)
+    h = s.cost_history()
+    assert h[-1] < 0.7 * h[0] and all(b <= a * (1 + 1e-12) for a, b in zip(h, h[1:])), h

@@ -19,6 +19,7 @@ CASES = {
     "volumetric_tiles": (examples.volumetric_synthetic, (67, 10, 9), dict(n_iter=2, l_iter=8)),
     "optical_flow": (examples.optical_flow_synthetic, (53, 38), dict(n_iter=3, l_iter=10)),
     "arap": (examples.arap_synthetic, (13, 11), dict(n_iter=3, l_iter=10)),
+    "sfs": (examples.sfs_synthetic, (45, 37), dict(n_iter=3, l_iter=10)),
 }
 
 
