@@ -11,6 +11,8 @@ OPTK_DECL(volumetric_mesh_deformation)
 OPTK_DECL(optical_flow)
 OPTK_DECL(arap_mesh_deformation)
 OPTK_DECL(shape_from_shading)
+OPTK_DECL(embedded_mesh_deformation)
+OPTK_DECL(cotangent_mesh_smoothing)
 #undef OPTK_DECL
 }
 
@@ -23,6 +25,8 @@ const Entry kTable[] = {
     {"optical_flow", optk_make_optical_flow},
     {"arap_mesh_deformation", optk_make_arap_mesh_deformation},
     {"shape_from_shading", optk_make_shape_from_shading},
+    {"embedded_mesh_deformation", optk_make_embedded_mesh_deformation},
+    {"cotangent_mesh_smoothing", optk_make_cotangent_mesh_smoothing},
 };
 const Entry* find(const char* energy) {
     for (const Entry& e : kTable) if (!strcmp(e.name, energy)) return &e;

@@ -213,6 +213,60 @@ def optical_flow_synthetic(W, H, seed=1234, n_iter=3, l_iter=20, kind="gaussNewt
                    {"nIterations": n_iter, "lIterations": l_iter}, kind=kind)
 
 
+def grid_mesh_rings(nx, ny):
+    """(head, tail, prev, next) of every directed edge of the height-field triangulation, neighbours of a vertex in
+    counter-clockwise ring order and prev/next taken cyclically in that ring
+    (cotangent_mesh_smoothing/src/CombinedSolver.h:66-120)."""
+    ring = [(1, 0), (1, 1), (0, 1), (-1, 0), (-1, -1), (0, -1)]
+    head, tail, prev, nxt = [], [], [], []
+    for y in range(ny):
+        for x in range(nx):
+            nb = [(x + dx) + nx * (y + dy) for dx, dy in ring if 0 <= x + dx < nx and 0 <= y + dy < ny]
+            n = len(nb)
+            for i in range(n):
+                head.append(x + nx * y); tail.append(nb[i]); prev.append(nb[(i + n - 1) % n]); nxt.append(nb[(i + 1) % n])
+    return [np.array(a, dtype=np.int32) for a in (head, tail, prev, nxt)]
+
+
+def cotangent_synthetic(nx, ny, seed=1234, n_iter=3, l_iter=10):
+    """cotangent_mesh_smoothing on a noisy height-field mesh: X = A = noisy positions (driver: both the input mesh,
+    CombinedSolver.h:128-150), weights sqrt(1), sqrt(0.5) (main.cpp:62-63)."""
+    rng = np.random.default_rng(seed)
+    f32 = np.float32
+    ys, xs = np.mgrid[0:ny, 0:nx]
+    z = 0.1 * np.sin(6.0 * xs / nx) * np.cos(5.0 * ys / ny)
+    pos = np.stack([xs / max(nx, ny), ys / max(nx, ny), z], -1).reshape(-1, 3)
+    A = (pos + 0.01 * rng.standard_normal(pos.shape)).astype(f32)
+    X = (A + 0.002 * rng.standard_normal(pos.shape)).astype(f32)
+    g = grid_mesh_rings(nx, ny)
+    ecount = np.array([len(g[0])], dtype=np.int32)
+    return Problem("cotangent_mesh_smoothing.t", [nx * ny, len(g[0])],
+                   [np.sqrt(f32(1.0)), np.sqrt(f32(0.5)), X, A, ecount] + g, [2],
+                   {"nIterations": n_iter, "lIterations": l_iter})
+
+
+def embedded_synthetic(nx, ny, seed=1234, n_iter=3, l_iter=10):
+    """embedded_mesh_deformation on a height-field mesh: Offset = UrShape + noise, RotMatrix = identity + noise
+    (driver: identity, embedded_mesh_deformation/src/CombinedSolver.h:117-131), a few vertices constrained, weights
+    sqrt(3), sqrt(12), sqrt(5) (:36-45)."""
+    rng = np.random.default_rng(seed)
+    f32 = np.float32
+    ys, xs = np.mgrid[0:ny, 0:nx]
+    z = 0.1 * np.sin(6.0 * xs / nx) * np.cos(5.0 * ys / ny)
+    ur = np.stack([xs / max(nx, ny), ys / max(nx, ny), z], -1).reshape(-1, 3).astype(f32)
+    n = nx * ny
+    v0, v1 = grid_mesh_edges(nx, ny)
+    cons = np.full((n, 3), -np.inf, dtype=f32)
+    pick = rng.choice(n, max(4, n // 50), replace=False)
+    cons[pick] = ur[pick] + (0.05 * rng.standard_normal((len(pick), 3))).astype(f32)
+    offset = (ur + 0.01 * rng.standard_normal((n, 3))).astype(f32)
+    rot = (np.tile(np.eye(3, dtype=f32).reshape(1, 9), (n, 1)) + 0.05 * rng.standard_normal((n, 9))).astype(f32)
+    ecount = np.array([len(v0)], dtype=np.int32)
+    return Problem("embedded_mesh_deformation.t", [n, len(v0)],
+                   [np.sqrt(f32(3.0)), np.sqrt(f32(12.0)), np.sqrt(f32(5.0)), offset, rot, ur, cons, ecount, v0, v1], [3, 4],
+                   {"nIterations": n_iter, "lIterations": l_iter})
+
+
 # lighting coefficients / intrinsics of examples/data/shape_from_shading/default.SFSSolverParameters
 # (layout: shape_from_shading/src/TerraSolverParameters.h:7-31)
 SFS_L = [0.6908317804336548, 0.044598858803510666, 0.01812959648668766, -0.1773163229227066, -0.04067882522940636,

@@ -247,9 +247,12 @@ struct ArapMeshDeformation : SpecBase<T> {
 }  // namespace oracle
 
 #include "energies_sfs.hpp"
+#include "energies_mesh.hpp"
 
 #define ORACLE_ENERGY_LIST(X)      \
     X(oracle::ShapeFromShading)    \
+    X(oracle::EmbeddedMeshDeformation) \
+    X(oracle::CotangentMeshSmoothing) \
     X(oracle::PoissonImageEditing) \
     X(oracle::ImageWarping)        \
     X(oracle::VolumetricMeshDeformation) \

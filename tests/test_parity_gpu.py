@@ -20,6 +20,8 @@ CASES = {
     "optical_flow": (examples.optical_flow_synthetic, (53, 38), dict(n_iter=3, l_iter=10)),
     "arap": (examples.arap_synthetic, (13, 11), dict(n_iter=3, l_iter=10)),
     "sfs": (examples.sfs_synthetic, (45, 37), dict(n_iter=3, l_iter=10)),
+    "embedded": (examples.embedded_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
+    "cotangent": (examples.cotangent_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
 }
 
 
@@ -62,6 +64,10 @@ def test_jtf_and_jtj_match_oracle(built, case, double):
     r_gpu, pre_gpu = sol.debug_read("r"), sol.debug_read("pre")
     r_ref, pre_ref = o.eval_jtf(pr.params, dt)
     tol = OP_RTOL[double]
+    if case == "cotangent" and not double:
+        # disc = (a.a)(b.b) - (a.b)^2 of the wrapped boundary rings is a catastrophic cancellation in fp32 (nearly
+        # collinear unit vectors): closed form and dual numbers round differently there; fp64 agrees to 1e-12
+        tol = 5e-4
     assert np.abs(r_gpu - r_ref).max() <= tol * np.abs(r_ref).max()
     assert np.abs(pre_gpu - pre_ref).max() <= tol * np.abs(pre_ref).max()
     rng = np.random.default_rng(7)
