@@ -13,6 +13,7 @@ OPTK_DECL(arap_mesh_deformation)
 OPTK_DECL(shape_from_shading)
 OPTK_DECL(embedded_mesh_deformation)
 OPTK_DECL(cotangent_mesh_smoothing)
+OPTK_DECL(robust_nonrigid_alignment)
 #undef OPTK_DECL
 }
 
@@ -27,6 +28,7 @@ const Entry kTable[] = {
     {"shape_from_shading", optk_make_shape_from_shading},
     {"embedded_mesh_deformation", optk_make_embedded_mesh_deformation},
     {"cotangent_mesh_smoothing", optk_make_cotangent_mesh_smoothing},
+    {"robust_nonrigid_alignment", optk_make_robust_nonrigid_alignment},
 };
 const Entry* find(const char* energy) {
     for (const Entry& e : kTable) if (!strcmp(e.name, energy)) return &e;

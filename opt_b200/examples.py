@@ -245,6 +245,32 @@ def cotangent_synthetic(nx, ny, seed=1234, n_iter=3, l_iter=10):
                    {"nIterations": n_iter, "lIterations": l_iter})
 
 
+def robust_synthetic(nx, ny, seed=1234, n_iter=3, l_iter=10, kind="LMGPU"):
+    """robust_nonrigid_alignment on a height-field mesh: point-to-plane constraints on a tenth of the vertices
+    (target = displaced position, unit normal), RobustWeights = 1 (CombinedSolver.h:343), Angle = 0, weights
+    sqrt(10), sqrt(64) (:158-169); the driver uses LM."""
+    rng = np.random.default_rng(seed)
+    f32 = np.float32
+    ys, xs = np.mgrid[0:ny, 0:nx]
+    z = 0.1 * np.sin(6.0 * xs / nx) * np.cos(5.0 * ys / ny)
+    ur = np.stack([xs / max(nx, ny), ys / max(nx, ny), z], -1).reshape(-1, 3).astype(f32)
+    n = nx * ny
+    v0, v1 = grid_mesh_edges(nx, ny)
+    cons = np.full((n, 3), -np.inf, dtype=f32)
+    nrm = np.zeros((n, 3), dtype=f32)
+    pick = rng.choice(n, max(4, n // 10), replace=False)
+    cons[pick] = ur[pick] + (0.05 * rng.standard_normal((len(pick), 3))).astype(f32)
+    d = rng.standard_normal((len(pick), 3)) + np.array([0, 0, 3.0])
+    nrm[pick] = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(f32)
+    offset = (ur + 0.005 * rng.standard_normal((n, 3))).astype(f32)
+    angle = (0.02 * rng.standard_normal((n, 3))).astype(f32)
+    rw = np.ones((n,), dtype=f32)
+    ecount = np.array([len(v0)], dtype=np.int32)
+    return Problem("robust_nonrigid_alignment.t", [n, len(v0)],
+                   [np.sqrt(f32(10.0)), np.sqrt(f32(64.0)), offset, angle, rw, ur, cons, nrm, ecount, v0, v1], [2, 3, 4],
+                   {"nIterations": n_iter, "lIterations": l_iter}, kind=kind)
+
+
 def embedded_synthetic(nx, ny, seed=1234, n_iter=3, l_iter=10):
     """embedded_mesh_deformation on a height-field mesh: Offset = UrShape + noise, RotMatrix = identity + noise
     (driver: identity, embedded_mesh_deformation/src/CombinedSolver.h:117-131), a few vertices constrained, weights

@@ -253,6 +253,7 @@ struct ArapMeshDeformation : SpecBase<T> {
     X(oracle::ShapeFromShading)    \
     X(oracle::EmbeddedMeshDeformation) \
     X(oracle::CotangentMeshSmoothing) \
+    X(oracle::RobustNonrigidAlignment) \
     X(oracle::PoissonImageEditing) \
     X(oracle::ImageWarping)        \
     X(oracle::VolumetricMeshDeformation) \

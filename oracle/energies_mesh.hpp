@@ -99,4 +99,50 @@ struct CotangentMeshSmoothing : SpecBase<T> {
     void precompute_all(int) {}
 };
 
+// ------------------------------------------------------------------------------------------
+// examples/robust_nonrigid_alignment/robust_nonrigid_alignment.t:1-30.  greatereq(Constraints(0), -999999.9) compares a
+// 3-vector: ad broadcasts (ad.t:373-395), so the fit and the confidence term are THREE residuals each.
+template <class T>
+struct RobustNonrigidAlignment : SpecBase<T> {
+    using Scalar = T;
+    static constexpr int U = 7, NT = 2, RMAX = 3, GV = 2, NGT = 1;
+    static constexpr bool USE_PRE = true;
+    static const char* name() { return "robust_nonrigid_alignment"; }
+    const T *Ur = nullptr, *Cn = nullptr, *Nn = nullptr;
+    T w_fit = 0, w_reg = 0;
+    void plan(const unsigned* d) { this->dim[0] = d[0]; this->N = d[0]; this->E = d[1]; }
+    void bind(void** pp) {
+        w_fit = (T) * (const float*)pp[0]; w_reg = (T) * (const float*)pp[1];
+        this->nimg = 0; this->add_unknown(pp[2], 3); this->add_unknown(pp[3], 3); this->add_unknown(pp[4], 1);
+        Ur = (const T*)pp[5]; Cn = (const T*)pp[6]; Nn = (const T*)pp[7];
+        this->gidx[0] = (const int*)pp[9]; this->gidx[1] = (const int*)pp[10];  // pp[8] = edge count, ignored (util.t:696)
+    }
+    bool exclude(int, int, int) const { return false; }
+    static int offsets(int, const int (**o)[3]) { ORACLE_OFFS({0, 0, 0}) }
+    template <class S, class C> int residual(int k, C& c, S* r) const {
+        S w = c.unk(2, 0);
+        if (k == 0) {
+            S e_fit = w * (c.arr(Nn, 3, 0) * (c.unk(0, 0) - c.arr(Cn, 3, 0)) + c.arr(Nn, 3, 1) * (c.unk(0, 1) - c.arr(Cn, 3, 1)) +
+                           c.arr(Nn, 3, 2) * (c.unk(0, 2) - c.arr(Cn, 3, 2)));
+            for (int ch = 0; ch < 3; ++ch) r[ch] = w_fit * select(c.arr(Cn, 3, ch) >= T(-999999.9), e_fit, S(T(0)));
+            return 3;
+        }
+        S e_conf = T(1) - (w * w);
+        for (int ch = 0; ch < 3; ++ch) r[ch] = T(0.1) * select(c.arr(Cn, 3, ch) >= T(-999999.9), e_conf, S(T(0)));
+        return 3;
+    }
+    template <class S, class G> int gresidual(int, G& g, S* r) const {
+        Vec<S, 3> dO, dU, A;
+        for (int ch = 0; ch < 3; ++ch) {
+            dO[ch] = g.unk(0, ch, 0) - g.unk(0, ch, 1);
+            dU[ch] = S(g.arr(Ur, 3, ch, 0) - g.arr(Ur, 3, ch, 1));
+            A[ch] = g.unk(1, ch, 0);
+        }
+        Vec<S, 3> e = dO - rotate3d(A, dU);
+        for (int ch = 0; ch < 3; ++ch) r[ch] = w_reg * e[ch];
+        return 3;
+    }
+    void precompute_all(int) {}
+};
+
 }  // namespace oracle

@@ -22,6 +22,7 @@ CASES = {
     "sfs": (examples.sfs_synthetic, (45, 37), dict(n_iter=3, l_iter=10)),
     "embedded": (examples.embedded_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
     "cotangent": (examples.cotangent_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
+    "robust": (examples.robust_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
 }
 
 
