@@ -14,6 +14,7 @@ OPTK_DECL(shape_from_shading)
 OPTK_DECL(embedded_mesh_deformation)
 OPTK_DECL(cotangent_mesh_smoothing)
 OPTK_DECL(robust_nonrigid_alignment)
+OPTK_DECL(intrinsic_image_decomposition)
 #undef OPTK_DECL
 }
 
@@ -29,6 +30,7 @@ const Entry kTable[] = {
     {"embedded_mesh_deformation", optk_make_embedded_mesh_deformation},
     {"cotangent_mesh_smoothing", optk_make_cotangent_mesh_smoothing},
     {"robust_nonrigid_alignment", optk_make_robust_nonrigid_alignment},
+    {"intrinsic_image_decomposition", optk_make_intrinsic_image_decomposition},
 };
 const Entry* find(const char* energy) {
     for (const Entry& e : kTable) if (!strcmp(e.name, energy)) return &e;

@@ -21,11 +21,12 @@ class Problem:
     solver: dict = field(default_factory=dict)   # solver parameters (nIterations, lIterations, ...)
     kind: str = "gaussNewtonGPU"
     double: bool = False
+    opt_float_scalars: list = field(default_factory=list)   # indices of Param(..., opt_float, ...) scalars
 
     def clone(self):
         return Problem(self.energy, list(self.dims),
                        [p.copy() if isinstance(p, np.ndarray) else p for p in self.params],
-                       list(self.unknowns), dict(self.solver), self.kind, self.double)
+                       list(self.unknowns), dict(self.solver), self.kind, self.double, list(self.opt_float_scalars))
 
     def as_double(self):
         """opt_float images become double; Param(float) scalars and index/uint8 arrays stay
@@ -34,6 +35,8 @@ class Problem:
         q.double = True
         q.params = [p.astype(np.float64) if isinstance(p, np.ndarray) and p.dtype == np.float32 else p
                     for p in q.params]
+        for i in q.opt_float_scalars:
+            q.params[i] = np.float64(q.params[i])
         return q
 
 
@@ -322,6 +325,24 @@ def sfs_synthetic(W, H, seed=1234, n_iter=3, l_iter=10, kind="gaussNewtonGPU", h
     scal = [f32(100.0), f32(100.0), f32(1.0), fx, fx, f32(W / 2), f32(H / 2)] + [f32(v) for v in SFS_L]
     return Problem("shape_from_shading.t", [W, H], scal + [X, D, Im, mR, mC], [16],
                    {"nIterations": n_iter, "lIterations": l_iter}, kind=kind)
+
+
+def intrinsic_synthetic(W, H, seed=1234, n_iter=3, l_iter=10, kind="gaussNewtonGPU"):
+    """intrinsic_image_decomposition: i = log of a piecewise-constant albedo times a smooth shading field, r = i,
+    s = 0 like the driver's start (src/CombinedSolver.h:60-88), weights sqrt(500), sqrt(1000), sqrt(10000) and
+    pNorm = 0.8 (:33-46; pNorm is an opt_float Param, intrinsic_image_decomposition.t:5)."""
+    rng = np.random.default_rng(seed)
+    f32 = np.float32
+    ys, xs = np.mgrid[0:H, 0:W].astype(np.float64)
+    blocks = rng.random((H // 8 + 1, W // 8 + 1, 3))
+    albedo = 0.2 + 0.7 * blocks[(ys // 8).astype(int), (xs // 8).astype(int)]
+    shading = 0.6 + 0.3 * np.sin(2 * np.pi * (0.8 * xs / W + 0.1)) * np.cos(2 * np.pi * 0.7 * ys / H)
+    img = np.log(albedo * shading[..., None] * (1.0 + 0.01 * rng.standard_normal((H, W, 3)))).astype(f32)
+    r = (img + 0.01 * rng.standard_normal((H, W, 3))).astype(f32)
+    s = (0.01 * rng.standard_normal((H, W))).astype(f32)
+    w = [np.sqrt(f32(500.0)), np.sqrt(f32(1000.0)), np.sqrt(f32(10000.0))]
+    return Problem("intrinsic_image_decomposition.t", [W, H], w + [f32(0.8), r, img, s], [4, 6],
+                   {"nIterations": n_iter, "lIterations": l_iter}, kind=kind, opt_float_scalars=[3])
 
 
 def grid_mesh_edges(nx, ny):

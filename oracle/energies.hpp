@@ -254,6 +254,7 @@ struct ArapMeshDeformation : SpecBase<T> {
     X(oracle::EmbeddedMeshDeformation) \
     X(oracle::CotangentMeshSmoothing) \
     X(oracle::RobustNonrigidAlignment) \
+    X(oracle::IntrinsicImageDecomposition) \
     X(oracle::PoissonImageEditing) \
     X(oracle::ImageWarping)        \
     X(oracle::VolumetricMeshDeformation) \

@@ -112,4 +112,65 @@ struct ShapeFromShading : SpecBase<T>, CenteredOnly<T> {
     }
 };
 
+// ------------------------------------------------------------------------------------------
+// examples/intrinsic_image_decomposition/intrinsic_image_decomposition.t:1-32.  L_p (lib.t:112-121) stores
+// sqrt(pow(|r_const(0,0) - r_const(x,y)| + 1e-7, pNorm - 2)) in one ComputedArray per stencil offset; r_const is the
+// SAME buffer as the unknown r (both parameter 4) read as a plain Array, so the weights carry no derivative and
+// are refreshed by every precompute (o.t:3131-3153).  No UsePreconditioner() call: off.  pNorm is an opt_float Param.
+template <class T>
+struct IntrinsicImageDecomposition : SpecBase<T>, CenteredOnly<T> {
+    using Scalar = T;
+    static constexpr int U = 4, NT = 9, RMAX = 3;
+    static constexpr bool USE_PRE = false;
+    static const char* name() { return "intrinsic_image_decomposition"; }
+    T w_fit = 0, w_alb = 0, w_shd = 0, pnorm = 0;
+    const T *rc = nullptr, *im = nullptr;
+    std::vector<T> Lp[4];
+    void plan(const unsigned* d) { this->dim[0] = d[0]; this->dim[1] = d[1]; this->N = (long)d[0] * d[1]; }
+    void bind(void** pp) {
+        w_fit = (T) * (const float*)pp[0]; w_alb = (T) * (const float*)pp[1]; w_shd = (T) * (const float*)pp[2];
+        pnorm = *(const T*)pp[3];
+        this->nimg = 0; this->add_unknown(pp[4], 3); this->add_unknown(pp[6], 1);
+        rc = (const T*)pp[4]; im = (const T*)pp[5];
+    }
+    bool exclude(int, int, int) const { return false; }
+    static int offsets(int k, const int (**o)[3]) {
+        static const int tab[5][2][3] = {{{0, 0, 0}, {1, 0, 0}}, {{0, 0, 0}, {-1, 0, 0}}, {{0, 0, 0}, {0, 1, 0}}, {{0, 0, 0}, {0, -1, 0}}, {{0, 0, 0}, {0, 0, 0}}};
+        *o = tab[k < 8 ? k % 4 : 4]; return k < 8 ? 2 : 1;
+    }
+    T rget(int x, int y, int ch) const { return this->inside(x, y, 0) ? rc[this->lin(x, y, 0) * 3 + ch] : T(0); }
+    void precompute_all(int threads) {
+        const int W = this->dim[0], H = this->dim[1];
+        for (auto& v : Lp) v.assign(this->N, T(0));
+#pragma omp parallel for num_threads(threads) schedule(static)
+        for (int j = 0; j < H; ++j)
+            for (int i = 0; i < W; ++i)
+                for (int k = 0; k < 4; ++k) {
+                    T d[3];
+                    for (int ch = 0; ch < 3; ++ch) d[ch] = rget(i, j, ch) - rget(i + kSt2[k][0], j + kSt2[k][1], ch);
+                    T dist = std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+                    T C = std::pow(dist + T(0.0000001), pnorm - T(2));
+                    Lp[k][this->lin(i, j, 0)] = std::sqrt(C);
+                }
+    }
+    template <class S, class C> int residual(int k, C& c, S* r) const {
+        const S zero(T(0));
+        if (k < 4) {                                            // reg Albedo
+            const int ox = kSt2[k][0], oy = kSt2[k][1];
+            const T sq = c.arr(Lp[k].data(), 1, 0);
+            const bool v = c.inb(0, 0) && c.inb(ox, oy);
+            for (int ch = 0; ch < 3; ++ch) r[ch] = w_alb * select(v, sq * (c.unk(0, ch) - c.unk(0, ch, ox, oy)), zero);
+            return 3;
+        }
+        if (k < 8) {                                            // reg Shading
+            const int ox = kSt2[k - 4][0], oy = kSt2[k - 4][1];
+            const bool v = c.inb(0, 0) && c.inb(ox, oy);
+            r[0] = w_shd * select(v, c.unk(1, 0) - c.unk(1, 0, ox, oy), zero);
+            return 1;
+        }
+        for (int ch = 0; ch < 3; ++ch) r[ch] = w_fit * (c.unk(0, ch) + c.unk(1, 0) - c.arr(im, 3, ch));   // fit
+        return 3;
+    }
+};
+
 }  // namespace oracle

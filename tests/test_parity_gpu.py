@@ -23,6 +23,7 @@ CASES = {
     "embedded": (examples.embedded_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
     "cotangent": (examples.cotangent_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
     "robust": (examples.robust_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
+    "intrinsic": (examples.intrinsic_synthetic, (43, 29), dict(n_iter=3, l_iter=10)),
 }
 
 
