@@ -328,8 +328,9 @@ def sfs_synthetic(W, H, seed=1234, n_iter=3, l_iter=10, kind="gaussNewtonGPU", h
 
 
 def intrinsic_synthetic(W, H, seed=1234, n_iter=3, l_iter=10, kind="gaussNewtonGPU"):
-    """intrinsic_image_decomposition: i = log of a piecewise-constant albedo times a smooth shading field, r = i,
-    s = 0 like the driver's start (src/CombinedSolver.h:60-88), weights sqrt(500), sqrt(1000), sqrt(10000) and
+    """intrinsic_image_decomposition on a synthetic picture (piecewise-constant albedo times a smooth shading
+    field, 1 % noise), initialised like the driver (src/CombinedSolver.h:68-108): i = log2(rgb + 0.01),
+    r = log2(chroma + 0.01), s = log2(intensity + 0.01); weights sqrt(500), sqrt(1000), sqrt(10000) and
     pNorm = 0.8 (:33-46; pNorm is an opt_float Param, intrinsic_image_decomposition.t:5)."""
     rng = np.random.default_rng(seed)
     f32 = np.float32
@@ -337,9 +338,12 @@ def intrinsic_synthetic(W, H, seed=1234, n_iter=3, l_iter=10, kind="gaussNewtonG
     blocks = rng.random((H // 8 + 1, W // 8 + 1, 3))
     albedo = 0.2 + 0.7 * blocks[(ys // 8).astype(int), (xs // 8).astype(int)]
     shading = 0.6 + 0.3 * np.sin(2 * np.pi * (0.8 * xs / W + 0.1)) * np.cos(2 * np.pi * 0.7 * ys / H)
-    img = np.log(albedo * shading[..., None] * (1.0 + 0.01 * rng.standard_normal((H, W, 3)))).astype(f32)
-    r = (img + 0.01 * rng.standard_normal((H, W, 3))).astype(f32)
-    s = (0.01 * rng.standard_normal((H, W))).astype(f32)
+    rgb = np.clip(albedo * shading[..., None] * (1.0 + 0.01 * rng.standard_normal((H, W, 3))), 0.02, 1.0).astype(f32)
+    eps = f32(0.01)
+    intensity = rgb.sum(-1, dtype=f32) / f32(3.0)
+    img = np.log2(rgb + eps).astype(f32)
+    r = np.log2(rgb / intensity[..., None] + eps).astype(f32)
+    s = np.log2(intensity + eps).astype(f32)
     w = [np.sqrt(f32(500.0)), np.sqrt(f32(1000.0)), np.sqrt(f32(10000.0))]
     return Problem("intrinsic_image_decomposition.t", [W, H], w + [f32(0.8), r, img, s], [4, 6],
                    {"nIterations": n_iter, "lIterations": l_iter}, kind=kind, opt_float_scalars=[3])

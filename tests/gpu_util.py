@@ -40,8 +40,8 @@ def assert_costs_close(gpu_costs, ref_costs, double, tol=None):
         assert np.isfinite(a) and abs(a - b) <= tol * abs(b), "cost after step %d: gpu %r oracle %r" % (k, a, b)
 
 
-def assert_unknowns_close(gx, rx, double):
-    tol = X_RTOL[double]
+def assert_unknowns_close(gx, rx, double, tol=None):
+    tol = X_RTOL[double] if tol is None else tol
     for i in gx:
         scale = np.abs(rx[i][np.isfinite(rx[i])]).max() + 1e-30
         err = np.abs(gx[i].reshape(-1) - rx[i].reshape(-1)).max()
