@@ -26,12 +26,25 @@ namespace optk {
 //   iteration l:  alphaNum = RZ[l%3], betaNum accumulates into RZ[(l+1)%3], alphaDen = ADEN[l&1]
 enum Scal { S_COST = 0, S_MODEL = 1, S_Q = 2, S_ADEN0 = 3, S_ADEN1 = 4, S_RZ0 = 5, S_RZ1 = 6, S_RZ2 = 7, S_DUMMY = 8, S_COUNT = 16 };
 
-// SoA view of one solver vector: plane u holds channel u of every site (x fastest)
-template <class T>
+// View of one solver vector.  UB == 0: SoA, plane u holds channel u of every site (x fastest).
+// UB == U > 0: blocked layout for functors whose J^T J kernel stages tiles with the bulk-copy engine
+// (VEC_UB in the functor): sites are grouped in blocks of 32 consecutive sites and a block stores its U channels
+// back to back, [site / 32][u][site % 32], so the U channels of a 32-site row segment are ONE contiguous 128 U-byte
+// chunk.  The flat streaming kernels do not care (all vectors of a plan share the layout); site kernels go
+// through operator().
+template <class T, int UB = 0>
 struct Vec {
     T* d;
     long plane;
-    __device__ __forceinline__ T& operator()(int u, long s) const { return d[(long)u * plane + s]; }
+    __device__ __forceinline__ static long index(int u, long s, long plane) {
+        if constexpr (UB == 0) return (long)u * plane + s;
+        else return (s >> 5) * (32 * UB) + u * 32 + (s & 31);
+    }
+    __device__ __forceinline__ T& operator()(int u, long s) const { return d[index(u, s, plane)]; }
+    static long host_index(int u, long s, long plane) {
+        if (UB == 0) return (long)u * plane + s;
+        return (s >> 5) * (32 * UB) + u * 32 + (s & 31);
+    }
 };
 
 __device__ __forceinline__ double warp_sum(double v) {

@@ -120,13 +120,13 @@ struct OptK_Plan {
     int n_sm = 0;
     std::map<const void*, int> occ_cache;
     template <class... KA>
-    dim3 persistent_grid(void (*kernel)(KA...), int threads, long ntiles) {
+    dim3 persistent_grid(void (*kernel)(KA...), int threads, long ntiles, size_t smem = 0) {
         if (!n_sm) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev); }
         auto it = occ_cache.find((const void*)kernel);
         int nb;
         if (it == occ_cache.end()) {
             nb = 1;
-            OPTK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, threads, 0));
+            OPTK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, threads, smem));
             if (nb < 1) nb = 1;
             occ_cache[(const void*)kernel] = nb;
         } else nb = it->second;
@@ -138,6 +138,17 @@ struct OptK_Plan {
     template <class... KA, class... A>
     void launch_tiles(const char* name, long ntiles, dim3 block, void (*kernel)(KA...), A... args) {
         launch(name, persistent_grid(kernel, (int)(block.x * block.y * block.z), ntiles), block, kernel, args...);
+    }
+    // same with dynamic shared memory (TMA-staged kernels): opt in to the large carve-out once per kernel
+    template <class... KA, class... A>
+    void launch_tiles_smem(const char* name, long ntiles, dim3 block, size_t smem, void (*kernel)(KA...), A... args) {
+        if (smem == 0) { launch_tiles(name, ntiles, block, kernel, args...); return; }
+        if (!occ_cache.count((const void*)kernel))
+            OPTK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const dim3 grid = persistent_grid(kernel, (int)(block.x * block.y * block.z), ntiles, smem);
+        pre_launch(name);
+        kernel<<<grid, block, smem, stream>>>(args...);
+        post_launch();
     }
     void print_timing() {                                    // backend_cuda.t:262-297
         if (!timing || timed.empty()) return;
@@ -159,6 +170,8 @@ struct OptK_Plan {
 };
 
 namespace optk {
+
+template <class F> using VecOf = Vec<typename F::Scalar, F::VEC_UB>;     // solver-vector view in the functor's layout
 
 // ------------------------------------------------------------------------------ site mapping
 // Site kernels are persistent: a fixed grid (a few CTAs per SM) loops over the virtual tiles of the
@@ -187,8 +200,8 @@ __device__ __forceinline__ bool thread_site(const F& f, const TileGrid& tg, long
 // ------------------------------------------------------------------------------ site kernels
 // PCGInit1 (solver:521-563).  For graph problems the raw diagonal is stored and inverted later.
 template <class F>
-__global__ void k_pcg_init1(F f, TileGrid tg, Vec<typename F::Scalar> delta, Vec<typename F::Scalar> r,
-                            Vec<typename F::Scalar> p, Vec<typename F::Scalar> pre, double* aNum) {
+__global__ void k_pcg_init1(F f, TileGrid tg, VecOf<F> delta, VecOf<F> r,
+                            VecOf<F> p, VecOf<F> pre, double* aNum) {
     using T = typename F::Scalar;
     constexpr int U = F::U;
     int x, y, z; long s;
@@ -228,22 +241,22 @@ __global__ void k_pcg_init1(F f, TileGrid tg, Vec<typename F::Scalar> delta, Vec
 // formed on the fly wherever the stencil reads it, written once at the thread's own site into the
 // OTHER p buffer (ping-pong: neighbours still read the old p), and Ap' = J^T J p' is produced in the
 // same pass.  Saves one read of p and one kernel per PCG iteration.
-template <class T>
+template <class V, class T>
 struct FusedDir {
-    Vec<T> z, p;
+    V z, p;
     T beta;
     __device__ __forceinline__ T operator()(int u, long s) const { return z(u, s) + beta * p(u, s); }
 };
 template <class F, bool LM>
-__global__ void k_apply_jtj_fused(F f, TileGrid tg, Vec<typename F::Scalar> z, Vec<typename F::Scalar> p_old,
-                                  Vec<typename F::Scalar> p_new, Vec<typename F::Scalar> out,
-                                  Vec<typename F::Scalar> CtC, const double* bNum, const double* aNum,
+__global__ void k_apply_jtj_fused(F f, TileGrid tg, VecOf<F> z, VecOf<F> p_old,
+                                  VecOf<F> p_new, VecOf<F> out,
+                                  VecOf<F> CtC, const double* bNum, const double* aNum,
                                   double* den, double* zero_a, double* zero_b) {
     using T = typename F::Scalar;
     constexpr int U = F::U;
     int x, y, zc; long s;
     double acc = 0.0;
-    FusedDir<T> dir{z, p_old, (T)(*bNum) / (T)(*aNum)};
+    FusedDir<VecOf<F>, T> dir{z, p_old, (T)(*bNum) / (T)(*aNum)};
     if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && linear_tid() == 0) {
         if (zero_a) *zero_a = 0.0;
         if (zero_b) *zero_b = 0.0;
@@ -266,8 +279,8 @@ __global__ void k_apply_jtj_fused(F f, TileGrid tg, Vec<typename F::Scalar> z, V
 
 // PCGStep1 / computeAdelta (solver:607-632, 873-878): out = (J^T J [+ CtC]) dir over non-excluded sites
 template <class F, bool LM>
-__global__ void k_apply_jtj(F f, TileGrid tg, Vec<typename F::Scalar> dir, Vec<typename F::Scalar> out,
-                            Vec<typename F::Scalar> CtC, double* den, double* zero_slot) {
+__global__ void k_apply_jtj(F f, TileGrid tg, VecOf<F> dir, VecOf<F> out,
+                            VecOf<F> CtC, double* den, double* zero_slot) {
     using T = typename F::Scalar;
     constexpr int U = F::U;
     int x, y, z; long s;
@@ -301,7 +314,7 @@ __global__ void k_cost(F f, TileGrid tg, double* target) {
 
 // computeModelCost (solver:1105-1118)
 template <class F>
-__global__ void k_model_cost(F f, TileGrid tg, Vec<typename F::Scalar> delta, double* target) {
+__global__ void k_model_cost(F f, TileGrid tg, VecOf<F> delta, double* target) {
     using T = typename F::Scalar;
     int x, y, z; long s;
     double acc = 0.0;
@@ -312,7 +325,7 @@ __global__ void k_model_cost(F f, TileGrid tg, Vec<typename F::Scalar> delta, do
 
 // PCGComputeCtC (solver:1042-1048): CtC = diag(J^T J) / radius
 template <class F>
-__global__ void k_compute_ctc(F f, TileGrid tg, Vec<typename F::Scalar> CtC, typename F::Scalar inv_radius) {
+__global__ void k_compute_ctc(F f, TileGrid tg, VecOf<F> CtC, typename F::Scalar inv_radius) {
     using T = typename F::Scalar;
     constexpr int U = F::U;
     int x, y, z; long s;
@@ -329,10 +342,10 @@ __global__ void k_compute_ctc(F f, TileGrid tg, Vec<typename F::Scalar> CtC, typ
 
 // PCGFinalizeDiagonal (solver:1061-1099)
 template <class F>
-__global__ void k_finalize_diagonal(F f, TileGrid tg, Vec<typename F::Scalar> CtC, Vec<typename F::Scalar> SSq,
-                                    Vec<typename F::Scalar> pre, Vec<typename F::Scalar> r,
-                                    Vec<typename F::Scalar> b, Vec<typename F::Scalar> p,
-                                    Vec<typename F::Scalar> delta, typename F::Scalar radius,
+__global__ void k_finalize_diagonal(F f, TileGrid tg, VecOf<F> CtC, VecOf<F> SSq,
+                                    VecOf<F> pre, VecOf<F> r,
+                                    VecOf<F> b, VecOf<F> p,
+                                    VecOf<F> delta, typename F::Scalar radius,
                                     typename F::Scalar min_diag, typename F::Scalar max_diag,
                                     double* aNum, double* q) {
     using T = typename F::Scalar;
@@ -367,7 +380,7 @@ __global__ void k_finalize_diagonal(F f, TileGrid tg, Vec<typename F::Scalar> Ct
 // PCGLinearUpdate / savePreviousUnknowns / revertUpdate (solver:854-887); MODE 0: X += delta,
 // 1: prevX = X, 2: X = prevX
 template <class F, int MODE>
-__global__ void k_unknown_update(F f, TileGrid tg, Vec<typename F::Scalar> v) {
+__global__ void k_unknown_update(F f, TileGrid tg, VecOf<F> v) {
     constexpr int U = F::U;
     int x, y, z; long s;
     OPTK_TILE_LOOP(tg)
@@ -395,14 +408,14 @@ __global__ void k_precompute(F f, TileGrid tg) {
 // ------------------------------------------------------------------------------ graph kernels
 // PCGInit1_Graph (solver:1188-1197): scatter -dr/du * r into r, (dr/du)^2 into pre
 template <class F>
-__global__ void k_graph_jtf(F f, long E, Vec<typename F::Scalar> r, Vec<typename F::Scalar> pre) {
+__global__ void k_graph_jtf(F f, long E, VecOf<F> r, VecOf<F> pre) {
     long e = blockIdx.x * (long)blockDim.x + threadIdx.x;
     if (e < E) f.graphJTF(e, r, pre);
 }
 // PCGInit1_Finish (solver:570-598): no exclude test
 template <class F>
-__global__ void k_pcg_init1_finish(F f, TileGrid tg, Vec<typename F::Scalar> r, Vec<typename F::Scalar> pre,
-                                   Vec<typename F::Scalar> p, double* aNum) {
+__global__ void k_pcg_init1_finish(F f, TileGrid tg, VecOf<F> r, VecOf<F> pre,
+                                   VecOf<F> p, double* aNum) {
     using T = typename F::Scalar;
     constexpr int U = F::U;
     int x, y, z; long s;
@@ -424,7 +437,7 @@ __global__ void k_pcg_init1_finish(F f, TileGrid tg, Vec<typename F::Scalar> r, 
 }
 // PCGStep1_Graph / computeAdelta_Graph (solver:1216-1244)
 template <class F>
-__global__ void k_graph_jtj(F f, long E, Vec<typename F::Scalar> dir, Vec<typename F::Scalar> out, double* den) {
+__global__ void k_graph_jtj(F f, long E, VecOf<F> dir, VecOf<F> out, double* den) {
     long e = blockIdx.x * (long)blockDim.x + threadIdx.x;
     double acc = 0.0;
     if (e < E) acc = (double)f.graphJTJ(e, dir, out);
@@ -439,7 +452,7 @@ __global__ void k_graph_cost(F f, long E, double* target) {
     block_accumulate(acc, target);
 }
 template <class F>
-__global__ void k_graph_model_cost(F f, long E, Vec<typename F::Scalar> delta, double* target) {
+__global__ void k_graph_model_cost(F f, long E, VecOf<F> delta, double* target) {
     using T = typename F::Scalar;
     long e = blockIdx.x * (long)blockDim.x + threadIdx.x;
     double acc = 0.0;
@@ -447,7 +460,7 @@ __global__ void k_graph_model_cost(F f, long E, Vec<typename F::Scalar> delta, d
     block_accumulate(acc, target);
 }
 template <class F>
-__global__ void k_graph_ctc(F f, long E, Vec<typename F::Scalar> CtC, typename F::Scalar inv_radius) {
+__global__ void k_graph_ctc(F f, long E, VecOf<F> CtC, typename F::Scalar inv_radius) {
     long e = blockIdx.x * (long)blockDim.x + threadIdx.x;
     if (e < E) f.graphCtC(e, CtC, inv_radius);
 }
@@ -476,8 +489,8 @@ static __global__ void k_incidence_offsets(const unsigned* __restrict__ keys, lo
 }
 template <class F, bool LM>
 __global__ void __launch_bounds__(128) k_gather_jtj(F f, long N, const int* __restrict__ off, const unsigned* __restrict__ inc,
-                                                    Vec<typename F::Scalar> dir, Vec<typename F::Scalar> out,
-                                                    Vec<typename F::Scalar> CtC, double* den, double* zero_slot) {
+                                                    VecOf<F> dir, VecOf<F> out,
+                                                    VecOf<F> CtC, double* den, double* zero_slot) {
     using T = typename F::Scalar;
     constexpr int U = F::U;
     double acc = 0.0;
@@ -651,6 +664,7 @@ __global__ void __launch_bounds__(256) k_residual_reset(long nvec, const unsigne
 template <class F>
 struct Engine : OptK_Plan {
     using T = typename F::Scalar;
+    using V = VecOf<F>;
     static constexpr int U = F::U;
     static constexpr bool GRAPH = F::GV > 0;
 
@@ -658,8 +672,8 @@ struct Engine : OptK_Plan {
     bool lm;
     long N, Npad, E;
     T* pool = nullptr;
-    Vec<T> delta, r, b, Adelta, z, p, Ap, CtC, pre, SSq, prevX;
-    Vec<T> p_alt;                                           // second p buffer of the fused Step3+Step1 kernel
+    V delta, r, b, Adelta, z, p, Ap, CtC, pre, SSq, prevX;
+    V p_alt;                                           // second p buffer of the fused Step3+Step1 kernel
     unsigned char* active4 = nullptr;                       // 1 flag per 4 sites (HAS_EXCLUDE functors only)
     unsigned* inc = nullptr;                                // HAS_GATHER: incidence payloads sorted by (vertex, slot)
     int* inc_off = nullptr;                                 //             N*GV + 1 segment offsets
@@ -686,7 +700,7 @@ struct Engine : OptK_Plan {
         size_t bytes = (size_t)nvec * U * Npad * sizeof(T);
         OPTK_CUDA(cudaMalloc(&pool, bytes));
         OPTK_CUDA(cudaMemsetAsync(pool, 0, bytes, stream));
-        Vec<T>* vs[12] = {&delta, &r, &z, &p, &Ap, &pre, &prevX, &p_alt, &b, &Adelta, &CtC, &SSq};
+        V* vs[12] = {&delta, &r, &z, &p, &Ap, &pre, &prevX, &p_alt, &b, &Adelta, &CtC, &SSq};
         for (int i = 0; i < 12; ++i) {
             vs[i]->plane = Npad;
             vs[i]->d = i < nvec ? pool + (size_t)i * U * Npad : nullptr;
@@ -768,7 +782,10 @@ struct Engine : OptK_Plan {
         OPTK_NCCL(ncclGroupEnd());
     }
     size_t slow_rowsz() const { return F::ND == 3 ? (size_t)f.W * f.H : (size_t)f.W; }
-    void exchange(Vec<T> v) { exchange_raw(v.d, U, (size_t)v.plane, slow_rowsz()); }
+    void exchange(V v) {
+        if constexpr (F::VEC_UB > 0) exchange_raw(v.d, 1, 0, slow_rowsz() * U);     // blocked layout: a slow-dimension slice is contiguous
+        else exchange_raw(v.d, U, (size_t)v.plane, slow_rowsz());
+    }
     void exchange_unknowns() {
         if (nranks <= 1) return;
         void* ptrs[8]; int ch[8];
@@ -857,7 +874,7 @@ struct Engine : OptK_Plan {
         exchange(p);                                        // Step1 reads p over the stencil
     }
 
-    void apply_A(const char* name, const char* gname, Vec<T> dir, Vec<T> out, double* den, double* zero_slot) {
+    void apply_A(const char* name, const char* gname, V dir, V out, double* den, double* zero_slot) {
         if constexpr (F::HAS_GATHER) {
             if (use_gather()) {
                 const long nb = (N + 127) / 128;
@@ -868,8 +885,8 @@ struct Engine : OptK_Plan {
         }
         if constexpr (F::HAS_FAST_APPLY) {
             if (f.fast_ok()) {
-                if (lm) this->launch_tiles(name, f.fast_tiles(), f.fast_block(), F::template fast_kernel<false, true>(), f, dir, dir, dir, out, CtC, (const unsigned char*)active4, (const double*)nullptr, (const double*)nullptr, den, zero_slot, (double*)nullptr);
-                else    this->launch_tiles(name, f.fast_tiles(), f.fast_block(), F::template fast_kernel<false, false>(), f, dir, dir, dir, out, CtC, (const unsigned char*)active4, (const double*)nullptr, (const double*)nullptr, den, zero_slot, (double*)nullptr);
+                if (lm) this->launch_tiles_smem(name, f.fast_tiles(), f.fast_block(), f.fast_smem(), f.template fast_kernel<false, true>(), f, dir, dir, dir, out, CtC, (const unsigned char*)active4, (const double*)nullptr, (const double*)nullptr, den, zero_slot, (double*)nullptr);
+                else    this->launch_tiles_smem(name, f.fast_tiles(), f.fast_block(), f.fast_smem(), f.template fast_kernel<false, false>(), f, dir, dir, dir, out, CtC, (const unsigned char*)active4, (const double*)nullptr, (const double*)nullptr, den, zero_slot, (double*)nullptr);
                 return;
             }
         }
@@ -892,8 +909,8 @@ struct Engine : OptK_Plan {
             double* prevA = S(S_RZ0 + (l + 2) % 3);
             if constexpr (F::HAS_FAST_APPLY) {
                 if (f.fast_ok()) {
-                    if (lm) this->launch_tiles("PCGStep3+1", f.fast_tiles(), f.fast_block(), F::template fast_kernel<true, true>(), f, z, p, p_alt, Ap, CtC, (const unsigned char*)active4, (const double*)aNum, (const double*)prevA, aDen, bNum, S(S_Q));
-                    else    this->launch_tiles("PCGStep3+1", f.fast_tiles(), f.fast_block(), F::template fast_kernel<true, false>(), f, z, p, p_alt, Ap, CtC, (const unsigned char*)active4, (const double*)aNum, (const double*)prevA, aDen, bNum, (double*)nullptr);
+                    if (lm) this->launch_tiles_smem("PCGStep3+1", f.fast_tiles(), f.fast_block(), f.fast_smem(), f.template fast_kernel<true, true>(), f, z, p, p_alt, Ap, CtC, (const unsigned char*)active4, (const double*)aNum, (const double*)prevA, aDen, bNum, S(S_Q));
+                    else    this->launch_tiles_smem("PCGStep3+1", f.fast_tiles(), f.fast_block(), f.fast_smem(), f.template fast_kernel<true, false>(), f, z, p, p_alt, Ap, CtC, (const unsigned char*)active4, (const double*)aNum, (const double*)prevA, aDen, bNum, (double*)nullptr);
                     std::swap(p.d, p_alt.d);
                     goto applied;
                 }
@@ -940,26 +957,26 @@ struct Engine : OptK_Plan {
         exchange_unknowns();
     }
 
-    Vec<T>* vec_by_name(const char* n) {
-        struct { const char* n; Vec<T>* v; } tab[] = {{"delta", &delta}, {"r", &r}, {"p", &p}, {"Ap", &Ap}, {"z", &z},
+    V* vec_by_name(const char* n) {
+        struct { const char* n; V* v; } tab[] = {{"delta", &delta}, {"r", &r}, {"p", &p}, {"Ap", &Ap}, {"z", &z},
                                                       {"pre", &pre}, {"CtC", &CtC}, {"b", &b}, {"prevX", &prevX}};
         for (auto& t : tab) if (!strcmp(t.n, n)) return t.v;
         return nullptr;
     }
     int debug_read(const char* name, void* host_out) override {
-        Vec<T>* v = vec_by_name(name);
+        V* v = vec_by_name(name);
         if (!v || !v->d) return -1;
         std::vector<T> tmp((size_t)U * Npad);
         OPTK_CUDA(cudaStreamSynchronize(stream));
         OPTK_CUDA(cudaMemcpy(tmp.data(), v->d, tmp.size() * sizeof(T), cudaMemcpyDeviceToHost));
         T* o = (T*)host_out;
-        for (long s = 0; s < N; ++s) for (int u = 0; u < U; ++u) o[s * U + u] = tmp[(size_t)u * Npad + s];
+        for (long s = 0; s < N; ++s) for (int u = 0; u < U; ++u) o[s * U + u] = tmp[(size_t)V::host_index(u, s, Npad)];
         return 0;
     }
     void debug_apply_jtj(const void* host_p, void* host_out) override {
         std::vector<T> tmp((size_t)U * Npad, T(0));
         const T* hp = (const T*)host_p;
-        for (long s = 0; s < N; ++s) for (int u = 0; u < U; ++u) tmp[(size_t)u * Npad + s] = hp[s * U + u];
+        for (long s = 0; s < N; ++s) for (int u = 0; u < U; ++u) tmp[(size_t)V::host_index(u, s, Npad)] = hp[s * U + u];
         OPTK_CUDA(cudaMemcpy(p.d, tmp.data(), tmp.size() * sizeof(T), cudaMemcpyHostToDevice));
         OPTK_CUDA(cudaMemsetAsync(Ap.d, 0, tmp.size() * sizeof(T), stream));
         bool saved = lm; lm = false;
@@ -981,8 +998,10 @@ struct FunctorDefaults {
     static constexpr bool HAS_FAST_APPLY = false;        // functors with a specialised J^T J kernel override this
     static constexpr bool SLAB_OK = true;                // grid functors whose bounds predicates survive a slab cut
     static constexpr bool HAS_GATHER = false;            // graph functors with a per-vertex gather form of J^T J p
+    static constexpr int VEC_UB = 0;                     // solver-vector layout: 0 = SoA, U = blocked (common.cuh, Vec)
     static constexpr bool FUSE_STEP3 = true;             // form p' = z + beta p inside the J^T J kernel (engine.cuh, FusedDir)
     bool fast_ok() const { return false; }
+    size_t fast_smem() const { return 0; }                 // dynamic shared memory of the fast J^T J kernel
     static constexpr int GV = 0;
     int E = 0;
     int o_lo = 0, o_hi = 0x7fffffff;                       // owned range along the slowest dimension (slab mode)
@@ -990,11 +1009,11 @@ struct FunctorDefaults {
     void alloc_temporaries(cudaStream_t) {}
     void free_temporaries() {}
     __device__ void precompute(int, int, int, long) const {}
-    __device__ void graphJTF(long, Vec<T>, Vec<T>) const {}
-    __device__ T graphJTJ(long, Vec<T>, Vec<T>) const { return T(0); }
+    template <class V> __device__ void graphJTF(long, V, V) const {}
+    template <class V> __device__ T graphJTJ(long, V, V) const { return T(0); }
     __device__ T graphCost(long) const { return T(0); }
-    __device__ T graphModelCost(long, Vec<T>) const { return T(0); }
-    __device__ void graphCtC(long, Vec<T>, T) const {}
+    template <class V> __device__ T graphModelCost(long, V) const { return T(0); }
+    template <class V> __device__ void graphCtC(long, V, T) const {}
 };
 
 template <template <class> class F>

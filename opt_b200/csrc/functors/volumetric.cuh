@@ -17,14 +17,17 @@ struct VolumetricFunctor : FunctorDefaults<T> {
     // the generic lazy p' = z + beta p accessor doubles the 42 stencil loads of this functor and the kernel
     // is issue-bound, not DRAM-bound (measured: fused 2.28 ms vs 1.44 + 0.17 ms at 256^3)
     static constexpr bool FUSE_STEP3 = false;
+    // fp32 keeps its solver vectors in the blocked layout (common.cuh, Vec) that the packed kernel's bulk copies need
+    static constexpr int VEC_UB = sizeof(T) == 4 ? 6 : 0;
     int W, H, D;
     T* O; T* A; const T* Ur; const T* Cn;
     T w_fit, w_reg;
     // Table refreshed by precompute (once per nonlinear iteration, like the reference's ComputedArrays,
     // o.t:3131-3153): sin/cos of the three Euler angles, UrShape and the fit-term predicate of every site,
-    // stored in the tile order of the J^T J kernel below: one record per 30 x FTY x 1 tile, laid out
-    // [plane 10][ty][32 lanes], where lanes 0 and 31 DUPLICATE the x-neighbours of the tile.  A warp row
-    // is therefore one aligned 128-byte line per plane and every table access of a thread is
+    // stored in the tile order of the J^T J kernels: one record per 30 x FTY x 1 tile, laid out
+    // [ty][plane 10][32 lanes], where lanes 0 and 31 DUPLICATE the x-neighbours of the tile.  A warp row
+    // is therefore one aligned 128-byte line per plane (and all planes of a row, or of the whole record, are one
+    // contiguous chunk for the bulk-copy engine), and every table access of a thread is
     // (one pointer) + (compile-time offset).  The kernel reads ONLY this table and p inside the PCG loop:
     // no sincos, no 12-byte-strided AoS loads.  Planes: sa ca sb cb sg cg ux uy uz fit.
     T* tab = nullptr;
@@ -34,24 +37,30 @@ struct VolumetricFunctor : FunctorDefaults<T> {
     static constexpr int FTY = 8, FTZ = 1, FTX = 30, FNT = 32 * FTY * FTZ;
     static constexpr int ZC = 32;                               // planes one warp marches through per work unit
     static constexpr long REC = (long)NP * FNT;                 // elements per tile record
+    static constexpr int PLS = 32, RWS = NP * 32;               // plane / row stride inside a record: [ty][plane][32 lanes]
     void plan(const unsigned* d) { W = d[0]; H = d[1]; D = d[2]; }
     __host__ __device__ int ntx() const { return (W + FTX - 1) / FTX; }
     __host__ __device__ int nty() const { return (H + FTY - 1) / FTY; }
     __host__ __device__ int ntz() const { return (D + FTZ - 1) / FTZ; }
+    // fp32 grids whose rows are a multiple of 32 sites run the packed kernel fed by bulk async copies
+    // (functors/volumetric_packed.cuh), fp64 the scalar marching kernel below, everything else the generic functor kernel
     void alloc_temporaries(cudaStream_t) {
         OPTK_CUDA(cudaMalloc(&tab, (size_t)ntx() * nty() * ntz() * REC * sizeof(T)));
     }
     void free_temporaries() { cudaFree(tab); tab = nullptr; }
+    size_t fast_smem() const;
     __device__ void precompute(int, int, int, long) const {}   // table is written by custom_precompute
     void custom_precompute(cudaStream_t stream, int n_sm) const;
-    bool fast_ok() const { return getenv("OPTB200_GENERIC_JTJ") == nullptr; }
+    bool use_packed() const { return sizeof(T) == 4 && W % 32 == 0; }
+    bool fast_ok() const { return getenv("OPTB200_GENERIC_JTJ") == nullptr && (sizeof(T) == 8 || use_packed()); }
     // a slab rank marches through its owned planes only
     __host__ __device__ int z_lo() const { return this->o_lo; }
     __host__ __device__ int z_hi() const { return this->o_hi < D ? this->o_hi : D; }
     __host__ __device__ int nseg() const { return (z_hi() - z_lo() + ZC - 1) / ZC; }
-    long fast_tiles() const { return (long)ntx() * nty() * nseg(); }
+    // the packed kernel works on 30 x 16 tiles (two table records stacked in y)
+    long fast_tiles() const { return (long)ntx() * (use_packed() ? (nty() + 1) / 2 : nty()) * nseg(); }
     dim3 fast_block() const { return dim3(32, FTY, FTZ); }
-    template <bool FUSED, bool LM> static auto fast_kernel();
+    template <bool FUSED, bool LM> auto fast_kernel() const;
     void bind(void** pp) {
         O = (T*)pp[0]; A = (T*)pp[1]; Ur = (const T*)pp[2]; Cn = (const T*)pp[3];
         w_fit = (T) * (const float*)pp[4]; w_reg = (T) * (const float*)pp[5];
@@ -143,7 +152,7 @@ struct VolumetricFunctor : FunctorDefaults<T> {
 #pragma unroll
         for (int k = 0; k < 3; ++k) { out[k] = vf * pi[k] + wr2 * acc[k]; out[3 + k] = wr2 * acc[3 + k]; }
     }
-    __device__ T modelCost(int x, int y, int z, long s, const Vec<T>& dl) const {
+    template <class V> __device__ T modelCost(int x, int y, int z, long s, const V& dl) const {
         T oi[3], ui[3], ai[3]; load3(O + s * 3, oi); load3(Ur + s * 3, ui); load3(A + s * 3, ai);
         Rot3<T> R; R.set(ai);
         T di[6];
@@ -207,9 +216,9 @@ __global__ void __launch_bounds__(VolumetricFunctor<T>::FNT) k_volumetric_table(
             for (int k = 0; k < 3; ++k) sincos_t(a[k], v[2 * k], v[2 * k + 1]);
             v[9] = f.Cn[s * 3] >= T(-999999.9) ? T(1) : T(0);
         }
-        T* rec = f.tab + (long)tile * F::REC + tid;
+        T* rec = f.tab + (long)tile * F::REC + (int)threadIdx.y * F::RWS + lane;
 #pragma unroll
-        for (int k = 0; k < F::NP; ++k) rec[k * NT] = v[k];
+        for (int k = 0; k < F::NP; ++k) rec[k * F::PLS] = v[k];
     }
 }
 template <class T> void VolumetricFunctor<T>::custom_precompute(cudaStream_t stream, int n_sm) const {
@@ -247,7 +256,7 @@ k_volumetric_apply(VolumetricFunctor<T> f, Vec<T> zv, Vec<T> p, Vec<T> p_new, Ve
     // row of the adjacent one (warp-uniform choice), the z neighbours one z-stride away
     const long rec_y = (long)ntx * F::REC, rec_z = (long)ntx * nty * F::REC;
     const bool typ = ty + 1 < TY, tym = ty > 0;
-    const long oyp = typ ? 32 : rec_y - (TY - 1) * 32, oym = tym ? -32 : -rec_y + (TY - 1) * 32;
+    const long oyp = typ ? F::RWS : rec_y - (TY - 1) * F::RWS, oym = tym ? -F::RWS : -rec_y + (TY - 1) * F::RWS;
     if (blockIdx.x == 0 && tid == 0) {
         if (zero_a) *zero_a = 0.0;
         if (zero_b) *zero_b = 0.0;
@@ -262,16 +271,16 @@ k_volumetric_apply(VolumetricFunctor<T> f, Vec<T> zv, Vec<T> p, Vec<T> p_new, Ve
         const bool hasR = inside && lane < 31 && x + 1 < W, hasL = inside && lane > 0 && x > 0;
         const bool eyp = inner && y + 1 < H, eym = inner && y > 0;
         long s = x + (long)sy * y + sz * z0;
-        const T* __restrict__ ts = f.tab + ((long)(z0 * nty + by) * ntx + bx) * F::REC + tid;
+        const T* __restrict__ ts = f.tab + ((long)(z0 * nty + by) * ntx + bx) * F::REC + ty * F::RWS + lane;
         const T* __restrict__ ps = p.d + s;
         bool havePrev = z0 > 0, writePrev = false;
 
         auto load_site = [&](VolSite<T>& c, const T* __restrict__ tn, const T* __restrict__ pn) {
 #pragma unroll
-            for (int k = 0; k < 6; ++k) { c.tr[k] = tn[k * NT]; c.pc[k] = inside ? pn[k * pp] : T(0); }
+            for (int k = 0; k < 6; ++k) { c.tr[k] = tn[k * F::PLS]; c.pc[k] = inside ? pn[k * pp] : T(0); }
 #pragma unroll
-            for (int k = 0; k < 3; ++k) c.uc[k] = tn[(6 + k) * NT];
-            c.fit = tn[9 * NT];
+            for (int k = 0; k < 3; ++k) c.uc[k] = tn[(6 + k) * F::PLS];
+            c.fit = tn[9 * F::PLS];
         };
         // Ap_O of a completed plane (all six jp_in and jp_ni collected in acc)
         auto write_O = [&](const VolSite<T>& c, const T* acc, long sp) {
@@ -350,12 +359,12 @@ k_volumetric_apply(VolumetricFunctor<T> f, Vec<T> zv, Vec<T> p, Vec<T> p_new, Ve
                     const T* __restrict__ pn_ = ps + poff;
                     T un[3], pn[3], u[3], q[3];
 #pragma unroll
-                    for (int k = 0; k < 3; ++k) { un[k] = tn[(6 + k) * NT]; pn[k] = pn_[k * pp]; }
+                    for (int k = 0; k < 3; ++k) { un[k] = tn[(6 + k) * F::PLS]; pn[k] = pn_[k * pp]; }
                     edge(un, pn, u, q, jp);
                     {
                         T t6[6], Mn[3][3];
 #pragma unroll
-                        for (int k = 0; k < 6; ++k) t6[k] = tn[k * NT];
+                        for (int k = 0; k < 6; ++k) t6[k] = tn[k * F::PLS];
                         RotM<T> rn; rn.set(t6);
                         rn.combine(pn_[3 * pp], pn_[4 * pp], pn_[5 * pp], Mn);
 #pragma unroll
@@ -408,7 +417,5 @@ k_volumetric_apply(VolumetricFunctor<T> f, Vec<T> zv, Vec<T> p, Vec<T> p_new, Ve
     }
     block_accumulate(dot, den);
 }
-
-template <class T> template <bool FUSED, bool LM> auto VolumetricFunctor<T>::fast_kernel() { return &k_volumetric_apply<T, FUSED, LM>; }
 
 }  // namespace optk

@@ -17,6 +17,9 @@ CASES = {
     "volumetric": (examples.volumetric_synthetic, (11, 9, 7), dict(n_iter=3, l_iter=10)),
     # several 30x4x4 (fp32) / 30x4x2 (fp64) tiles of the tiled J^T J kernel per dimension, ragged edges
     "volumetric_tiles": (examples.volumetric_synthetic, (67, 10, 9), dict(n_iter=2, l_iter=8)),
+    # rows that are a multiple of 32 sites: the packed fp32 kernel fed by bulk copies (ragged tiles in x and y, two
+    # z segments, 30 x 16 tiles: 3 x 2 of them)
+    "volumetric_packed": (examples.volumetric_synthetic, (64, 19, 37), dict(n_iter=2, l_iter=8)),
     "optical_flow": (examples.optical_flow_synthetic, (53, 38), dict(n_iter=3, l_iter=10)),
     "arap": (examples.arap_synthetic, (13, 11), dict(n_iter=3, l_iter=10)),
     "sfs": (examples.sfs_synthetic, (45, 37), dict(n_iter=3, l_iter=10)),
@@ -88,12 +91,12 @@ def test_jtf_and_jtj_match_oracle(built, case, double):
     assert np.abs(ap_gpu - ap_ref).max() <= tol * np.abs(ap_ref).max()
 
 
-@pytest.mark.parametrize("double", [False, True])
-def test_volumetric_tiled_jtj_equals_generic(built, double, monkeypatch):
-    """The tiled kernel (precomputed trig table, shared-memory exchange of J p) against the generic
-    one-thread-per-site functor kernel: two different derivations of the same operator."""
+@pytest.mark.parametrize("case,double", [("volumetric_tiles", True), ("volumetric_packed", True), ("volumetric_packed", False)])
+def test_volumetric_tiled_jtj_equals_generic(built, case, double, monkeypatch):
+    """The marching kernels (precomputed trig table; fp64 scalar, fp32 packed pairs fed by bulk copies) against the
+    generic one-thread-per-site functor kernel: two different derivations of the same operator."""
     from opt_b200 import solver as S
-    pr = make("volumetric_tiles", double=double)
+    pr = make(case, double=double)
     named = S.upload(pr)
     dt = np.float64 if double else np.float32
     rng = np.random.default_rng(11)
