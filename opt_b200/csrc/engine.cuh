@@ -977,7 +977,9 @@ struct Engine : OptK_Plan {
         std::vector<T> tmp((size_t)U * Npad, T(0));
         const T* hp = (const T*)host_p;
         for (long s = 0; s < N; ++s) for (int u = 0; u < U; ++u) tmp[(size_t)V::host_index(u, s, Npad)] = hp[s * U + u];
-        OPTK_CUDA(cudaMemcpy(p.d, tmp.data(), tmp.size() * sizeof(T), cudaMemcpyHostToDevice));
+        // on the plan's stream: a pageable cudaMemcpy on the legacy stream may still be in flight when the kernels
+        // below start on the (non-blocking) plan stream
+        OPTK_CUDA(cudaMemcpyAsync(p.d, tmp.data(), tmp.size() * sizeof(T), cudaMemcpyHostToDevice, stream));
         OPTK_CUDA(cudaMemsetAsync(Ap.d, 0, tmp.size() * sizeof(T), stream));
         bool saved = lm; lm = false;
         if (use_gather()) build_incidence();

@@ -1,7 +1,11 @@
-// Instantiates the generic engine for volumetric_mesh_deformation (fp32 and fp64).
+// Instantiates the generic engine for volumetric_mesh_deformation: fp64 and fp32 with SoA solver vectors and the
+// scalar marching kernel, and fp32 with blocked vectors and the packed kernel fed by bulk copies for grids whose rows
+// are a multiple of 32 sites (OPTB200_VOL_SCALAR=1 at plan time forces the former).
 #include "../engine.cuh"
 #include "../functors/volumetric_packed.cuh"
 
 extern "C" OptK_Plan* optk_make_volumetric_mesh_deformation(int is_double, int is_lm, const unsigned* dims, int timing) {
-    return optk::make_engine<optk::VolumetricFunctor>(is_double, is_lm, dims, timing);
+    if (!is_double && dims[0] % 32 == 0 && getenv("OPTB200_VOL_SCALAR") == nullptr)
+        return new optk::Engine<optk::VolumetricPackedFunctor<float>>(dims, is_lm != 0, timing != 0);
+    return optk::make_engine<optk::VolumetricScalarFunctor>(is_double, is_lm, dims, timing);
 }

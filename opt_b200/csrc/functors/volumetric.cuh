@@ -9,7 +9,10 @@
 
 namespace optk {
 
-template <class T>
+// UB = 0: SoA solver vectors, scalar marching kernel (fp64, and fp32 grids whose rows are not a multiple of 32 sites);
+// UB = 6: blocked solver vectors + the packed fp32 kernel of functors/volumetric_packed.cuh.  The plan chooses
+// (examples/volumetric_mesh_deformation.cu).
+template <class T, int UB = 0>
 struct VolumetricFunctor : FunctorDefaults<T> {
     using Scalar = T;
     static constexpr int U = 6, ND = 3;
@@ -17,8 +20,7 @@ struct VolumetricFunctor : FunctorDefaults<T> {
     // the generic lazy p' = z + beta p accessor doubles the 42 stencil loads of this functor and the kernel
     // is issue-bound, not DRAM-bound (measured: fused 2.28 ms vs 1.44 + 0.17 ms at 256^3)
     static constexpr bool FUSE_STEP3 = false;
-    // fp32 keeps its solver vectors in the blocked layout (common.cuh, Vec) that the packed kernel's bulk copies need
-    static constexpr int VEC_UB = sizeof(T) == 4 ? 6 : 0;
+    static constexpr int VEC_UB = UB;                          // blocked layout (common.cuh, Vec) for the packed kernel's bulk copies
     int W, H, D;
     T* O; T* A; const T* Ur; const T* Cn;
     T w_fit, w_reg;
@@ -42,8 +44,6 @@ struct VolumetricFunctor : FunctorDefaults<T> {
     __host__ __device__ int ntx() const { return (W + FTX - 1) / FTX; }
     __host__ __device__ int nty() const { return (H + FTY - 1) / FTY; }
     __host__ __device__ int ntz() const { return (D + FTZ - 1) / FTZ; }
-    // fp32 grids whose rows are a multiple of 32 sites run the packed kernel fed by bulk async copies
-    // (functors/volumetric_packed.cuh), fp64 the scalar marching kernel below, everything else the generic functor kernel
     void alloc_temporaries(cudaStream_t) {
         OPTK_CUDA(cudaMalloc(&tab, (size_t)ntx() * nty() * ntz() * REC * sizeof(T)));
     }
@@ -51,8 +51,8 @@ struct VolumetricFunctor : FunctorDefaults<T> {
     size_t fast_smem() const;
     __device__ void precompute(int, int, int, long) const {}   // table is written by custom_precompute
     void custom_precompute(cudaStream_t stream, int n_sm) const;
-    bool use_packed() const { return sizeof(T) == 4 && W % 32 == 0; }
-    bool fast_ok() const { return getenv("OPTB200_GENERIC_JTJ") == nullptr && (sizeof(T) == 8 || use_packed()); }
+    static constexpr bool use_packed() { return UB > 0; }
+    bool fast_ok() const { return getenv("OPTB200_GENERIC_JTJ") == nullptr; }
     // a slab rank marches through its owned planes only
     __host__ __device__ int z_lo() const { return this->o_lo; }
     __host__ __device__ int z_hi() const { return this->o_hi < D ? this->o_hi : D; }
@@ -195,9 +195,9 @@ struct VolumetricFunctor : FunctorDefaults<T> {
 // 21 sincos and ~1850 instructions per site; this needs no sincos and ~40 % of the instructions.
 // Writes the tile-ordered table (same thread <-> site mapping as k_volumetric_apply; slots outside the
 // grid are zero-filled so that the apply kernel can read them unconditionally).
-template <class T>
-__global__ void __launch_bounds__(VolumetricFunctor<T>::FNT) k_volumetric_table(VolumetricFunctor<T> f) {
-    using F = VolumetricFunctor<T>;
+template <class F>
+__global__ void __launch_bounds__(F::FNT) k_volumetric_table(F f) {
+    using T = typename F::Scalar;
     constexpr int TX = F::FTX, TY = F::FTY, TZ = F::FTZ, NT = F::FNT;
     const int W = f.W, H = f.H, D = f.D;
     const int ntx = f.ntx(), nty = f.nty();
@@ -221,10 +221,10 @@ __global__ void __launch_bounds__(VolumetricFunctor<T>::FNT) k_volumetric_table(
         for (int k = 0; k < F::NP; ++k) rec[k * F::PLS] = v[k];
     }
 }
-template <class T> void VolumetricFunctor<T>::custom_precompute(cudaStream_t stream, int n_sm) const {
+template <class T, int UB> void VolumetricFunctor<T, UB>::custom_precompute(cudaStream_t stream, int n_sm) const {
     const long ntiles = (long)ntx() * nty() * ntz();
     const unsigned grid = (unsigned)(ntiles < (long)n_sm * 4 ? ntiles : (long)n_sm * 4);
-    k_volumetric_table<T><<<grid, dim3(32, FTY, FTZ), 0, stream>>>(*this);
+    k_volumetric_table<VolumetricFunctor<T, UB>><<<grid, dim3(32, FTY, FTZ), 0, stream>>>(*this);
 }
 
 

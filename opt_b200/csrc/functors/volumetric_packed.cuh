@@ -126,10 +126,10 @@ struct VolRing {
 
 template <bool FUSED, bool LM>
 __global__ void __launch_bounds__(256, 1)
-k_volumetric_apply_packed(VolumetricFunctor<float> f, Vec<float, 6> zv, Vec<float, 6> p, Vec<float, 6> p_new, Vec<float, 6> out,
+k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<float, 6> p, Vec<float, 6> p_new, Vec<float, 6> out,
                           Vec<float, 6> CtC, const unsigned char* __restrict__, const double* bNum, const double* aNum, double* den,
                           double* zero_a, double* zero_b) {
-    using F = VolumetricFunctor<float>;
+    using F = VolumetricFunctor<float, 6>;
     using G = VolRing;
     constexpr int TX = F::FTX, TY = G::TILEY, ZC = F::ZC, NS = G::NS, PL = 32;     // PL: plane / channel stride inside a stage row
     const int W = f.W, H = f.H, D = f.D;
@@ -408,11 +408,14 @@ k_volumetric_apply_packed(VolumetricFunctor<float> f, Vec<float, 6> zv, Vec<floa
     block_accumulate(dot, den);
 }
 
-template <class T> size_t VolumetricFunctor<T>::fast_smem() const { return use_packed() ? VolRing::SMEM : 0; }
+template <class T, int UB> size_t VolumetricFunctor<T, UB>::fast_smem() const { return UB > 0 ? VolRing::SMEM : 0; }
 
-template <class T> template <bool FUSED, bool LM> auto VolumetricFunctor<T>::fast_kernel() const {
-    if constexpr (sizeof(T) == 4) return &k_volumetric_apply_packed<FUSED, LM>;
+template <class T, int UB> template <bool FUSED, bool LM> auto VolumetricFunctor<T, UB>::fast_kernel() const {
+    if constexpr (UB > 0) return &k_volumetric_apply_packed<FUSED, LM>;
     else return &k_volumetric_apply<T, FUSED, LM>;
 }
+
+template <class T> using VolumetricPackedFunctor = VolumetricFunctor<T, 6>;
+template <class T> using VolumetricScalarFunctor = VolumetricFunctor<T, 0>;
 
 }  // namespace optk

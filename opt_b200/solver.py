@@ -32,6 +32,10 @@ def load_library():
         if not os.path.exists(LIB_PATH):
             raise RuntimeError("libOptB200.so is not built (run `python -m opt_b200.build`); "
                                "there is no fallback implementation")
+        try:                    # torch bundles its own NCCL; its symbols must be resolved before the system libnccl
+            import torch        # noqa: F401  that libOptB200.so links is mapped (undefined ncclDevCommCreate otherwise)
+        except ImportError:
+            pass
         _lib = C.CDLL(LIB_PATH)
         _fn = capi.bind(_lib, "Opt_")
         P = C.c_void_p

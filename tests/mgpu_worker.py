@@ -21,6 +21,9 @@ CASES = {
     "image_warping": (lambda: examples.image_warping_synthetic(48, 64, n_iter=3, l_iter=10), 1e-4, 1),
     "optical_flow_lm": (lambda: examples.optical_flow_synthetic(40, 60, n_iter=3, l_iter=12, kind="LMGPU"), 1e-4, 4),
     "volumetric": (lambda: examples.volumetric_synthetic(12, 10, 16, n_iter=2, l_iter=10), 1e-5, 1),
+    # rows of 32 sites: blocked solver vectors + packed kernel, ghost planes exchanged as one contiguous slice
+    "volumetric_packed": (lambda: examples.volumetric_synthetic(32, 11, 20, n_iter=2, l_iter=10), 1e-5, 1),
+    "volumetric_packed_lm": (lambda: examples.volumetric_synthetic(64, 6, 12, n_iter=3, l_iter=8), 1e-5, 1),
     "volumetric_lm_f64": (lambda: examples.volumetric_synthetic(8, 6, 12, n_iter=3, l_iter=12).as_double(), 1e-9, 1),
 }
 

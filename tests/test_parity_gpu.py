@@ -44,14 +44,15 @@ def test_solve_matches_oracle(built, case, kind, double):
     pr = make(case, kind, double)
     gc, gx, sol, _ = run_gpu(pr)
     rc, rx, _ = run_oracle(pr)
-    if case == "intrinsic" and not double:
+    if case == "intrinsic":
         # The L_p weights pow(|r_c - r_n| + 1e-7, pNorm - 2) are refreshed from the current r before every
         # nonlinear step (lib.t:112-121) and the albedo prior drives |r_c - r_n| towards 0, so from the second
-        # step on the weights amplify the fp32 rounding of r by 1.2 / |r_c - r_n|: two fp32 evaluations
-        # (powf on the GPU, std::pow here) agree to 1e-4 for the first step only; fp64 holds 1e-9 throughout.
-        assert_costs_close(gc[:2], rc[:2], False)
-        assert_costs_close(gc[2:], rc[2:], False, tol=2e-2)
-        assert_unknowns_close(gx, rx, False, tol=2e-2)
+        # step on the weights amplify the rounding of r (and the last-ulp differences between the device's and
+        # libm's pow) by 1.2 / |r_c - r_n|.  The first step holds BASELINE's gates (1e-4 fp32 / 1e-9 fp64); the
+        # re-weighted steps are held to 2e-2 (fp32) and 1e-7 (fp64).
+        assert_costs_close(gc[:2], rc[:2], double)
+        assert_costs_close(gc[2:], rc[2:], double, tol=1e-7 if double else 2e-2)
+        assert_unknowns_close(gx, rx, double, tol=1e-6 if double else 2e-2)
         return
     assert_costs_close(gc, rc, double)
     assert_unknowns_close(gx, rx, double)
@@ -91,7 +92,7 @@ def test_jtf_and_jtj_match_oracle(built, case, double):
     assert np.abs(ap_gpu - ap_ref).max() <= tol * np.abs(ap_ref).max()
 
 
-@pytest.mark.parametrize("case,double", [("volumetric_tiles", True), ("volumetric_packed", True), ("volumetric_packed", False)])
+@pytest.mark.parametrize("case,double", [("volumetric_tiles", False), ("volumetric_tiles", True), ("volumetric_packed", False), ("volumetric_packed", True)])
 def test_volumetric_tiled_jtj_equals_generic(built, case, double, monkeypatch):
     """The marching kernels (precomputed trig table; fp64 scalar, fp32 packed pairs fed by bulk copies) against the
     generic one-thread-per-site functor kernel: two different derivations of the same operator."""
@@ -108,6 +109,27 @@ def test_volumetric_tiled_jtj_equals_generic(built, case, double, monkeypatch):
     generic = sol.debug_apply_jtj(named, p)
     assert not np.array_equal(fast, generic)          # really two code paths
     assert np.abs(fast - generic).max() <= OP_RTOL[double] * np.abs(generic).max()
+
+
+def test_volumetric_packed_equals_scalar_marching_kernel(built, monkeypatch):
+    """fp32: the packed-pair kernel on blocked vectors against the scalar marching kernel on SoA vectors (the plan
+    picks the variant; OPTB200_VOL_SCALAR is read when the plan is made), GN and LM solves included."""
+    from opt_b200 import solver as S
+    pr = make("volumetric_packed")
+    rng = np.random.default_rng(3)
+    p = rng.standard_normal((int(np.prod(pr.dims)), 6)).astype(np.float32)
+    packed = S.OptSolver(pr.dims, pr.energy, pr.kind).debug_apply_jtj(S.upload(pr), p)
+    monkeypatch.setenv("OPTB200_VOL_SCALAR", "1")
+    scalar = S.OptSolver(pr.dims, pr.energy, pr.kind).debug_apply_jtj(S.upload(pr), p)
+    assert not np.array_equal(packed, scalar)
+    assert np.abs(packed - scalar).max() <= OP_RTOL[False] * np.abs(scalar).max()
+    for kind in ("gaussNewtonGPU", "LMGPU"):
+        q = make("volumetric_packed", kind)
+        cs, _, _, _ = run_gpu(q)
+        monkeypatch.delenv("OPTB200_VOL_SCALAR")
+        cp, _, _, _ = run_gpu(q)
+        monkeypatch.setenv("OPTB200_VOL_SCALAR", "1")
+        assert_costs_close(cp, cs, False)
 
 
 @pytest.mark.parametrize("double", [False, True])
