@@ -15,6 +15,12 @@ __device__ __forceinline__ void load4(const double* p, double* o) {
     double2 a = reinterpret_cast<const double2*>(p)[0], b = reinterpret_cast<const double2*>(p)[1];
     o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
 }
+// 4 consecutive elements, 16-byte aligned
+__device__ __forceinline__ void st4v(float* p, const float* v) { *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]); }
+__device__ __forceinline__ void st4v(double* p, const double* v) {
+    reinterpret_cast<double2*>(p)[0] = make_double2(v[0], v[1]);
+    reinterpret_cast<double2*>(p)[1] = make_double2(v[2], v[3]);
+}
 template <class T> __device__ __forceinline__ void load3(const T* p, T* o) { o[0] = p[0]; o[1] = p[1]; o[2] = p[2]; }
 
 // Rotate3D of lib.t:84-98 (Z-Y-X Euler angles a = (alpha,beta,gamma), row-major R) applied to u,

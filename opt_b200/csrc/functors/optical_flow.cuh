@@ -16,6 +16,26 @@ struct OpticalFlowFunctor : FunctorDefaults<T> {
     int W, H, D;
     T* X; const T* I; const T* Ih; const T* Idx; const T* Idy;
     T w_fit, w_reg;
+    // The Jacobian of the fit term, -w_f (Ihat_dx, Ihat_dy) sampled at x + X(x), only changes with X: it is sampled
+    // once per nonlinear iteration into two planes (precompute, like the reference's ComputedArrays) and the
+    // vectorised J^T J kernel below reads those instead of gathering 8 taps per site and PCG iteration.
+    T* GX = nullptr; T* GY = nullptr;
+    static constexpr bool HAS_PRECOMPUTE = true, HAS_FAST_APPLY = true;
+    void alloc_temporaries(cudaStream_t) {
+        const size_t n = (size_t)round_up((long)W * H, 64);
+        OPTK_CUDA(cudaMalloc(&GX, 2 * n * sizeof(T)));
+        GY = GX + n;
+    }
+    void free_temporaries() { cudaFree(GX); GX = GY = nullptr; }
+    __device__ void precompute(int x, int y, int, long s) const {
+        T xi[2]; load2(X + s * 2, xi);
+        const T px = (T)x + xi[0], py = (T)y + xi[1];
+        GX[s] = sample(Idx, px, py); GY[s] = sample(Idy, px, py);
+    }
+    bool fast_ok() const { return W % 4 == 0 && getenv("OPTB200_GENERIC_JTJ") == nullptr; }
+    long fast_tiles() const { return (long)((W / 4 + 31) / 32) * ((H + 7) / 8); }
+    dim3 fast_block() const { return dim3(32, 8, 1); }
+    template <bool FUSED, bool LM> static auto fast_kernel();
     void plan(const unsigned* d) { W = d[0]; H = d[1]; D = 1; }
     void bind(void** pp) {
         w_fit = (T) * (const float*)pp[0]; w_reg = (T) * (const float*)pp[1];
@@ -96,5 +116,97 @@ struct OpticalFlowFunctor : FunctorDefaults<T> {
         return sum;
     }
 };
+
+// ---------------------------------------------------------------------------------------------
+// Vectorised J^T J apply for optical_flow, optionally fused with PCGStep3 (p' = z + beta p, engine.cuh):
+//   (J^T J p)(i) = w_f^2 g_i (g_i . p_i) + 2 w_r^2 sum_{n in image} (p_i - p_n),   g_i = (GX, GY)(i) from precompute
+// Same structure as k_poisson_apply: a thread owns four consecutive pixels of a row, 128-bit loads for the centre /
+// upper / lower quads of both channel planes, lateral neighbours from the adjacent lanes by shuffle.
+template <class T, bool FUSED, bool LM>
+__global__ void __launch_bounds__(256) k_flow_apply(OpticalFlowFunctor<T> f, Vec<T> z, Vec<T> p, Vec<T> p_new, Vec<T> out, Vec<T> CtC,
+                                                    const unsigned char* __restrict__, const double* bNum, const double* aNum,
+                                                    double* den, double* zero_a, double* zero_b) {
+    const int W = f.W, H = f.H;
+    const int tiles_x = (W / 4 + 31) / 32;
+    const long ntiles = (long)tiles_x * ((H + 7) / 8);
+    const int lane = threadIdx.x;
+    const T wf2 = f.w_fit * f.w_fit, wr2 = T(2) * f.w_reg * f.w_reg;
+    T beta = T(0);
+    if (FUSED) beta = (T)(*bNum) / (T)(*aNum);
+    if (blockIdx.x == 0 && linear_tid() == 0) {
+        if (zero_a) *zero_a = 0.0;
+        if (zero_b) *zero_b = 0.0;
+    }
+    double acc = 0.0;
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int gx = ((int)(tile % tiles_x) * 32 + lane) * 4;
+        const int y = (int)(tile / tiles_x) * 8 + threadIdx.y;
+        const bool in_img = gx < W && y < H;
+        const bool own = in_img && y >= f.o_lo && y < f.o_hi;
+        const long s = (long)y * W + gx;
+        const bool up = y > 0, dn = y + 1 < H;
+        T pv[2][4], lap[2][4];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const T* pc = p.d + (long)c * p.plane;
+            const T* zc = z.d + (long)c * z.plane;
+            auto dirq = [&](long at, T* o) {                 // direction at a quad
+                T a[4]; load4(pc + at, a);
+                if (FUSED) { T b[4]; load4(zc + at, b);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) o[j] = b[j] + beta * a[j];
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) o[j] = a[j];
+                }
+            };
+            auto dir1 = [&](long at) -> T { return FUSED ? zc[at] + beta * pc[at] : pc[at]; };
+            T* ctr = pv[c];
+            ctr[0] = ctr[1] = ctr[2] = ctr[3] = T(0);
+            if (in_img) dirq(s, ctr);
+            T lft = __shfl_up_sync(0xffffffffu, ctr[3], 1);
+            T rgt = __shfl_down_sync(0xffffffffu, ctr[0], 1);
+            if (own) {
+                if (lane == 0) lft = gx > 0 ? dir1(s - 1) : T(0);
+                if (lane == 31) rgt = gx + 4 < W ? dir1(s + 4) : T(0);
+                T u4[4] = {T(0), T(0), T(0), T(0)}, d4[4] = {T(0), T(0), T(0), T(0)};
+                if (up) dirq(s - W, u4);
+                if (dn) dirq(s + W, d4);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const T v = ctr[j];
+                    T a = T(0);
+                    if (gx + j + 1 < W) a += v - (j < 3 ? ctr[j + 1] : rgt);
+                    if (gx + j > 0) a += v - (j > 0 ? ctr[j - 1] : lft);
+                    if (dn) a += v - d4[j];
+                    if (up) a += v - u4[j];
+                    lap[c][j] = a;
+                }
+            }
+        }
+        if (own) {
+            T g0[4], g1[4], o0[4], o1[4];
+            load4(f.GX + s, g0); load4(f.GY + s, g1);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const T jp = g0[j] * pv[0][j] + g1[j] * pv[1][j];
+                o0[j] = wf2 * g0[j] * jp + wr2 * lap[0][j];
+                o1[j] = wf2 * g1[j] * jp + wr2 * lap[1][j];
+            }
+            if (LM) {
+                T c0[4], c1[4]; load4(CtC.d + s, c0); load4(CtC.d + CtC.plane + s, c1);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { o0[j] += c0[j] * pv[0][j]; o1[j] += c1[j] * pv[1][j]; }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc += (double)(pv[0][j] * o0[j] + pv[1][j] * o1[j]);
+            if (FUSED) { st4v(p_new.d + s, pv[0]); st4v(p_new.d + p_new.plane + s, pv[1]); }
+            st4v(out.d + s, o0); st4v(out.d + out.plane + s, o1);
+        }
+    }
+    block_accumulate(acc, den);
+}
+
+template <class T> template <bool FUSED, bool LM> auto OpticalFlowFunctor<T>::fast_kernel() { return &k_flow_apply<T, FUSED, LM>; }
 
 }  // namespace optk

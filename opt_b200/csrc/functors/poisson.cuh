@@ -90,11 +90,6 @@ struct PoissonFunctor : FunctorDefaults<T> {
 // 31 touch memory for them).  ~2 LDG.128 per pixel instead of 25 scalar loads: the generic kernel
 // was LSU-issue bound at 2.3 TB/s (profiles/r1_a).  Quads without unknowns are skipped via active4.
 template <class T> __device__ __forceinline__ void ld4v(const T* p, T* o) { load4(p, o); }
-__device__ __forceinline__ void st4v(float* p, const float* v) { *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]); }
-__device__ __forceinline__ void st4v(double* p, const double* v) {
-    reinterpret_cast<double2*>(p)[0] = make_double2(v[0], v[1]);
-    reinterpret_cast<double2*>(p)[1] = make_double2(v[2], v[3]);
-}
 
 template <class T, bool FUSED, bool LM>
 __global__ void __launch_bounds__(256) k_poisson_apply(PoissonFunctor<T> f, Vec<T> z, Vec<T> p, Vec<T> p_new, Vec<T> out,
