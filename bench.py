@@ -65,6 +65,17 @@ WORKLOADS = {
 }
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the `ncu --set full`
+# captures summarised under profiles/ (README there): workload -> (bytes, capture)
+NCU_TRAFFIC = {}
+
+
+def load_traffic():
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(path):
+        NCU_TRAFFIC.update(json.load(open(path)))
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -132,6 +143,10 @@ def make_problem(name, size=None, rank=0, world=1):
     return w["builder"](*args, **w["kw"]), w, None
 
 
+def sz_of(pr):
+    return 8 if pr.double else 4
+
+
 def pcg_iterations(pr):
     return int(pr.solver["nIterations"]) * int(pr.solver["lIterations"])
 
@@ -187,8 +202,8 @@ def run_reference(args, pr, w):
         "impl": "reference", "metric": "pcg_iterations_per_second", "value": rate, "unit": "PCG iters/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1000.0 * pcg_iterations(pr) / rate, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": w["desc"], "dims": pr.dims, "timing": "host wall clock", "wall_s": wall},
+        "vs_baseline": None, "dtype": "f64" if pr.double else "f32", "data": "synthetic",
+        "config": {"workload": w["desc"], "dims": pr.dims, "solver": pr.kind, "timing": "host wall clock", "wall_s": wall},
         "cpu_baseline": {"value": rate, "unit": "PCG iters/s", "cores": threads, "kind": "port", "sample": samples[0]},
         "e2e": {"value": rate, "unit": "PCG iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -310,7 +325,10 @@ def run_ours(args, pr, w, rank, world, mode):
             it_rate = iters * args.steps / (ms * 1e-3)
             it_survey = sz * N * (iter_words + 3 * w["iexcl"]) + w["extra"] * N
             roof = {"bound": "hbm", "kernel": "PCGStep3+PCGStep1 (fused)" if fused else "PCGStep1",
-                    "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                    "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                    "traffic": (NCU_TRAFFIC.get(args.workload + ("_f64" if pr.double else "")) or {}).get("bytes_per_launch") if world == 1 and not args.size else None,
+                    "traffic_source": (NCU_TRAFFIC.get(args.workload + ("_f64" if pr.double else "")) or {}).get("capture"),
+                    "frac_of_nominal_8TBs": ach / 8000.0,
                     "peak_source": peak_src, "algorithmic_bytes_per_launch": alg, "ms_per_launch": per_launch_ms,
                     "active_sites": n_act, "sites": N,
                     "kernel_ms": {k: (v[1] / v[0] if v[0] else None) for k, v in kt.items()},
@@ -335,8 +353,8 @@ def run_ours(args, pr, w, rank, world, mode):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "strong" if mode == "strong" else "weak", "vs_baseline": None,
         "dtype": "f32" if not pr.double else "f64", "data": "synthetic",
-        "config": {"workload": w["desc"], "dims": pr.dims, "pcg_iterations_per_step": iters,
-                   "l2": "inputs larger than L2 (each solver vector is %.0f MB)" % (w["U"] * sol.site_count() * 4 / 1e6),
+        "config": {"workload": w["desc"], "dims": pr.dims, "solver": pr.kind, "pcg_iterations_per_step": iters,
+                   "l2": "inputs larger than L2 (each solver vector is %.0f MB)" % (w["U"] * sol.site_count() * sz_of(pr) / 1e6),
                    "final_cost": cost, "parallelism": "1 GPU" if world == 1 else ("%d ranks, %s" % (world, (
                        "slab decomposition along the slowest dim (%s scaling), NCCL halo exchange + all-reduced PCG scalars" % mode)
                        if mode else "independent replicas"))},
@@ -359,17 +377,26 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="poisson_4096", choices=sorted(WORKLOADS))
     ap.add_argument("--size", type=int, nargs="+", default=None, help="override the workload's grid size")
+    ap.add_argument("--double", action="store_true", help="run the workload in fp64 (doublePrecision = 1)")
+    ap.add_argument("--kind", default=None, choices=["gaussNewtonGPU", "LMGPU"], help="override the workload's solver kind")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
     args = ap.parse_args()
+    load_traffic()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
+    def variant(pr):
+        if args.kind:
+            pr.kind = args.kind
+        return pr.as_double() if args.double else pr
+
     if args.impl == "reference":
         if rank == 0:
             pr, w, _ = make_problem(args.workload, args.size)
-            run_reference(args, pr, w)
+            run_reference(args, variant(pr), w)
         return
     pr, w, mode = make_problem(args.workload, args.size, rank, world)
+    pr = variant(pr)
     if world > 1:
         import torch
         import torch.distributed as dist
