@@ -145,48 +145,48 @@ __global__ void __launch_bounds__(256) k_flow_apply(OpticalFlowFunctor<T> f, Vec
         const bool own = in_img && y >= f.o_lo && y < f.o_hi;
         const long s = (long)y * W + gx;
         const bool up = y > 0, dn = y + 1 < H;
-        T pv[2][4], lap[2][4];
+        // Phase 1: issue every load of the tile before anything is consumed (latency-bound kernel, see k_poisson_apply)
+        T pv[2][4], u4[2][4], d4[2][4], lmem[2], rmem[2], g0[4] = {T(0), T(0), T(0), T(0)}, g1[4] = {T(0), T(0), T(0), T(0)};
+        const bool ledge = own && lane == 0 && gx > 0, redge = own && lane == 31 && gx + 4 < W;
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
             const T* pc = p.d + (long)c * p.plane;
             const T* zc = z.d + (long)c * z.plane;
-            auto dirq = [&](long at, T* o) {                 // direction at a quad
-                T a[4]; load4(pc + at, a);
-                if (FUSED) { T b[4]; load4(zc + at, b);
+            auto dirq = [&](bool on, long at, T* o) {          // direction at a quad (0 when not loaded)
+                T a[4] = {T(0), T(0), T(0), T(0)}, b[4] = {T(0), T(0), T(0), T(0)};
+                if (on) { load4(pc + at, a); if (FUSED) load4(zc + at, b); }
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) o[j] = b[j] + beta * a[j];
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) o[j] = a[j];
-                }
+                for (int j = 0; j < 4; ++j) o[j] = FUSED ? b[j] + beta * a[j] : a[j];
             };
-            auto dir1 = [&](long at) -> T { return FUSED ? zc[at] + beta * pc[at] : pc[at]; };
-            T* ctr = pv[c];
-            ctr[0] = ctr[1] = ctr[2] = ctr[3] = T(0);
-            if (in_img) dirq(s, ctr);
-            T lft = __shfl_up_sync(0xffffffffu, ctr[3], 1);
-            T rgt = __shfl_down_sync(0xffffffffu, ctr[0], 1);
-            if (own) {
-                if (lane == 0) lft = gx > 0 ? dir1(s - 1) : T(0);
-                if (lane == 31) rgt = gx + 4 < W ? dir1(s + 4) : T(0);
-                T u4[4] = {T(0), T(0), T(0), T(0)}, d4[4] = {T(0), T(0), T(0), T(0)};
-                if (up) dirq(s - W, u4);
-                if (dn) dirq(s + W, d4);
+            auto dir1 = [&](bool on, long at) -> T { return on ? (FUSED ? zc[at] + beta * pc[at] : pc[at]) : T(0); };
+            dirq(in_img, s, pv[c]);
+            dirq(own && up, s - W, u4[c]);
+            dirq(own && dn, s + W, d4[c]);
+            lmem[c] = dir1(ledge, s - 1);
+            rmem[c] = dir1(redge, s + 4);
+        }
+        if (own) { load4(f.GX + s, g0); load4(f.GY + s, g1); }
+        // Phase 2
+        T lap[2][4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const T v = ctr[j];
-                    T a = T(0);
-                    if (gx + j + 1 < W) a += v - (j < 3 ? ctr[j + 1] : rgt);
-                    if (gx + j > 0) a += v - (j > 0 ? ctr[j - 1] : lft);
-                    if (dn) a += v - d4[j];
-                    if (up) a += v - u4[j];
-                    lap[c][j] = a;
-                }
+        for (int c = 0; c < 2; ++c) {
+            T lft = __shfl_up_sync(0xffffffffu, pv[c][3], 1);
+            T rgt = __shfl_down_sync(0xffffffffu, pv[c][0], 1);
+            if (lane == 0) lft = lmem[c];
+            if (lane == 31) rgt = rmem[c];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const T v = pv[c][j];
+                T a = T(0);
+                if (gx + j + 1 < W) a += v - (j < 3 ? pv[c][j + 1] : rgt);
+                if (gx + j > 0) a += v - (j > 0 ? pv[c][j - 1] : lft);
+                if (dn) a += v - d4[c][j];
+                if (up) a += v - u4[c][j];
+                lap[c][j] = a;
             }
         }
         if (own) {
-            T g0[4], g1[4], o0[4], o1[4];
-            load4(f.GX + s, g0); load4(f.GY + s, g1);
+            T o0[4], o1[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const T jp = g0[j] * pv[0][j] + g1[j] * pv[1][j];

@@ -137,17 +137,23 @@ __global__ void __launch_bounds__(256) k_poisson_apply(PoissonFunctor<T> f, Vec<
             }
         };
         auto dir1 = [&](long at) -> T { return FUSED ? zc[at] + beta * pc[at] : pc[at]; };
-        T ctr[4] = {T(0), T(0), T(0), T(0)};
+        // all loads of the channel are issued before the shuffles consume the centre quad: one exposed memory
+        // latency per channel instead of two (the kernel is latency-bound, ncu r1i)
+        T ctr[4] = {T(0), T(0), T(0), T(0)}, u4[4] = {T(0), T(0), T(0), T(0)}, d4[4] = {T(0), T(0), T(0), T(0)};
+        T lmem = T(0), rmem = T(0);
         if (act) dirq(s, ctr);
+        if (act && own) {
+            if (up) dirq(s - W, u4);
+            if (dn) dirq(s + W, d4);
+            if (lane == 0 && gx > 0) lmem = dir1(s - 1);
+            if (lane == 31 && gx + 4 < W) rmem = dir1(s + 4);
+        }
         // lateral neighbours: from the adjacent lanes, from memory at the warp's ends
         T lft = __shfl_up_sync(0xffffffffu, ctr[3], 1);
         T rgt = __shfl_down_sync(0xffffffffu, ctr[0], 1);
         if (act && own) {
-            if (lane == 0) lft = gx > 0 ? dir1(s - 1) : T(0);
-            if (lane == 31) rgt = gx + 4 < W ? dir1(s + 4) : T(0);
-            T u4[4] = {T(0), T(0), T(0), T(0)}, d4[4] = {T(0), T(0), T(0), T(0)};
-            if (up) dirq(s - W, u4);
-            if (dn) dirq(s + W, d4);
+            if (lane == 0) lft = lmem;
+            if (lane == 31) rgt = rmem;
             T o[4], pn[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
