@@ -349,6 +349,121 @@ def intrinsic_synthetic(W, H, seed=1234, n_iter=3, l_iter=10, kind="gaussNewtonG
                    {"nIterations": n_iter, "lIterations": l_iter}, kind=kind, opt_float_scalars=[3])
 
 
+def intrinsic_golden(npz, n_iter=1, l_iter=1):
+    """The reference's golden run of intrinsic_image_decomposition (examples/test_final_cost.py:60,81: stride 12):
+    src/main.cpp:28-39 (strided copy) and src/CombinedSolver.h:33-46, 68-108 (weights, log2 initialisation)."""
+    f32 = np.float32
+    v = npz["rgb"].astype(f32) / f32(255.0)
+    intensity = (v[..., 0] + v[..., 1] + v[..., 2]) / f32(3.0)
+    eps = f32(0.01)
+    img = np.log2(v + eps).astype(f32)
+    r = np.log2(v / intensity[..., None] + eps).astype(f32)
+    s = np.log2(intensity + eps).astype(f32)
+    H, W = s.shape
+    w = [np.sqrt(f32(500.0)), np.sqrt(f32(1000.0)), np.sqrt(f32(10000.0))]
+    return Problem("intrinsic_image_decomposition.t", [W, H], w + [f32(0.8), r, img, s], [4, 6],
+                   {"nIterations": n_iter, "lIterations": l_iter}, opt_float_scalars=[3])
+
+
+def _filter_gaussian(img, sigma):
+    """examples/optical_flow/src/ImageHelper.h:68-114: separable, kernel radius ceil(2 sigma), renormalised at the border."""
+    f32 = np.float32
+    R = int(np.ceil(2.0 * sigma))
+    k = np.exp(-((np.arange(R + 1, dtype=f32) ** 2) / f32(2.0 * sigma * sigma))).astype(f32)
+
+    def one_pass(im, axis):
+        n = im.shape[axis]
+        out = np.zeros_like(im)
+        for i in range(n):
+            v = np.zeros(np.delete(im.shape, axis), dtype=f32)
+            w = f32(0)
+            for kk in range(-R, R + 1):
+                j = i + kk
+                if 0 <= j < n:
+                    v = v + k[abs(kk)] * np.take(im, j, axis=axis)
+                    w = f32(w + k[abs(kk)])
+            v = v / w
+            if axis == 1:
+                out[:, i] = v
+            else:
+                out[i, :] = v
+        return out
+    return one_pass(one_pass(img.astype(f32), 1), 0)
+
+
+def _prewitt8(im, horizontal):
+    """computeDU / computeDV, examples/optical_flow/src/CombinedSolver.h:152-178 (zero on the border)."""
+    f32 = np.float32
+    r = np.zeros_like(im)
+    if horizontal:
+        r[1:-1, 1:-1] = (-im[:-2, :-2] - im[1:-1, :-2] - im[2:, :-2] + im[:-2, 2:] + im[1:-1, 2:] + im[2:, 2:]) / f32(8.0)
+    else:
+        r[1:-1, 1:-1] = (-im[:-2, :-2] - im[:-2, 1:-1] - im[:-2, 2:] + im[2:, :-2] + im[2:, 1:-1] + im[2:, 2:]) / f32(8.0)
+    return r
+
+
+def optical_flow_golden(npz, n_iter=1, l_iter=1):
+    """The FIRST solve of the reference's golden run of optical_flow (test_final_cost.py:62, stride 16, oIterations 1):
+    the coarse level of the driver's 2-level pyramid (sigma = 5, CombinedSolver.h:25-37, solved first :47-66) with zero
+    flow, fit weight 10 + (50 - 10) / (1 * 2) = 30 (:69-93) and regularisation weight 0.1."""
+    f32 = np.float32
+    S, T = _filter_gaussian(npz["source"], 5.0), _filter_gaussian(npz["target"], 5.0)
+    H, W = S.shape
+    X = np.zeros((H, W, 2), dtype=f32)
+    return Problem("optical_flow.t", [W, H], [np.sqrt(f32(30.0)), np.sqrt(f32(0.1)), X, S, T, _prewitt8(T, True), _prewitt8(T, False)],
+                   [2], {"nIterations": n_iter, "lIterations": l_iter})
+
+
+# ---------------------------------------------------------------------------------------------
+# mesh drivers: connectivity the reference derives with OpenMesh, restated on plain index arrays
+def _vertex_edges(nv, faces):
+    """Directed edge lists (v0, v1): for every vertex, all of its one-ring neighbours.  The graph energies sum over
+    edges, so the order inside a ring is immaterial for the cost; ascending is used here
+    (examples/*/src/CombinedSolver.h: the vv_iter loops that fill the edge lists)."""
+    nbr = [set() for _ in range(nv)]
+    for f in faces:
+        k = len(f)
+        for a in range(k):
+            x, y = int(f[a]), int(f[(a + 1) % k])
+            nbr[x].add(y)
+            nbr[y].add(x)
+    v0 = [a for a in range(nv) for _ in nbr[a]]
+    v1 = [b for a in range(nv) for b in sorted(nbr[a])]
+    return np.array(v0, dtype=np.int32), np.array(v1, dtype=np.int32)
+
+
+def _vertex_rings(nv, faces):
+    """One-ring of every vertex in rotation order (what a half-edge circulator walks); an open fan is walked from
+    one boundary end to the other."""
+    succ = [dict() for _ in range(nv)]   # at vertex a: succ[a][b] = c for every oriented face (a, b, c)
+    for a, b, c in faces:
+        a, b, c = int(a), int(b), int(c)
+        succ[a][b] = c
+        succ[b][c] = a
+        succ[c][a] = b
+    rings = []
+    for a in range(nv):
+        s = succ[a]
+        if not s:
+            rings.append([])
+            continue
+        preds = set(s.values())
+        starts = [b for b in s if b not in preds]
+        start = starts[0] if starts else next(iter(s))
+        ring, cur = [start], start
+        while cur in s and s[cur] != start and len(ring) <= len(s) + 1:
+            cur = s[cur]
+            ring.append(cur)
+        rings.append(ring)
+    return rings
+
+
+def _marker_constraints(nv, npz):
+    cons = np.full((nv, 3), -np.inf, dtype=np.float32)
+    cons[npz["marker_vertex"]] = npz["marker_pos"].astype(np.float32)
+    return cons
+
+
 def grid_mesh_edges(nx, ny):
     """Directed edges of a regular height-field triangulation, both directions of every mesh
     edge, sorted by head vertex (the order examples/shared/OptGraph.h:78-89 produces)."""
@@ -379,3 +494,124 @@ def arap_synthetic(nx, ny, seed=1234, n_iter=2, l_iter=10):
     return Problem("arap_mesh_deformation.t", [n, len(v0)],
                    [w_fit, w_reg, offset, angle, ur, cons, ecount, v0, v1], [2, 3],
                    {"nIterations": n_iter, "lIterations": l_iter})
+
+
+# ---------------------------------------------------------------------------------------------
+# mesh goldens (examples/test_final_cost.py:56-66; inputs stored by tools/make_golden.py)
+def cotangent_golden(npz, n_iter=1, l_iter=1):
+    """cotangent_mesh_smoothing on head.ply: examples/cotangent_mesh_smoothing/src/CombinedSolver.h:66-135 (every
+    directed edge (head, tail) carries the ring neighbours before and after the tail), weights 1.0 / 0.5 (:18-19)."""
+    f32 = np.float32
+    v = npz["vertices"].astype(f32)
+    head, tail, prev, nxt = [], [], [], []
+    for a, ring in enumerate(_vertex_rings(len(v), npz["faces"])):
+        n = len(ring)
+        for i, c in enumerate(ring):
+            head.append(a)
+            tail.append(c)
+            prev.append(ring[(i + n - 1) % n])
+            nxt.append(ring[(i + 1) % n])
+    g = [np.array(x, dtype=np.int32) for x in (head, tail, prev, nxt)]
+    E = len(head)
+    return Problem("cotangent_mesh_smoothing.t", [len(v), E],
+                   [np.sqrt(f32(1.0)), np.sqrt(f32(0.5)), v.copy(), v.copy(), np.array([E], dtype=np.int32)] + g, [2],
+                   {"nIterations": n_iter, "lIterations": l_iter})
+
+
+def _rotation_deg(axis, deg):
+    """mLib matrix3x3.h:127-174 (rotationX/Y/Z of an angle in degrees, float arithmetic)."""
+    f32 = np.float32
+    a = f32(f32(deg) * f32(np.pi) / f32(180.0))
+    s, c = f32(np.sin(a)), f32(np.cos(a))
+    if axis == "x":
+        return np.array([[1, 0, 0], [0, c, -s], [0, s, c]], dtype=f32)
+    if axis == "y":
+        return np.array([[c, 0, s], [0, 1, 0], [-s, 0, c]], dtype=f32)
+    return np.array([[c, -s, 0], [s, c, 0], [0, 0, 1]], dtype=f32)
+
+
+def embedded_golden(npz, n_iter=1, l_iter=1):
+    """embedded_mesh_deformation on raptor_simplify2k: examples/embedded_mesh_deformation/src/CombinedSolver.h:34-160
+    (weights 3 / 12 / 5 at :39-41, rotations start as R_y R_x R_z of 1e-3 degrees, unconstrained vertices = -inf)."""
+    f32 = np.float32
+    v = npz["vertices"].astype(f32)
+    nv = len(v)
+    v0, v1 = _vertex_edges(nv, npz["faces"])
+    R = (_rotation_deg("y", 1e-3) @ _rotation_deg("x", 1e-3) @ _rotation_deg("z", 1e-3)).astype(f32)
+    rots = np.tile(R.reshape(1, 9), (nv, 1)).astype(f32)
+    E = len(v0)
+    return Problem("embedded_mesh_deformation.t", [nv, E],
+                   [np.sqrt(f32(3.0)), np.sqrt(f32(12.0)), np.sqrt(f32(5.0)), v.copy(), rots, v.copy(),
+                    _marker_constraints(nv, npz), np.array([E], dtype=np.int32), v0, v1], [3, 4],
+                   {"nIterations": n_iter, "lIterations": l_iter})
+
+
+def sqrt3_subdivide(v, faces):
+    """One step of Kobbelt's sqrt(3) subdivision on a closed triangle mesh, as the reference's ARAP driver applies it
+    before solving (examples/arap_mesh_deformation/src/main.cpp:65-81, OpenMesh Sqrt3T with numSubdivides = 1):
+    old vertices relax towards their ring average with alpha(n) = (4 - 2 cos(2 pi / n)) / 9, a new vertex is
+    inserted at every face centroid (of the un-relaxed positions), and every old edge is flipped so that it joins the
+    two centroids next to it.  Returns the positions (old vertices first, then one per face) and, for every
+    vertex, the set of its neighbours in the subdivided mesh."""
+    f32 = np.float32
+    v = v.astype(f32)
+    nv = len(v)
+    edge_faces = {}
+    for fi, (a, b, c) in enumerate(faces):
+        for x, y in ((a, b), (b, c), (c, a)):
+            edge_faces.setdefault((min(int(x), int(y)), max(int(x), int(y))), []).append(fi)
+    if any(len(l) != 2 for l in edge_faces.values()):
+        raise ValueError("sqrt3_subdivide: closed manifold meshes only")
+    ring = [set() for _ in range(nv)]
+    for x, y in edge_faces:
+        ring[x].add(y)
+        ring[y].add(x)
+    relaxed = v.copy()
+    for a in range(nv):
+        k = len(ring[a])
+        alpha = (4.0 - 2.0 * np.cos(2.0 * np.pi / k)) / 9.0
+        acc = np.zeros(3, dtype=f32)
+        for b in ring[a]:
+            acc = acc + v[b]
+        relaxed[a] = acc * f32(alpha / k) + f32(1.0 - alpha) * v[a]
+    cent = np.empty((len(faces), 3), dtype=f32)
+    for fi, (a, b, c) in enumerate(faces):
+        cent[fi] = ((v[a] + v[b]) + v[c]) / f32(3.0)
+    adj = [set() for _ in range(nv + len(faces))]
+    for fi, f in enumerate(faces):
+        for x in f:
+            adj[nv + fi].add(int(x))
+            adj[int(x)].add(nv + fi)
+    for l in edge_faces.values():
+        adj[nv + l[0]].add(nv + l[1])
+        adj[nv + l[1]].add(nv + l[0])
+    return np.concatenate([relaxed, cent], 0), adj
+
+
+def arap_golden(npz, n_iter=1, l_iter=1):
+    """arap_mesh_deformation on small_armadillo after one sqrt(3) subdivision: examples/arap_mesh_deformation/src/
+    main.cpp:45-81 and CombinedSolver.h:23-24 (weights 4 / 1), :84-135 (angles start at 0.1, offsets = rest shape =
+    subdivided positions, marker vertices constrained, everything else -inf)."""
+    f32 = np.float32
+    P, adj = sqrt3_subdivide(npz["vertices"], npz["faces"])
+    n = len(P)
+    v0 = np.array([a for a in range(n) for _ in adj[a]], dtype=np.int32)
+    v1 = np.array([b for a in range(n) for b in sorted(adj[a])], dtype=np.int32)
+    E = len(v0)
+    return Problem("arap_mesh_deformation.t", [n, E],
+                   [np.sqrt(f32(4.0)), np.sqrt(f32(1.0)), P.copy(), np.full((n, 3), 1e-1, dtype=f32), P.copy(),
+                    _marker_constraints(n, npz), np.array([E], dtype=np.int32), v0, v1], [2, 3],
+                   {"nIterations": n_iter, "lIterations": l_iter})
+
+
+def poisson_golden(npz, n_iter=1, l_iter=1):
+    """poisson_image_editing at stride 4 (test_final_cost.py:61,82): examples/poisson_image_editing/src/
+    CombinedSolver.h:70-93 (alpha forced to 255; mask 0 = unknown where the driver's mask image reads 255).  The mask
+    in the fixture is the one the driver effectively derives, see tools/make_golden.py:poisson."""
+    f32 = np.float32
+    H, W = (int(t) for t in npz["shape"])
+    unknown = np.unpackbits(npz["unknown"])[:H * W].reshape(H, W).astype(bool)
+    X = np.concatenate([npz["image"].astype(f32), np.full((H, W, 1), 255, dtype=f32)], -1)
+    T = np.concatenate([npz["target"].astype(f32), np.full((H, W, 1), 255, dtype=f32)], -1)
+    M = np.where(unknown, 0, 255).astype(f32)
+    return Problem("poisson_image_editing.t", [W, H], [X, T, M], [0], {"nIterations": n_iter, "lIterations": l_iter})

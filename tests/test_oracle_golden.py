@@ -11,6 +11,12 @@ from oracle_api import OracleSolver
 GOLDEN = [
     ("image_warping_cat512.npz", examples.image_warping_golden),
     ("volumetric_head.npz", examples.volumetric_golden),
+    ("intrinsic_ye_high2_stride12.npz", examples.intrinsic_golden),
+    ("optical_flow_dogdance_stride16.npz", examples.optical_flow_golden),
+    ("cotangent_head.npz", examples.cotangent_golden),
+    ("embedded_raptor2k.npz", examples.embedded_golden),
+    ("arap_small_armadillo.npz", examples.arap_golden),
+    ("poisson_stride4.npz", examples.poisson_golden),
 ]
 
 
