@@ -855,7 +855,14 @@ struct Engine : OptK_Plan {
         if (nIter == 0 && use_gather()) build_incidence();
         if (F::HAS_EXCLUDE)                                 // Exclude() may read inputs the caller changed
             this->launch("activeGroups", dim3((unsigned)((Npad / 4 + 255) / 256)), dim3(256), k_active4<F>, f, Npad / 4, active4);
-        this->launch_tiles("PCGInit1", tg.n, sblock, k_pcg_init1<F>, f, tg, delta, r, p, pre, S(S_RZ0));
+        bool fast_init = false;
+        if constexpr (F::HAS_FAST_INIT) {
+            if (f.fast_ok()) {
+                this->launch_tiles_smem("PCGInit1", f.fast_tiles(), f.fast_block(), f.fast_smem(), f.fast_init_kernel(), f, delta, r, p, pre, S(S_RZ0));
+                fast_init = true;
+            }
+        }
+        if (!fast_init) this->launch_tiles("PCGInit1", tg.n, sblock, k_pcg_init1<F>, f, tg, delta, r, p, pre, S(S_RZ0));
         if (GRAPH) {
             this->launch("PCGInit1_Graph", edge_grid(), dim3(256), k_graph_jtf<F>, f, E, r, pre);
             this->launch_tiles("PCGInit1_Finish", tg.n, sblock, k_pcg_init1_finish<F>, f, tg, r, pre, p, S(S_RZ0));
@@ -998,6 +1005,7 @@ struct FunctorDefaults {
     static constexpr bool HAS_CUSTOM_PRECOMPUTE = false; // precompute is a functor-launched kernel (own table layout)
     static constexpr bool HAS_EXCLUDE = false;           // functors with an Exclude() override this
     static constexpr bool HAS_FAST_APPLY = false;        // functors with a specialised J^T J kernel override this
+    static constexpr bool HAS_FAST_INIT = false;         // ... and with a specialised PCGInit1 (fast_init_kernel())
     static constexpr bool SLAB_OK = true;                // grid functors whose bounds predicates survive a slab cut
     static constexpr bool HAS_GATHER = false;            // graph functors with a per-vertex gather form of J^T J p
     static constexpr int VEC_UB = 0;                     // solver-vector layout: 0 = SoA, U = blocked (common.cuh, Vec)

@@ -23,21 +23,32 @@ template <class T>
 struct SfsFunctor : FunctorDefaults<T> {
     using Scalar = T;
     static constexpr int U = 1, ND = 2;
-    static constexpr bool USE_PRE = false, HAS_EXCLUDE = true, HAS_PRECOMPUTE = true, FUSE_STEP3 = false;
+    static constexpr bool USE_PRE = false, HAS_EXCLUDE = true, HAS_PRECOMPUTE = true;
     static constexpr bool SLAB_OK = false;     // the expanded-bounds predicates would need global row numbers
-    // tiled J^T J apply (k_sfs_apply below): J p per residual once per pixel in shared memory, then J^T
+    // marching J^T J apply (k_sfs_march below): a warp owns a strip of STRIP written pixels and a band of bandR rows
     static constexpr bool HAS_FAST_APPLY = true;
-    static constexpr int FTW = 32, FTH = 16;
-    bool fast_ok() const { return getenv("OPTB200_GENERIC_JTJ") == nullptr; }
-    long fast_tiles() const { return (long)((W + FTW - 1) / FTW) * ((H + FTH - 1) / FTH); }
+    static constexpr int STRIP = 120;
+    int bandR = 16;
+    bool fast_ok() const { return W % 4 == 0 && getenv("OPTB200_GENERIC_JTJ") == nullptr; }
+    __host__ __device__ int strips() const { return (W + STRIP - 1) / STRIP; }
+    long fast_tiles() const { return ((long)strips() * ((H + bandR - 1) / bandR) + 7) / 8; }
     dim3 fast_block() const { return dim3(32, 8, 1); }
     template <bool FUSED, bool LM> static auto fast_kernel();
-    __device__ long fast_tiles_dev() const { return (long)((W + FTW - 1) / FTW) * ((H + FTH - 1) / FTH); }
+    static constexpr bool HAS_FAST_INIT = true;        // PCGInit1 by the same pipeline (k_sfs_init)
+    static auto fast_init_kernel();
+    size_t fast_smem() const;
     int W, H, D;
     T* X; const T* Di; const T* Im; const unsigned char* mR; const unsigned char* mC;
     T w_p, w_s, w_g, f_x, f_y, u_x, u_y, L[9];
     T* BI = nullptr; T* G0 = nullptr; T* G1 = nullptr; T* G2 = nullptr; unsigned char* valid = nullptr;
-    void plan(const unsigned* d) { W = d[0]; H = d[1]; D = 1; }
+    void plan(const unsigned* d) {
+        W = d[0]; H = d[1]; D = 1;
+        // all (strip, band) items resident at once: 8 warps per CTA, 2 CTAs per SM in fp32, 1 in fp64
+        int dev = 0, nsm = 148;
+        cudaGetDevice(&dev); cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+        const long slots = (long)nsm * 8 * (sizeof(T) == 4 ? 2 : 1);
+        bandR = (int)std::min<long>(256, std::max<long>(8, ((long)H * strips() + slots - 1) / slots));
+    }
     void bind(void** pp) {
         // sqrt(Param(...)): the float parameter is cast to opt_float, then the square root is taken (o.t:2430)
         w_p = std::sqrt((T) * (const float*)pp[0]); w_s = std::sqrt((T) * (const float*)pp[1]); w_g = std::sqrt((T) * (const float*)pp[2]);
@@ -240,109 +251,293 @@ struct SfsFunctor : FunctorDefaults<T> {
     }
 };
 
+
 // ---------------------------------------------------------------------------------------------
-// Tiled J^T J apply for shape_from_shading.  The per-site functor form above is a gather of gathers: every site
-// re-evaluates J p of the 10 shading residuals and 5 regularisation residuals that touch it (~200 loads and a dozen
-// divisions per site; 0.47 ms for 2048^2, 5 % of the HBM roofline).  Here a 32 x 16 tile does it in three
-// shared-memory stages, each quantity once per pixel:
-//   1. p on the tile + 2 halo pixels;  dB(q) = g0(q) p(q) + g1(q) p(q-ex) + g2(q) p(q-ey)
-//   2. per residual centre q (tile + 1 halo):  th(q) = k_h(q)^2 (dB(q) - dB(q+ex)),  tv(q) = k_v(q)^2 (dB(q) - dB(q+ey)),
-//      ts_ch(q) = k_s(q)^2 (4 a_ch(q) p(q) - sum_o a_ch(q+o) p(q+o))                     (k_r J_r p of every residual)
-//   3. J^T:  T(q) = th(q) - th(q-ex) + tv(q) - tv(q-ey);
-//      out(s) = g0(s) T(s) + g1(s+ex) T(s+ex) + g2(s+ey) T(s+ey) + sum_ch a_ch(s) (4 ts_ch(s) - sum_o ts_ch(s-o)) + [D_i(s)>0] w_p^2 p(s)
-// Global traffic per site: p, three gradient images, two uint8 masks, valid, D_i -- the algorithmic minimum.
-template <class T, bool FUSED, bool LM>
-__global__ void __launch_bounds__(256) k_sfs_apply(SfsFunctor<T> f, Vec<T> zv, Vec<T> p, Vec<T> p_new, Vec<T> out, Vec<T> CtC,
-                                                   const unsigned char* __restrict__, const double* bNum, const double* aNum,
-                                                   double* den, double* zero_a, double* zero_b) {
+// Marching J^T J apply for shape_from_shading, optionally fused with PCGStep3 (p' = z + beta p, engine.cuh).
+// The per-site functor form above is a gather of gathers (every site re-evaluates J p of the 10 shading and 5
+// regularisation residuals that touch it: ~200 loads per site, 0.47 ms for 2048^2); a shared-memory tile version
+// with three block barriers per tile ran at 82 us, bound by instruction issue.  Here a warp owns a strip of
+// 128 pixels (lane = 4 consecutive pixels, 128-bit loads; lanes 0 and 31 are halo lanes, 120 pixels are written)
+// and marches down a band of rows; every intermediate lives in registers for the one or two rows it is needed
+// and crosses lanes by shuffle.  Row n is loaded once (p, g0, g1, g2, D_i, masks, valid [+ z, CtC]) and then
+//   dB[n]   = g0 p + g1 p(x-1) + g2 p[n-1]                       th[n] = k_h^2 (dB - dB(x+1))
+//   tv[n-1] = k_v^2[n-1] (dB[n-1] - dB[n])                       T[n-1] = th - th(x-1) + tv[n-1] - tv[n-2]
+//   out[n-1] += g0[n-1] T[n-1] + (g1 T)[n-1](x+1),  out[n-2] += g2[n-1] T[n-1]                (J^T of the shading terms)
+//   regularisation, row q = n-1:  lap = 4 p - p(x-1) - p(x+1) - p[q-1] - p[q+1],
+//       t0 = k_s^2 (a0 lap - (p(x+1) - p(x-1)) / f_x),  t1 = k_s^2 (a1 lap - (p[q+1] - p[q-1]) / f_y),  t2 = k_s^2 lap
+//       (= k_s^2 J_s p per channel, using a0(x +- 1) = a0 +- 1/f_x and a1(y +- 1) = a1 +- 1/f_y), and with
+//       w = a0 t0 + a1 t1 + t2:   out[q] += 4 w - (w + t0/f_x)(x-1) - (w - t0/f_x)(x+1),
+//       out[q-1] -= w - t1/f_y,   out[q+1] = [D_i > 0] w_p^2 p (+ CtC p) - (w + t1/f_y)
+// so row n-2 is complete at the end of step n.  A band of R rows costs R + 4 steps; R is chosen at plan time so that
+// all bands are resident at once (2 CTAs of 8 warps per SM in fp32).  Global traffic per site: the algorithmic minimum
+// (p, three gradient images, D_i, two masks, valid) plus (4 / R) of it for the warm-up rows, which hit in L2.
+// Rows are prefetched three or four steps ahead with per-thread cp.async (16 bytes per lane and array, zero-filled
+// outside the image) into a shared-memory ring that only the issuing thread reads back: no barrier, no
+// registers held by data in flight.  MODE 0: out = J^T J p;  1: p' = z + beta p, out = J^T J p';  2: PCGInit1
+// (r = -J^T F with dB replaced by B_I and p by X in the pipeline above, p = pre r, delta = 0).
+namespace sfsm {
+__device__ __forceinline__ void cp16(void* dst, const void* src, bool on) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+    const int n = on ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(n) : "memory");
+}
+__device__ __forceinline__ void cp4(void* dst, const void* src, bool on) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+    const int n = on ? 4 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(src), "r"(n) : "memory");
+}
+__device__ __forceinline__ void commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ float u8f(unsigned char v, float) { return (float)v; }
+__device__ __forceinline__ double u8f(unsigned char v, double) { return (double)v; }
+}  // namespace sfsm
+
+template <class T>
+struct SfsMarchArgs {
+    const T* z; const T* p; T* p_new; T* out; const T* ctc;     // MODE 0 / 1
+    T* delta; T* r; T* pre; T* p0;                              // MODE 2
+    T beta;
+};
+
+template <class T, int MODE, bool LM>
+struct SfsMarch {
     using F = SfsFunctor<T>;
-    constexpr int TW = F::FTW, TH = F::FTH;
-    constexpr int PW = TW + 4, PH = TH + 4;            // p / dB region: origin (X0-2, Y0-2)
-    constexpr int RW = TW + 2, RH = TH + 2;            // residual-centre region: origin (X0-1, Y0-1)
-    __shared__ T sp[PH][PW], sdb[PH][PW], sth[RH][RW], stv[RH][RW], sts[3][RH][RW];
-    const int W = f.W, H = f.H;
-    const int tiles_x = (W + TW - 1) / TW;
-    const long ntiles = f.fast_tiles_dev();
-    const int tid = linear_tid();
+    static constexpr int NF = 5 + (MODE == 1) + (LM && MODE != 2) + (MODE == 2);    // float arrays per row
+    static constexpr int QB = 4 * (int)sizeof(T);                                   // bytes of a lane's quad
+    static constexpr int STAGE = NF * 256 * QB + 3 * 256 * 4;
+    static constexpr int D = NF <= 5 ? 4 : 3;                                       // ring depth
+    static constexpr int A_P = 0, A_G0 = 1, A_G1 = 2, A_G2 = 3, A_DI = 4, A_Z = 5, A_C = 5 + (MODE == 1), A_BI = 5;
+
+    static __device__ __forceinline__ unsigned char* slot(unsigned char* ring, int stage, int arr, int tid) {
+        return ring + (size_t)stage * STAGE + (size_t)arr * 256 * QB + (size_t)tid * QB;
+    }
+    static __device__ __forceinline__ unsigned char* bslot(unsigned char* ring, int stage, int arr, int tid) {
+        return ring + (size_t)stage * STAGE + (size_t)NF * 256 * QB + (size_t)arr * 1024 + (size_t)tid * 4;
+    }
+    static __device__ __forceinline__ void cpq(unsigned char* dst, const T* src, bool on) {
+#pragma unroll
+        for (int k = 0; k < QB / 16; ++k) sfsm::cp16(dst + 16 * k, (const unsigned char*)src + 16 * k, on);
+    }
+    // one row of this lane's quad into ring stage `st` (always commits a group, possibly empty)
+    static __device__ __forceinline__ void issue(const F& f, const SfsMarchArgs<T>& a, unsigned char* ring, int st, int tid,
+                                                 bool on, long s) {
+        if (!on) s = 0;
+        cpq(slot(ring, st, A_P, tid), (MODE == 2 ? f.X : a.p) + s, on);
+        cpq(slot(ring, st, A_G0, tid), f.G0 + s, on);
+        cpq(slot(ring, st, A_G1, tid), f.G1 + s, on);
+        cpq(slot(ring, st, A_G2, tid), f.G2 + s, on);
+        cpq(slot(ring, st, A_DI, tid), f.Di + s, on);
+        if (MODE == 1) cpq(slot(ring, st, A_Z, tid), a.z + s, on);
+        if (LM && MODE != 2) cpq(slot(ring, st, A_C, tid), a.ctc + s, on);
+        if (MODE == 2) cpq(slot(ring, st, A_BI, tid), f.BI + s, on);
+        sfsm::cp4(bslot(ring, st, 0, tid), f.mR + s, on);
+        sfsm::cp4(bslot(ring, st, 1, tid), f.mC + s, on);
+        sfsm::cp4(bslot(ring, st, 2, tid), f.valid + s, on);
+        sfsm::commit();
+    }
+    static __device__ __forceinline__ void rd(unsigned char* ring, int st, int arr, int tid, T* o) {
+        load4(reinterpret_cast<const T*>(slot(ring, st, arr, tid)), o);
+    }
+    static __device__ __forceinline__ uchar4 rdb(unsigned char* ring, int st, int arr, int tid) {
+        return *reinterpret_cast<const uchar4*>(bslot(ring, st, arr, tid));
+    }
+    static __device__ void run(const F& f, const SfsMarchArgs<T>& a, unsigned char* ring, double& acc);
+};
+
+template <class T, int MODE, bool LM>
+__device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a, unsigned char* ring, double& acc) {
+    constexpr unsigned FULL = 0xffffffffu;
+    const int W = f.W, H = f.H, R = f.bandR;
+    const int strips = f.strips();
+    const long nitems = (long)strips * ((H + R - 1) / R);
+    const long ntiles = (nitems + 7) / 8;
+    const int lane = threadIdx.x, warp = threadIdx.y, tid = warp * 32 + lane;
     const T ifx = T(1) / f.f_x, ify = T(1) / f.f_y;
-    if (blockIdx.x == 0 && tid == 0) {
+    const T wp2 = f.w_p * f.w_p, ws2 = f.w_s * f.w_s, wg2 = f.w_g * f.w_g;
+    const T beta = a.beta;
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long item = tile * 8 + warp;
+        if (item >= nitems) continue;                                  // warp-uniform
+        const int strip = (int)(item % strips), band = (int)(item / strips);
+        const int x0 = strip * F::STRIP - 4 + lane * 4;               // first of this lane's four pixels
+        const int y0 = band * R, y1 = min(y0 + R, H);
+        const bool col_in = x0 >= 0 && x0 < W;                        // W % 4 == 0: a quad is inside or outside as a whole
+        const bool owner = col_in && lane >= 1 && lane <= 30;
+        T a0[4], xin[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            a0[j] = ((T)(x0 + j) - f.u_x) * ifx;
+            xin[j] = (x0 + j >= 1 && x0 + j + 1 < W) ? T(1) : T(0);   // x part of the expanded-bounds predicate
+        }
+        // rows n-1 ("1") and n-2 ("2") carried between steps
+        T p1[4], p2[4], db1[4], th1[4], tvp[4], g0p[4], g1p[4], g2p[4], kv1[4], ks1[4], oA[4], oB[4], p1l = T(0);
+        bool e1[4], e2[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            p1[j] = p2[j] = db1[j] = th1[j] = tvp[j] = g0p[j] = g1p[j] = g2p[j] = kv1[j] = ks1[j] = oA[j] = oB[j] = T(0);
+            e1[j] = e2[j] = false;
+        }
+        const int nbeg = y0 - 2, nend = y1 + 2;
+        auto row_on = [&](int n) { return col_in && n >= 0 && n < H && n < nend; };
+#pragma unroll
+        for (int k = 0; k < D - 1; ++k) issue(f, a, ring, k, tid, row_on(nbeg + k), x0 + (long)W * (nbeg + k));
+        int st = 0;
+        for (int n = nbeg; n < nend; ++n) {
+            const long s = x0 + (long)W * n;
+            {
+                const int sf = st == 0 ? D - 1 : st - 1;              // the stage consumed in the previous step
+                issue(f, a, ring, sf, tid, row_on(n + D - 1), s + (long)W * (D - 1));
+            }
+            sfsm::wait<D - 1>();
+            T pn[4], g0[4], g1[4], g2[4], di[4];
+            rd(ring, st, A_P, tid, pn); rd(ring, st, A_G0, tid, g0); rd(ring, st, A_G1, tid, g1); rd(ring, st, A_G2, tid, g2);
+            rd(ring, st, A_DI, tid, di);
+            const uchar4 mr = rdb(ring, st, 0, tid), mc = rdb(ring, st, 1, tid), va = rdb(ring, st, 2, tid);
+            if (MODE == 1) {
+                T z[4]; rd(ring, st, A_Z, tid, z);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) pn[j] = z[j] + beta * pn[j];
+                if (owner && n >= y0 && n < y1) st4v(a.p_new + s, pn);
+            }
+            const T yin = (n >= 1 && n + 1 < H) ? T(1) : T(0);
+            // ---- shading terms: dB[n], th[n], tv[n-1], T[n-1] ----
+            const T pl = __shfl_up_sync(FULL, pn[3], 1);
+            T db[4], thn[4], kvn[4], ksn[4], oC[4];
+            bool en[4];
+            const unsigned char mrb[4] = {mr.x, mr.y, mr.z, mr.w}, mcb[4] = {mc.x, mc.y, mc.z, mc.w}, vab[4] = {va.x, va.y, va.z, va.w};
+            if (MODE == 2) rd(ring, st, A_BI, tid, db);
+            else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) db[j] = g0[j] * pn[j] + g1[j] * (j > 0 ? pn[j > 0 ? j - 1 : 0] : pl) + g2[j] * p1[j];
+            }
+            const T dbr = __shfl_down_sync(FULL, db[0], 1);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const T in = xin[j] * yin;
+                const T mh = sfsm::u8f(mrb[j], T(0)), mv = sfsm::u8f(mcb[j], T(0));
+                thn[j] = (wg2 * mh * mh * in) * (db[j] - (j < 3 ? db[j < 3 ? j + 1 : 3] : dbr));
+                kvn[j] = wg2 * mv * mv * in;
+                ksn[j] = vab[j] == 1 ? ws2 * in : T(0);
+                en[j] = di[j] > T(0);
+                oC[j] = en[j] ? wp2 * (MODE == 2 ? pn[j] - di[j] : pn[j]) : T(0);
+            }
+            if (LM && MODE != 2) {
+                T c[4]; rd(ring, st, A_C, tid, c);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) oC[j] += c[j] * pn[j];
+            }
+            const T th1l = __shfl_up_sync(FULL, th1[3], 1);
+            T tv[4], gT[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                tv[j] = kv1[j] * (db1[j] - db[j]);
+                const T Tq = th1[j] - (j > 0 ? th1[j > 0 ? j - 1 : 0] : th1l) + tv[j] - tvp[j];
+                gT[j] = g1p[j] * Tq;
+                oB[j] += g0p[j] * Tq;
+                oA[j] += g2p[j] * Tq;
+            }
+            const T gTr = __shfl_down_sync(FULL, gT[0], 1);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) oB[j] += j < 3 ? gT[j < 3 ? j + 1 : 3] : gTr;
+            // ---- regularisation terms of row q = n-1 ----
+            const T p1r = __shfl_down_sync(FULL, p1[0], 1);
+            const T a1q = ((T)(n - 1) - f.u_y) * ify;
+            T w[4], t0x[4], t1y[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const T l = j > 0 ? p1[j > 0 ? j - 1 : 0] : p1l, r = j < 3 ? p1[j < 3 ? j + 1 : 3] : p1r;
+                const T lap = T(4) * p1[j] - (l + p2[j] + r + pn[j]);
+                const T t2 = ks1[j] * lap;
+                const T t0 = a0[j] * t2 - ks1[j] * (ifx * (r - l));
+                const T t1 = a1q * t2 - ks1[j] * (ify * (pn[j] - p2[j]));
+                w[j] = a0[j] * t0 + a1q * t1 + t2;
+                t0x[j] = ifx * t0;
+                t1y[j] = ify * t1;
+            }
+            const T fromL = __shfl_up_sync(FULL, w[3] + t0x[3], 1);
+            const T fromR = __shfl_down_sync(FULL, w[0] - t0x[0], 1);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const T lft = j > 0 ? w[j > 0 ? j - 1 : 0] + t0x[j > 0 ? j - 1 : 0] : fromL;
+                const T rgt = j < 3 ? w[j < 3 ? j + 1 : 3] - t0x[j < 3 ? j + 1 : 3] : fromR;
+                oB[j] += T(4) * w[j] - lft - rgt;
+                oA[j] -= w[j] - t1y[j];
+                oC[j] -= w[j] + t1y[j];
+            }
+            // ---- row n-2 is complete ----
+            if (owner && n - 2 >= y0 && n - 2 < y1) {
+                const long so = s - 2 * (long)W;
+                T rs = T(0);
+                if (MODE == 2) {
+                    // PCGInit1 (engine.cuh k_pcg_init1): preconditioner off -> diagonal 1, guarded inverse 1/4
+                    const T m = guarded_invert(T(1));
+                    T rr[4], pp[4], dd[4], zz[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        rr[j] = e2[j] ? -oA[j] : T(0); pp[j] = m * rr[j]; dd[j] = e2[j] ? m : T(0); zz[j] = T(0);
+                        rs += rr[j] * pp[j];
+                    }
+                    st4v(a.r + so, rr); st4v(a.p0 + so, pp); st4v(a.pre + so, dd); st4v(a.delta + so, zz);
+                } else {
+                    T o[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { o[j] = e2[j] ? oA[j] : T(0); rs += p2[j] * o[j]; }
+                    st4v(a.out + so, o);
+                }
+                acc += (double)rs;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                p2[j] = p1[j]; p1[j] = pn[j]; db1[j] = db[j]; th1[j] = thn[j]; tvp[j] = tv[j];
+                g0p[j] = g0[j]; g1p[j] = g1[j]; g2p[j] = g2[j]; kv1[j] = kvn[j]; ks1[j] = ksn[j];
+                oA[j] = oB[j]; oB[j] = oC[j]; e2[j] = e1[j]; e1[j] = en[j];
+            }
+            p1l = pl;
+            st = st + 1 == D ? 0 : st + 1;
+        }
+        sfsm::wait<0>();
+    }
+}
+
+template <class T, bool FUSED, bool LM>
+__global__ void __launch_bounds__(256, sizeof(T) == 4 ? 2 : 1)
+k_sfs_march(SfsFunctor<T> f, Vec<T> zv, Vec<T> p, Vec<T> p_new, Vec<T> out, Vec<T> CtC,
+            const unsigned char* __restrict__, const double* bNum, const double* aNum,
+            double* den, double* zero_a, double* zero_b) {
+    extern __shared__ __align__(16) unsigned char sfs_ring[];
+    SfsMarchArgs<T> a{};
+    a.z = zv.d; a.p = p.d; a.p_new = p_new.d; a.out = out.d; a.ctc = CtC.d;
+    a.beta = FUSED ? (T)(*bNum) / (T)(*aNum) : T(0);
+    if (blockIdx.x == 0 && linear_tid() == 0) {
         if (zero_a) *zero_a = 0.0;
         if (zero_b) *zero_b = 0.0;
     }
     double acc = 0.0;
-    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int X0 = (int)(tile % tiles_x) * TW, Y0 = (int)(tile / tiles_x) * TH;
-        // ---- stage 1a: p with a halo of 2 (0 outside the image) ----
-        for (int i = tid; i < PW * PH; i += 256) {
-            const int lx = i % PW, ly = i / PW, x = X0 - 2 + lx, y = Y0 - 2 + ly;
-            sp[ly][lx] = f.inimg(x, y) ? p.d[x + (long)W * y] : T(0);
-        }
-        __syncthreads();
-        // ---- stage 1b: dB on the same region except its first row / column ----
-        for (int i = tid; i < PW * PH; i += 256) {
-            const int lx = i % PW, ly = i / PW, x = X0 - 2 + lx, y = Y0 - 2 + ly;
-            T v = T(0);
-            if (lx > 0 && ly > 0 && f.inimg(x, y)) {
-                const long q = x + (long)W * y;
-                v = f.G0[q] * sp[ly][lx] + f.G1[q] * sp[ly][lx - 1] + f.G2[q] * sp[ly - 1][lx];
-            }
-            sdb[ly][lx] = v;
-        }
-        __syncthreads();
-        // ---- stage 2: k_r J_r p of the residuals centred on the tile + 1 halo pixel ----
-        for (int i = tid; i < RW * RH; i += 256) {
-            const int lx = i % RW, ly = i / RW, x = X0 - 1 + lx, y = Y0 - 1 + ly;
-            const int px = lx + 1, py = ly + 1;                          // same pixel in the p / dB region
-            T th = T(0), tv = T(0), t0 = T(0), t1 = T(0), t2 = T(0);
-            if (f.inbexp1(x, y)) {
-                const long q = x + (long)W * y;
-                const T kh = f.w_g * (T)f.mR[q], kv = f.w_g * (T)f.mC[q];
-                const T db = sdb[py][px];
-                th = kh * (kh * (db - sdb[py][px + 1]));
-                tv = kv * (kv * (db - sdb[py + 1][px]));
-                if (f.valid[q] == 1) {
-                    const T c = sp[py][px], l = sp[py][px - 1], r = sp[py][px + 1], u = sp[py - 1][px], d = sp[py + 1][px];
-                    const T a0 = ((T)x - f.u_x) * ifx, a1 = ((T)y - f.u_y) * ify;
-                    const T ws2 = f.w_s * f.w_s;
-                    t0 = ws2 * (T(4) * a0 * c - ((a0 - ifx) * l + a0 * u + (a0 + ifx) * r + a0 * d));
-                    t1 = ws2 * (T(4) * a1 * c - (a1 * l + (a1 - ify) * u + a1 * r + (a1 + ify) * d));
-                    t2 = ws2 * (T(4) * c - (l + u + r + d));
-                }
-            }
-            sth[ly][lx] = th; stv[ly][lx] = tv; sts[0][ly][lx] = t0; sts[1][ly][lx] = t1; sts[2][ly][lx] = t2;
-        }
-        __syncthreads();
-        // ---- stage 3: J^T at the sites of the tile (two rows per thread) ----
-#pragma unroll
-        for (int rr = 0; rr < 2; ++rr) {
-            const int lx = threadIdx.x, ly = threadIdx.y + rr * 8;
-            const int x = X0 + lx, y = Y0 + ly;
-            if (x < W && y < H) {
-                const long s = x + (long)W * y;
-                const T di = f.Di[s];
-                if (di > T(0)) {                                           // Exclude(D_i <= 0)
-                    const int rx = lx + 1, ry = ly + 1;                    // this site in the residual-centre region
-                    auto Tq = [&](int qx, int qy) { return sth[qy][qx] - sth[qy][qx - 1] + stv[qy][qx] - stv[qy - 1][qx]; };
-                    const T pv = sp[ly + 2][lx + 2];
-                    T o = f.w_p * f.w_p * pv + f.G0[s] * Tq(rx, ry);
-                    if (x + 1 < W) o += f.G1[s + 1] * Tq(rx + 1, ry);
-                    if (y + 1 < H) o += f.G2[s + W] * Tq(rx, ry + 1);
-                    T a3[3];
-#pragma unroll
-                    for (int ch = 0; ch < 3; ++ch)
-                        a3[ch] = T(4) * sts[ch][ry][rx] - (sts[ch][ry][rx - 1] + sts[ch][ry][rx + 1] + sts[ch][ry - 1][rx] + sts[ch][ry + 1][rx]);
-                    o += ((T)x - f.u_x) * ifx * a3[0] + ((T)y - f.u_y) * ify * a3[1] + a3[2];
-                    if (LM) o += CtC.d[s] * pv;
-                    out.d[s] = o;
-                    acc += (double)(pv * o);
-                }
-            }
-        }
-        __syncthreads();
-    }
+    SfsMarch<T, FUSED ? 1 : 0, LM>::run(f, a, sfs_ring, acc);
     block_accumulate(acc, den);
 }
 
-template <class T> template <bool FUSED, bool LM> auto SfsFunctor<T>::fast_kernel() { return &k_sfs_apply<T, FUSED, LM>; }
+template <class T>
+__global__ void __launch_bounds__(256, sizeof(T) == 4 ? 2 : 1)
+k_sfs_init(SfsFunctor<T> f, Vec<T> delta, Vec<T> r, Vec<T> p, Vec<T> pre, double* aNum) {
+    extern __shared__ __align__(16) unsigned char sfs_ring[];
+    SfsMarchArgs<T> a{};
+    a.delta = delta.d; a.r = r.d; a.p0 = p.d; a.pre = pre.d; a.beta = T(0);
+    double acc = 0.0;
+    SfsMarch<T, 2, false>::run(f, a, sfs_ring, acc);
+    block_accumulate(acc, aNum);
+}
+
+template <class T> template <bool FUSED, bool LM> auto SfsFunctor<T>::fast_kernel() { return &k_sfs_march<T, FUSED, LM>; }
+template <class T> auto SfsFunctor<T>::fast_init_kernel() { return &k_sfs_init<T>; }
+template <class T> size_t SfsFunctor<T>::fast_smem() const {
+    size_t m = 0;
+    m = std::max<size_t>(m, (size_t)SfsMarch<T, 0, false>::STAGE * SfsMarch<T, 0, false>::D);
+    m = std::max<size_t>(m, (size_t)SfsMarch<T, 0, true>::STAGE * SfsMarch<T, 0, true>::D);
+    m = std::max<size_t>(m, (size_t)SfsMarch<T, 1, false>::STAGE * SfsMarch<T, 1, false>::D);
+    m = std::max<size_t>(m, (size_t)SfsMarch<T, 1, true>::STAGE * SfsMarch<T, 1, true>::D);
+    m = std::max<size_t>(m, (size_t)SfsMarch<T, 2, false>::STAGE * SfsMarch<T, 2, false>::D);
+    return m;
+}
 
 }  // namespace optk

@@ -23,6 +23,8 @@ CASES = {
     "optical_flow": (examples.optical_flow_synthetic, (53, 38), dict(n_iter=3, l_iter=10)),
     "arap": (examples.arap_synthetic, (13, 11), dict(n_iter=3, l_iter=10)),
     "sfs": (examples.sfs_synthetic, (45, 37), dict(n_iter=3, l_iter=10)),
+    # rows of whole quads: the marching J^T J kernel (two strips of 120 written pixels, five bands of 8 rows)
+    "sfs_quads": (examples.sfs_synthetic, (132, 37), dict(n_iter=3, l_iter=10)),
     "embedded": (examples.embedded_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
     "cotangent": (examples.cotangent_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
     "robust": (examples.robust_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
@@ -108,6 +110,23 @@ def test_volumetric_tiled_jtj_equals_generic(built, case, double, monkeypatch):
     monkeypatch.setenv("OPTB200_GENERIC_JTJ", "1")
     generic = sol.debug_apply_jtj(named, p)
     assert not np.array_equal(fast, generic)          # really two code paths
+    assert np.abs(fast - generic).max() <= OP_RTOL[double] * np.abs(generic).max()
+
+
+@pytest.mark.parametrize("double", [False, True])
+@pytest.mark.parametrize("kind", ["gaussNewtonGPU", "LMGPU"])
+def test_sfs_marching_jtj_equals_generic(built, kind, double, monkeypatch):
+    """k_sfs_march (register pipeline over rows, shuffles across lanes) against the per-site functor kernel."""
+    from opt_b200 import solver as S
+    pr = make("sfs_quads", kind=kind, double=double)
+    named = S.upload(pr)
+    rng = np.random.default_rng(5)
+    p = rng.standard_normal((int(np.prod(pr.dims)), 1)).astype(np.float64 if double else np.float32)
+    sol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=double)
+    fast = sol.debug_apply_jtj(named, p)
+    monkeypatch.setenv("OPTB200_GENERIC_JTJ", "1")
+    generic = sol.debug_apply_jtj(named, p)
+    assert not np.array_equal(fast, generic)
     assert np.abs(fast - generic).max() <= OP_RTOL[double] * np.abs(generic).max()
 
 
