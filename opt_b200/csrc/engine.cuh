@@ -17,6 +17,7 @@
 #include <nccl.h>
 #include <cub/device/device_radix_sort.cuh>
 #include "common.cuh"
+#include "functors/math.cuh"
 #include "optk.h"
 
 #define OPTK_NCCL(call)                                                                        \
@@ -392,6 +393,23 @@ __global__ void k_unknown_update(F f, TileGrid tg, VecOf<F> v) {
             else if (MODE == 1) v(u, s) = *xp;
             else *xp = v(u, s);
         }
+    }
+}
+
+// Single-channel unknowns (U = 1): the unknown image and the solver vectors share one flat layout, and excluded sites
+// carry delta = 0 / prevX = X, so the three updates are plain 128-bit streaming passes over all sites.
+template <class T, int MODE>
+__global__ void __launch_bounds__(256) k_flat_update(long n4, T* __restrict__ X, T* __restrict__ v) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
+        T a[4], b[4];
+        if (MODE != 2) load4(X + 4 * i, a);
+        if (MODE != 1) load4(v + 4 * i, b);
+        if (MODE == 0) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) a[j] += b[j];
+            st4v(X + 4 * i, a);
+        } else if (MODE == 1) st4v(v + 4 * i, a);
+        else st4v(X + 4 * i, b);
     }
 }
 
@@ -831,11 +849,28 @@ struct Engine : OptK_Plan {
             this->pre_launch("precompute");
             f.custom_precompute(stream, nsm);
             this->post_launch();
-        } else if (F::HAS_PRECOMPUTE) this->launch_tiles("precompute", tg.n, sblock, k_precompute<F>, f, tg);
+        } else if (F::HAS_PRECOMPUTE) {
+            if constexpr (F::HAS_FAST_PRECOMPUTE) {
+                if (f.fast_ok()) {
+                    this->pre_launch("precompute");
+                    f.fast_precompute(stream, nsm);
+                    this->post_launch();
+                    return;
+                }
+            }
+            this->launch_tiles("precompute", tg.n, sblock, k_precompute<F>, f, tg);
+        }
     }
     double cost() override {
         OPTK_CUDA(cudaMemsetAsync(S(S_COST), 0, sizeof(double), stream));
-        this->launch_tiles("computeCost", tg.n, sblock, k_cost<F>, f, tg, S(S_COST));
+        bool fast_cost = false;
+        if constexpr (F::HAS_FAST_COST) {
+            if (f.fast_ok()) {
+                this->launch_tiles_smem("computeCost", f.fast_tiles(), f.fast_block(), f.fast_smem(), f.fast_cost_kernel(), f, S(S_COST));
+                fast_cost = true;
+            }
+        }
+        if (!fast_cost) this->launch_tiles("computeCost", tg.n, sblock, k_cost<F>, f, tg, S(S_COST));
         if (GRAPH) this->launch("computeCost_Graph", edge_grid(), dim3(256), k_graph_cost<F>, f, E, S(S_COST));
         reduce(S_COST);
         return (double)(T)read_scalar(S_COST);
@@ -954,13 +989,31 @@ struct Engine : OptK_Plan {
         for (int l = 0; l < lIterations; ++l) pcg_iter(l, 0);
     }
 
-    void save_unknowns() override { this->launch_tiles("savePreviousUnknowns", tg.n, sblock, k_unknown_update<F, 1>, f, tg, prevX); }
+    static constexpr bool FLAT_X = F::U == 1 && F::VEC_UB == 0 && !GRAPH;
+    template <int MODE> bool flat_update(const char* name, V v) {
+        if constexpr (FLAT_X) {
+            if (N % 4 == 0 && comm == nullptr) {
+                const long n4 = N / 4;
+                void* img[8]; int ch[8];
+                f.unknown_images(img, ch);
+                this->launch(name, dim3((unsigned)std::min<long>((n4 + 255) / 256, (long)nsm * 16)), dim3(256), k_flat_update<T, MODE>, n4, (T*)img[0], v.d);
+                return true;
+            }
+        }
+        return false;
+    }
+    void save_unknowns() override {
+        if (flat_update<1>("savePreviousUnknowns", prevX)) return;
+        this->launch_tiles("savePreviousUnknowns", tg.n, sblock, k_unknown_update<F, 1>, f, tg, prevX);
+    }
     void linear_update() override {
-        this->launch_tiles("PCGLinearUpdate", tg.n, sblock, k_unknown_update<F, 0>, f, tg, delta);
+        if (!flat_update<0>("PCGLinearUpdate", delta))
+            this->launch_tiles("PCGLinearUpdate", tg.n, sblock, k_unknown_update<F, 0>, f, tg, delta);
         exchange_unknowns();                                // neighbours read X over the stencil
     }
     void revert_update() override {
-        this->launch_tiles("revertUpdate", tg.n, sblock, k_unknown_update<F, 2>, f, tg, prevX);
+        if (!flat_update<2>("revertUpdate", prevX))
+            this->launch_tiles("revertUpdate", tg.n, sblock, k_unknown_update<F, 2>, f, tg, prevX);
         exchange_unknowns();
     }
 
@@ -1006,6 +1059,8 @@ struct FunctorDefaults {
     static constexpr bool HAS_EXCLUDE = false;           // functors with an Exclude() override this
     static constexpr bool HAS_FAST_APPLY = false;        // functors with a specialised J^T J kernel override this
     static constexpr bool HAS_FAST_INIT = false;         // ... and with a specialised PCGInit1 (fast_init_kernel())
+    static constexpr bool HAS_FAST_COST = false;         // ... and computeCost (fast_cost_kernel())
+    static constexpr bool HAS_FAST_PRECOMPUTE = false;   // ... and precompute (fast_precompute(stream, nsm))
     static constexpr bool SLAB_OK = true;                // grid functors whose bounds predicates survive a slab cut
     static constexpr bool HAS_GATHER = false;            // graph functors with a per-vertex gather form of J^T J p
     static constexpr int VEC_UB = 0;                     // solver-vector layout: 0 = SoA, U = blocked (common.cuh, Vec)

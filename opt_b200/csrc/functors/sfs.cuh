@@ -36,6 +36,10 @@ struct SfsFunctor : FunctorDefaults<T> {
     template <bool FUSED, bool LM> static auto fast_kernel();
     static constexpr bool HAS_FAST_INIT = true;        // PCGInit1 by the same pipeline (k_sfs_init)
     static auto fast_init_kernel();
+    static constexpr bool HAS_FAST_COST = true;        // computeCost likewise (k_sfs_cost)
+    static auto fast_cost_kernel();
+    static constexpr bool HAS_FAST_PRECOMPUTE = true;  // one thread per quad of a row (k_sfs_precompute4)
+    void fast_precompute(cudaStream_t stream, int nsm) const;
     size_t fast_smem() const;
     int W, H, D;
     T* X; const T* Di; const T* Im; const unsigned char* mR; const unsigned char* mC;
@@ -80,39 +84,41 @@ struct SfsFunctor : FunctorDefaults<T> {
     __device__ __forceinline__ T ks(int x, int y) const { return (inbexp1(x, y) && valid[x + (long)W * y] == 1) ? w_s : T(0); }
 
     // ---- precompute: B_I, its three gradient images, valid -------------------------------------------
+    // B(normal(d00, dm0, d0m)) - shading target and its derivatives wrt (d00, dm0, d0m) at pixel (x, y)
+    __device__ __forceinline__ void shade(int x, int y, T d00, T dm0, T d0m, T target, T& b, T* g) const {
+        const T ify = T(1) / f_y, ifx = T(1) / f_x, cx = (u_x - (T)x) / f_x, cy = (u_y - (T)y) / f_y, ifxy = T(1) / (f_x * f_y);
+        // n and its derivatives wrt (d00, dm0, d0m)
+        T n[3], dn[3][3];
+        n[0] = d0m * (d00 - dm0) * ify;
+        dn[0][0] = d0m * ify; dn[0][1] = -d0m * ify; dn[0][2] = (d00 - dm0) * ify;
+        n[1] = dm0 * (d00 - d0m) * ifx;
+        dn[1][0] = dm0 * ifx; dn[1][1] = (d00 - d0m) * ifx; dn[1][2] = -dm0 * ifx;
+        n[2] = n[0] * cx + n[1] * cy - dm0 * d0m * ifxy;
+        dn[2][0] = dn[0][0] * cx + dn[1][0] * cy;
+        dn[2][1] = dn[0][1] * cx + dn[1][1] * cy - d0m * ifxy;
+        dn[2][2] = dn[0][2] * cx + dn[1][2] * cy - dm0 * ifxy;
+        const T sq = n[0] * n[0] + n[1] * n[1] + n[2] * n[2];
+        const bool pos = sq > T(0);
+        const T inv = pos ? T(1) / sqrt(sq) : T(1);
+        const T N0 = inv * n[0], N1 = inv * n[1], N2 = inv * n[2];
+        b = L[0] + L[1] * N1 + L[2] * N2 + L[3] * N0 + L[4] * N0 * N1 + L[5] * N1 * N2 +
+            L[6] * (-(N0 * N0) - N1 * N1 + T(2) * N2 * N2) + L[7] * N2 * N0 + L[8] * (N0 * N0 - N1 * N1);
+        const T bN0 = L[3] + L[4] * N1 - T(2) * L[6] * N0 + L[7] * N2 + T(2) * L[8] * N0;
+        const T bN1 = L[1] + L[4] * N0 + L[5] * N2 - T(2) * L[6] * N1 - T(2) * L[8] * N1;
+        const T bN2 = L[2] + L[5] * N1 + T(4) * L[6] * N2 + L[7] * N0;
+#pragma unroll
+        for (int v = 0; v < 3; ++v) {
+            // dN/dv = inv (dn/dv - N (N . dn/dv)) when the normal was normalised, dn/dv otherwise
+            const T nd = pos ? N0 * dn[0][v] + N1 * dn[1][v] + N2 * dn[2][v] : T(0);
+            g[v] = inv * (bN0 * (dn[0][v] - N0 * nd) + bN1 * (dn[1][v] - N1 * nd) + bN2 * (dn[2][v] - N2 * nd));
+        }
+        b -= target;
+    }
     __device__ void precompute(int x, int y, int, long s) const {
         const T d00 = X[s], dm0 = get(X, x - 1, y), d0m = get(X, x, y - 1);
         const bool ok = inbexp1(x, y) && dv(x - 1, y) && dv(x, y) && dv(x, y - 1);
         T b = T(0), g[3] = {T(0), T(0), T(0)};
-        if (ok) {
-            const T ify = T(1) / f_y, ifx = T(1) / f_x, cx = (u_x - (T)x) / f_x, cy = (u_y - (T)y) / f_y, ifxy = T(1) / (f_x * f_y);
-            // n and its derivatives wrt (d00, dm0, d0m)
-            T n[3], dn[3][3];
-            n[0] = d0m * (d00 - dm0) * ify;
-            dn[0][0] = d0m * ify; dn[0][1] = -d0m * ify; dn[0][2] = (d00 - dm0) * ify;
-            n[1] = dm0 * (d00 - d0m) * ifx;
-            dn[1][0] = dm0 * ifx; dn[1][1] = (d00 - d0m) * ifx; dn[1][2] = -dm0 * ifx;
-            n[2] = n[0] * cx + n[1] * cy - dm0 * d0m * ifxy;
-            dn[2][0] = dn[0][0] * cx + dn[1][0] * cy;
-            dn[2][1] = dn[0][1] * cx + dn[1][1] * cy - d0m * ifxy;
-            dn[2][2] = dn[0][2] * cx + dn[1][2] * cy - dm0 * ifxy;
-            const T sq = n[0] * n[0] + n[1] * n[1] + n[2] * n[2];
-            const bool pos = sq > T(0);
-            const T inv = pos ? T(1) / sqrt(sq) : T(1);
-            const T N0 = inv * n[0], N1 = inv * n[1], N2 = inv * n[2];
-            b = L[0] + L[1] * N1 + L[2] * N2 + L[3] * N0 + L[4] * N0 * N1 + L[5] * N1 * N2 +
-                L[6] * (-(N0 * N0) - N1 * N1 + T(2) * N2 * N2) + L[7] * N2 * N0 + L[8] * (N0 * N0 - N1 * N1);
-            const T bN0 = L[3] + L[4] * N1 - T(2) * L[6] * N0 + L[7] * N2 + T(2) * L[8] * N0;
-            const T bN1 = L[1] + L[4] * N0 + L[5] * N2 - T(2) * L[6] * N1 - T(2) * L[8] * N1;
-            const T bN2 = L[2] + L[5] * N1 + T(4) * L[6] * N2 + L[7] * N0;
-#pragma unroll
-            for (int v = 0; v < 3; ++v) {
-                // dN/dv = inv (dn/dv - N (N . dn/dv)) when the normal was normalised, dn/dv otherwise
-                const T nd = pos ? N0 * dn[0][v] + N1 * dn[1][v] + N2 * dn[2][v] : T(0);
-                g[v] = inv * (bN0 * (dn[0][v] - N0 * nd) + bN1 * (dn[1][v] - N1 * nd) + bN2 * (dn[2][v] - N2 * nd));
-            }
-            b -= Im[s] * T(0.5) + T(0.25) * (get(Im, x - 1, y) + get(Im, x, y - 1));
-        }
+        if (ok) shade(x, y, d00, dm0, d0m, Im[s] * T(0.5) + T(0.25) * (get(Im, x - 1, y) + get(Im, x, y - 1)), b, g);
         BI[s] = b; G0[s] = g[0]; G1[s] = g[1]; G2[s] = g[2];
         auto cont = [&](int ox, int oy) { return fabs(d00 - get(X, x + ox, y + oy)) < T(0.01); };
         const bool v = dv(x, y) && dv(x, y - 1) && dv(x, y + 1) && dv(x - 1, y) && dv(x + 1, y) &&
@@ -302,11 +308,13 @@ struct SfsMarchArgs {
 template <class T, int MODE, bool LM>
 struct SfsMarch {
     using F = SfsFunctor<T>;
-    static constexpr int NF = 5 + (MODE == 1) + (LM && MODE != 2) + (MODE == 2);    // float arrays per row
+    static constexpr bool HAS_G = MODE != 3;                                        // the cost pass needs no gradient images
+    static constexpr bool USE_C = LM && MODE < 2;
+    static constexpr int NF = (HAS_G ? 5 : 2) + (MODE == 1) + USE_C + (MODE >= 2);  // float arrays per row
     static constexpr int QB = 4 * (int)sizeof(T);                                   // bytes of a lane's quad
     static constexpr int STAGE = NF * 256 * QB + 3 * 256 * 4;
     static constexpr int D = NF <= 5 ? 4 : 3;                                       // ring depth
-    static constexpr int A_P = 0, A_G0 = 1, A_G1 = 2, A_G2 = 3, A_DI = 4, A_Z = 5, A_C = 5 + (MODE == 1), A_BI = 5;
+    static constexpr int A_P = 0, A_G0 = 1, A_G1 = 2, A_G2 = 3, A_DI = HAS_G ? 4 : 1, A_Z = A_DI + 1, A_C = A_DI + 1 + (MODE == 1), A_BI = A_DI + 1;
 
     static __device__ __forceinline__ unsigned char* slot(unsigned char* ring, int stage, int arr, int tid) {
         return ring + (size_t)stage * STAGE + (size_t)arr * 256 * QB + (size_t)tid * QB;
@@ -322,14 +330,16 @@ struct SfsMarch {
     static __device__ __forceinline__ void issue(const F& f, const SfsMarchArgs<T>& a, unsigned char* ring, int st, int tid,
                                                  bool on, long s) {
         if (!on) s = 0;
-        cpq(slot(ring, st, A_P, tid), (MODE == 2 ? f.X : a.p) + s, on);
-        cpq(slot(ring, st, A_G0, tid), f.G0 + s, on);
-        cpq(slot(ring, st, A_G1, tid), f.G1 + s, on);
-        cpq(slot(ring, st, A_G2, tid), f.G2 + s, on);
+        cpq(slot(ring, st, A_P, tid), (MODE >= 2 ? f.X : a.p) + s, on);
+        if (HAS_G) {
+            cpq(slot(ring, st, A_G0, tid), f.G0 + s, on);
+            cpq(slot(ring, st, A_G1, tid), f.G1 + s, on);
+            cpq(slot(ring, st, A_G2, tid), f.G2 + s, on);
+        }
         cpq(slot(ring, st, A_DI, tid), f.Di + s, on);
         if (MODE == 1) cpq(slot(ring, st, A_Z, tid), a.z + s, on);
-        if (LM && MODE != 2) cpq(slot(ring, st, A_C, tid), a.ctc + s, on);
-        if (MODE == 2) cpq(slot(ring, st, A_BI, tid), f.BI + s, on);
+        if (USE_C) cpq(slot(ring, st, A_C, tid), a.ctc + s, on);
+        if (MODE >= 2) cpq(slot(ring, st, A_BI, tid), f.BI + s, on);
         sfsm::cp4(bslot(ring, st, 0, tid), f.mR + s, on);
         sfsm::cp4(bslot(ring, st, 1, tid), f.mC + s, on);
         sfsm::cp4(bslot(ring, st, 2, tid), f.valid + s, on);
@@ -377,7 +387,7 @@ __device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a,
             p1[j] = p2[j] = db1[j] = th1[j] = tvp[j] = g0p[j] = g1p[j] = g2p[j] = kv1[j] = ks1[j] = oA[j] = oB[j] = T(0);
             e1[j] = e2[j] = false;
         }
-        const int nbeg = y0 - 2, nend = y1 + 2;
+        const int nbeg = y0 - (MODE == 3 ? 1 : 2), nend = y1 + (MODE == 3 ? 1 : 2);
         auto row_on = [&](int n) { return col_in && n >= 0 && n < H && n < nend; };
 #pragma unroll
         for (int k = 0; k < D - 1; ++k) issue(f, a, ring, k, tid, row_on(nbeg + k), x0 + (long)W * (nbeg + k));
@@ -389,8 +399,9 @@ __device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a,
                 issue(f, a, ring, sf, tid, row_on(n + D - 1), s + (long)W * (D - 1));
             }
             sfsm::wait<D - 1>();
-            T pn[4], g0[4], g1[4], g2[4], di[4];
-            rd(ring, st, A_P, tid, pn); rd(ring, st, A_G0, tid, g0); rd(ring, st, A_G1, tid, g1); rd(ring, st, A_G2, tid, g2);
+            T pn[4], g0[4] = {}, g1[4] = {}, g2[4] = {}, di[4];
+            rd(ring, st, A_P, tid, pn);
+            if (HAS_G) { rd(ring, st, A_G0, tid, g0); rd(ring, st, A_G1, tid, g1); rd(ring, st, A_G2, tid, g2); }
             rd(ring, st, A_DI, tid, di);
             const uchar4 mr = rdb(ring, st, 0, tid), mc = rdb(ring, st, 1, tid), va = rdb(ring, st, 2, tid);
             if (MODE == 1) {
@@ -405,7 +416,7 @@ __device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a,
             T db[4], thn[4], kvn[4], ksn[4], oC[4];
             bool en[4];
             const unsigned char mrb[4] = {mr.x, mr.y, mr.z, mr.w}, mcb[4] = {mc.x, mc.y, mc.z, mc.w}, vab[4] = {va.x, va.y, va.z, va.w};
-            if (MODE == 2) rd(ring, st, A_BI, tid, db);
+            if (MODE >= 2) rd(ring, st, A_BI, tid, db);
             else {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) db[j] = g0[j] * pn[j] + g1[j] * (j > 0 ? pn[j > 0 ? j - 1 : 0] : pl) + g2[j] * p1[j];
@@ -415,13 +426,38 @@ __device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a,
             for (int j = 0; j < 4; ++j) {
                 const T in = xin[j] * yin;
                 const T mh = sfsm::u8f(mrb[j], T(0)), mv = sfsm::u8f(mcb[j], T(0));
-                thn[j] = (wg2 * mh * mh * in) * (db[j] - (j < 3 ? db[j < 3 ? j + 1 : 3] : dbr));
+                const T dh = db[j] - (j < 3 ? db[j < 3 ? j + 1 : 3] : dbr);
+                thn[j] = (wg2 * mh * mh * in) * dh;
                 kvn[j] = wg2 * mv * mv * in;
                 ksn[j] = vab[j] == 1 ? ws2 * in : T(0);
                 en[j] = di[j] > T(0);
-                oC[j] = en[j] ? wp2 * (MODE == 2 ? pn[j] - di[j] : pn[j]) : T(0);
+                oC[j] = en[j] ? wp2 * (MODE >= 2 ? pn[j] - di[j] : pn[j]) : T(0);
+                if (MODE == 3) oC[j] = oC[j] * (pn[j] - di[j]) + (en[j] ? thn[j] * dh : T(0));      // r_p^2 + r_h^2 of row n
             }
-            if (LM && MODE != 2) {
+            if (MODE == 3) {
+                // cost pass: sum of squared residuals centred on non-excluded pixels (k_cost in engine.cuh); rows n and n-1
+                T cs = T(0);
+                const T a1c = ((T)(n - 1) - f.u_y) * ify;
+                const T p1rc = __shfl_down_sync(FULL, p1[0], 1);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (n >= y0 && n < y1) cs += oC[j];
+                    if (n - 1 >= y0 && n - 1 < y1 && e1[j]) {
+                        const T dv = db1[j] - db[j];
+                        const T l = j > 0 ? p1[j > 0 ? j - 1 : 0] : p1l, r = j < 3 ? p1[j < 3 ? j + 1 : 3] : p1rc;
+                        const T lap = T(4) * p1[j] - (l + p2[j] + r + pn[j]);
+                        const T u0 = a0[j] * lap - ifx * (r - l), u1 = a1c * lap - ify * (pn[j] - p2[j]);
+                        cs += kv1[j] * dv * dv + ks1[j] * (u0 * u0 + u1 * u1 + lap * lap);
+                    }
+                }
+                if (owner) acc += (double)(T(0.5) * cs);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { p2[j] = p1[j]; p1[j] = pn[j]; db1[j] = db[j]; kv1[j] = kvn[j]; ks1[j] = ksn[j]; e1[j] = en[j]; }
+                p1l = pl;
+                st = st + 1 == D ? 0 : st + 1;
+                continue;
+            }
+            if (USE_C) {
                 T c[4]; rd(ring, st, A_C, tid, c);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) oC[j] += c[j] * pn[j];
@@ -528,6 +564,69 @@ k_sfs_init(SfsFunctor<T> f, Vec<T> delta, Vec<T> r, Vec<T> p, Vec<T> pre, double
     block_accumulate(acc, aNum);
 }
 
+template <class T>
+__global__ void __launch_bounds__(256, sizeof(T) == 4 ? 2 : 1) k_sfs_cost(SfsFunctor<T> f, double* target) {
+    extern __shared__ __align__(16) unsigned char sfs_ring[];
+    SfsMarchArgs<T> a{};
+    double acc = 0.0;
+    SfsMarch<T, 3, false>::run(f, a, sfs_ring, acc);
+    block_accumulate(acc, target);
+}
+
+// precompute with one thread per quad of a row: 128-bit loads of the three X / D_i rows and two image rows, lateral
+// neighbours from the adjacent lanes (the first and last lane of a warp fetch theirs), 128-bit stores of B_I, g0..g2.
+template <class T>
+__global__ void __launch_bounds__(256) k_sfs_precompute4(SfsFunctor<T> f) {
+    constexpr unsigned FULL = 0xffffffffu;
+    const int W = f.W, H = f.H;
+    const int tiles_x = (W / 4 + 31) / 32;
+    const long ntiles = (long)tiles_x * ((H + 7) / 8);
+    const int lane = threadIdx.x;
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int x0 = ((int)(tile % tiles_x) * 32 + lane) * 4;
+        const int y = (int)(tile / tiles_x) * 8 + threadIdx.y;
+        const bool on = x0 < W && y < H;
+        const long s = (long)y * W + x0;
+        const bool up = on && y > 0, dn = on && y + 1 < H;
+        T xc[4] = {}, xu[4] = {}, xd[4] = {}, dc[4] = {}, du[4] = {}, dd[4] = {}, ic[4] = {}, iu[4] = {};
+        if (on) { load4(f.X + s, xc); load4(f.Di + s, dc); load4(f.Im + s, ic); }
+        if (up) { load4(f.X + s - W, xu); load4(f.Di + s - W, du); load4(f.Im + s - W, iu); }
+        if (dn) { load4(f.X + s + W, xd); load4(f.Di + s + W, dd); }
+        const bool ledge = on && lane == 0 && x0 > 0, redge = on && (lane == 31 || x0 + 4 >= W) && x0 + 4 < W;
+        T xl = __shfl_up_sync(FULL, xc[3], 1), dl = __shfl_up_sync(FULL, dc[3], 1), il = __shfl_up_sync(FULL, ic[3], 1);
+        T xr = __shfl_down_sync(FULL, xc[0], 1), dr = __shfl_down_sync(FULL, dc[0], 1);
+        if (lane == 0) { xl = ledge ? f.X[s - 1] : T(0); dl = ledge ? f.Di[s - 1] : T(0); il = ledge ? f.Im[s - 1] : T(0); }
+        if (lane == 31) { xr = redge ? f.X[s + 4] : T(0); dr = redge ? f.Di[s + 4] : T(0); }
+        if (!on) continue;
+        T b[4], g0[4], g1[4], g2[4];
+        unsigned char vb[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int x = x0 + j;
+            const T d00 = xc[j], dm0 = j > 0 ? xc[j > 0 ? j - 1 : 0] : xl, dp0 = j < 3 ? xc[j < 3 ? j + 1 : 3] : xr;
+            const T d0m = xu[j], d0p = xd[j];
+            const T vl = j > 0 ? dc[j > 0 ? j - 1 : 0] : dl, vr = j < 3 ? dc[j < 3 ? j + 1 : 3] : dr;
+            const T iml = j > 0 ? ic[j > 0 ? j - 1 : 0] : il;
+            const bool inb = f.inbexp1(x, y);
+            const bool ok = inb && vl > T(0) && dc[j] > T(0) && du[j] > T(0);
+            T bb = T(0), g[3] = {T(0), T(0), T(0)};
+            if (ok) f.shade(x, y, d00, dm0, d0m, ic[j] * T(0.5) + T(0.25) * (iml + iu[j]), bb, g);
+            b[j] = bb; g0[j] = g[0]; g1[j] = g[1]; g2[j] = g[2];
+            const bool v = inb && dc[j] > T(0) && du[j] > T(0) && dd[j] > T(0) && vl > T(0) && vr > T(0) &&
+                           fabs(d00 - d0m) < T(0.01) && fabs(d00 - d0p) < T(0.01) && fabs(d00 - dm0) < T(0.01) && fabs(d00 - dp0) < T(0.01);
+            vb[j] = v ? 1 : 0;
+        }
+        st4v(f.BI + s, b); st4v(f.G0 + s, g0); st4v(f.G1 + s, g1); st4v(f.G2 + s, g2);
+        *reinterpret_cast<uchar4*>(f.valid + s) = make_uchar4(vb[0], vb[1], vb[2], vb[3]);
+    }
+}
+
+template <class T> void SfsFunctor<T>::fast_precompute(cudaStream_t stream, int nsm) const {
+    const long ntiles = (long)((W / 4 + 31) / 32) * ((H + 7) / 8);
+    k_sfs_precompute4<T><<<(unsigned)std::min<long>(ntiles, (long)nsm * 8), dim3(32, 8, 1), 0, stream>>>(*this);
+}
+
+template <class T> auto SfsFunctor<T>::fast_cost_kernel() { return &k_sfs_cost<T>; }
 template <class T> template <bool FUSED, bool LM> auto SfsFunctor<T>::fast_kernel() { return &k_sfs_march<T, FUSED, LM>; }
 template <class T> auto SfsFunctor<T>::fast_init_kernel() { return &k_sfs_init<T>; }
 template <class T> size_t SfsFunctor<T>::fast_smem() const {
@@ -537,6 +636,7 @@ template <class T> size_t SfsFunctor<T>::fast_smem() const {
     m = std::max<size_t>(m, (size_t)SfsMarch<T, 1, false>::STAGE * SfsMarch<T, 1, false>::D);
     m = std::max<size_t>(m, (size_t)SfsMarch<T, 1, true>::STAGE * SfsMarch<T, 1, true>::D);
     m = std::max<size_t>(m, (size_t)SfsMarch<T, 2, false>::STAGE * SfsMarch<T, 2, false>::D);
+    m = std::max<size_t>(m, (size_t)SfsMarch<T, 3, false>::STAGE * SfsMarch<T, 3, false>::D);
     return m;
 }
 
