@@ -53,12 +53,12 @@ WORKLOADS = {
     "sfs_2048": dict(builder=examples.sfs_synthetic, args=(2048, 2048), kw=dict(n_iter=10, l_iter=10, holes=False),
                      U=1, ijtj=5.5, iexcl=1, extra=0, mask=None,
                      desc="shape_from_shading 2048x2048, GN 10x10 PCG, fp32"),
-    "volumetric_512": dict(builder=examples.volumetric_synthetic, args=(512, 512, 512), kw=dict(n_iter=2, l_iter=20),
+    "volumetric_512": dict(builder=examples.volumetric_synthetic, args=(512, 512, 512), kw=dict(n_iter=2, l_iter=60),
                            U=6, ijtj=9, iexcl=0, extra=0, mask=None,
-                           desc="volumetric_mesh_deformation 512^3, GN 2x20 PCG, fp32"),
-    "volumetric_256": dict(builder=examples.volumetric_synthetic, args=(256, 256, 256), kw=dict(n_iter=2, l_iter=20),
+                           desc="volumetric_mesh_deformation 512^3, GN 2x60 PCG (the driver's 60 linear iterations per nonlinear step, main.cpp:32-36), fp32"),
+    "volumetric_256": dict(builder=examples.volumetric_synthetic, args=(256, 256, 256), kw=dict(n_iter=2, l_iter=60),
                            U=6, ijtj=9, iexcl=0, extra=0, mask=None,
-                           desc="volumetric_mesh_deformation 256^3, GN 2x20 PCG, fp32"),
+                           desc="volumetric_mesh_deformation 256^3, GN 2x60 PCG, fp32"),
     "arap_1m": dict(builder=examples.arap_synthetic, args=(1024, 1024), kw=dict(n_iter=2, l_iter=100),
                     U=6, ijtj=9, iexcl=0, extra=48, mask=None,
                     desc="arap_mesh_deformation 1024x1024-vertex mesh (6.28M directed edges), GN 2x100 PCG, fp32"),

@@ -486,16 +486,30 @@ __global__ void k_graph_ctc(F f, long E, VecOf<F> CtC, typename F::Scalar inv_ra
 // ------------------------------------------------------------------------------ graph terms as a gather
 // Instead of one global atomicAdd per edge and channel (the reference, o.t:2586-2600), J^T J p over the
 // graph domain is gathered per vertex: at Init the engine sorts every (edge, slot) incidence by
-// (vertex, slot) -- a segmented, deterministic adjacency -- and a functor with HAS_GATHER then evaluates,
-// for its own vertex, the contribution of every incident edge.  No atomics, no memset of Ap, Ap is written
-// once, and alphaDen = <p, Ap> comes out of the same kernel.
+// (vertex, other endpoint, slot) -- a segmented, deterministic adjacency in which the two directions of a mesh edge
+// are neighbours -- and a functor with HAS_GATHER then evaluates, for its own vertex, the contribution of every
+// incident edge.  A sorted entry is 2 * payload + slot; k_incidence_merge turns it into 4 * payload + direction
+// bits.  No atomics, no memset of Ap, Ap is written once, and
+// alphaDen = <p, Ap> comes out of the same kernel.
 template <class F>
-__global__ void k_incidence_keys(F f, long n, unsigned* keys, unsigned* vals) {
+__global__ void k_incidence_keys(F f, long n, unsigned* entries, unsigned* vertices) {
+    static_assert(F::GV <= 2, "entry = 2 * payload + slot");
     const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
     if (i >= n) return;
     const long e = i / F::GV; const int slot = (int)(i % F::GV);
-    keys[i] = (unsigned)f.graph_vertex(e, slot) * F::GV + slot;
-    vals[i] = f.incidence_payload(e, slot);
+    entries[i] = f.incidence_payload(e, slot) * 2u + (unsigned)slot;
+    vertices[i] = (unsigned)f.graph_vertex(e, slot);
+}
+// Merge the two directions of a mesh edge: sorted entries 2n, 2n+1 of the same vertex become (4n + 3, SKIP); a lone
+// entry 2n + slot becomes 4n + 1 (edge v -> n) or 4n + 2 (edge n -> v).  Positions are kept, so no compaction.
+static constexpr unsigned OPTK_INC_SKIP = 0xffffffffu;
+static __global__ void k_incidence_merge(const unsigned* __restrict__ entries, const unsigned* __restrict__ vertices, long n, unsigned* out) {
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned e = entries[i], v = vertices[i];
+    const unsigned nb = e >> 1;
+    if (e & 1u) out[i] = (i > 0 && vertices[i - 1] == v && entries[i - 1] == e - 1u) ? OPTK_INC_SKIP : nb * 4u + 2u;
+    else        out[i] = (i + 1 < n && vertices[i + 1] == v && entries[i + 1] == e + 1u) ? nb * 4u + 3u : nb * 4u + 1u;
 }
 // off[k] = first position whose key is >= k, for k in [0, nkeys]
 static __global__ void k_incidence_offsets(const unsigned* __restrict__ keys, long n, long nkeys, int* off) {
@@ -506,7 +520,7 @@ static __global__ void k_incidence_offsets(const unsigned* __restrict__ keys, lo
     for (long k = lo; k <= hi; ++k) off[k] = (int)i;
 }
 template <class F, bool LM>
-__global__ void __launch_bounds__(128) k_gather_jtj(F f, long N, const int* __restrict__ off, const unsigned* __restrict__ inc,
+__global__ void __launch_bounds__(128, sizeof(typename F::Scalar) == 4 ? 6 : 2) k_gather_jtj(F f, long N, const int* __restrict__ off, const unsigned* __restrict__ inc,
                                                     VecOf<F> dir, VecOf<F> out,
                                                     VecOf<F> CtC, double* den, double* zero_slot) {
     using T = typename F::Scalar;
@@ -515,7 +529,7 @@ __global__ void __launch_bounds__(128) k_gather_jtj(F f, long N, const int* __re
     if (zero_slot && blockIdx.x == 0 && threadIdx.x == 0) *zero_slot = 0.0;
     for (long v = blockIdx.x * (long)blockDim.x + threadIdx.x; v < N; v += (long)gridDim.x * blockDim.x) {
         T o[U];
-        f.gatherJTJ(v, off + v * F::GV, inc, dir, o);
+        f.gatherJTJ(v, off + v, inc, dir, o);
         T dsum = T(0);
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -821,7 +835,7 @@ struct Engine : OptK_Plan {
     // nonlinear iteration of every solve because the index arrays belong to the caller
     void build_incidence() {
         if constexpr (F::HAS_GATHER) {
-            const long n = E * F::GV, nkeys = N * F::GV;
+            const long n = E * F::GV, nkeys = N;
             if (!inc) {
                 OPTK_CUDA(cudaMalloc(&inc, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
                 OPTK_CUDA(cudaMalloc(&inc_off, (size_t)(nkeys + 1) * sizeof(int)));
@@ -831,15 +845,18 @@ struct Engine : OptK_Plan {
                 cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp_bytes, key_a, key_b, val_a, inc, (int)n);
                 OPTK_CUDA(cudaMalloc(&sort_tmp, sort_tmp_bytes));
             }
-            int bits = 1;
-            while ((1L << bits) < nkeys) ++bits;
+            int vbits = 1;
+            while ((1L << vbits) < nkeys) ++vbits;
             if (n > 0) {
+                // two stable passes: by entry (other endpoint, slot), then by vertex
                 this->launch("graphIncidenceKeys", dim3((unsigned)((n + 255) / 256)), dim3(256), k_incidence_keys<F>, f, n, key_a, val_a);
                 this->pre_launch("graphIncidenceSort");
-                cub::DeviceRadixSort::SortPairs(sort_tmp, sort_tmp_bytes, key_a, key_b, val_a, inc, (int)n, 0, bits, stream);
+                cub::DeviceRadixSort::SortPairs(sort_tmp, sort_tmp_bytes, key_a, key_b, val_a, inc, (int)n, 0, vbits + 1, stream);   // entries -> key_b, vertices -> inc
+                cub::DeviceRadixSort::SortPairs(sort_tmp, sort_tmp_bytes, inc, key_a, key_b, val_a, (int)n, 0, vbits, stream);      // vertices -> key_a, entries -> val_a
                 this->post_launch();
+                this->launch("graphIncidenceMerge", dim3((unsigned)((n + 255) / 256)), dim3(256), k_incidence_merge, (const unsigned*)val_a, (const unsigned*)key_a, n, inc);
             }
-            this->launch("graphIncidenceOffsets", dim3((unsigned)((n + 1 + 255) / 256)), dim3(256), k_incidence_offsets, (const unsigned*)key_b, n, nkeys, inc_off);
+            this->launch("graphIncidenceOffsets", dim3((unsigned)((n + 1 + 255) / 256)), dim3(256), k_incidence_offsets, (const unsigned*)key_a, n, nkeys, inc_off);
         }
     }
     bool use_gather() const { return F::HAS_GATHER && getenv("OPTB200_GRAPH_ATOMICS") == nullptr; }

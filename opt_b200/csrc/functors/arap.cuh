@@ -17,70 +17,75 @@ struct ArapFunctor : FunctorDefaults<T> {
     int W, H, D, E;
     T* O; T* A; const T* Ur; const T* Cn; const int* v0; const int* v1;
     T w_fit, w_reg;
-    // per-vertex table refreshed by precompute (once per nonlinear iteration): SoA planes sa ca sb cb sg cg ux uy uz fit
+    // per-vertex table refreshed by precompute (once per nonlinear iteration), 12 scalars per vertex so that a
+    // neighbour costs three 128-bit loads: [sa ca sb cb | sg cg ux uy | uz fit 0 0]
     T* tab = nullptr;
-    long tplane = 0;
+    static constexpr int TS = 12;
     static constexpr bool HAS_PRECOMPUTE = true, HAS_GATHER = true;
     void plan(const unsigned* d) { W = d[0]; H = 1; D = 1; E = d[1]; }
-    void alloc_temporaries(cudaStream_t) {
-        tplane = round_up((long)W, 64);
-        OPTK_CUDA(cudaMalloc(&tab, (size_t)10 * tplane * sizeof(T)));
-    }
+    void alloc_temporaries(cudaStream_t) { OPTK_CUDA(cudaMalloc(&tab, (size_t)TS * round_up((long)W, 64) * sizeof(T))); }
     void free_temporaries() { cudaFree(tab); tab = nullptr; }
     __device__ void precompute(int, int, int, long s) const {
-        T a[3], u[3]; load3(A + s * 3, a); load3(Ur + s * 3, u);
+        T a[3], u[3], t[TS]; load3(A + s * 3, a); load3(Ur + s * 3, u);
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            T sn, cs; sincos_t(a[k], sn, cs);
-            tab[(2 * k) * tplane + s] = sn; tab[(2 * k + 1) * tplane + s] = cs; tab[(6 + k) * tplane + s] = u[k];
-        }
-        tab[9 * tplane + s] = fit_valid(s) ? T(1) : T(0);
+        for (int k = 0; k < 3; ++k) { sincos_t(a[k], t[2 * k], t[2 * k + 1]); t[6 + k] = u[k]; }
+        t[9] = fit_valid(s) ? T(1) : T(0); t[10] = t[11] = T(0);
+#pragma unroll
+        for (int k = 0; k < TS; k += 4) st4v(tab + s * TS + k, t + k);
     }
-    // ---- gather form of J^T J p (engine.cuh, k_gather_jtj): incidences of a vertex sorted by slot; the
-    // payload is the OTHER endpoint of the edge, so the index arrays are not touched inside the PCG loop
+    // ---- gather form of J^T J p (engine.cuh, k_gather_jtj).  The incidences of a vertex are sorted by the other
+    // endpoint n of the edge and the two directions of a mesh edge merged: entry = 4 n + [edge v -> n] + 2 [edge n -> v]
+    // (or SKIP), so both share one fetch of the neighbour's table row and direction; the index arrays are not touched
+    // inside the PCG loop.
     __device__ long graph_vertex(long e, int slot) const { return slot == 0 ? v0[e] : v1[e]; }
     __device__ unsigned incidence_payload(long e, int slot) const { return (unsigned)(slot == 0 ? v1[e] : v0[e]); }
     // With M_a = sum_j pA_a[j] dR/da_j(A_a): J p of edge a->b is jp_ab = (pO_a - pO_b) - M_a (U_a - U_b);
     //   Ap_O(v) = vf pO_v + w_r^2 ( sum_{v->n} jp_vn - sum_{n->v} jp_nv ),  Ap_A(v)[j] = -w_r^2 <dR/da_j(A_v), sum_{v->n} jp_vn u^T>
     template <class P> __device__ void gatherJTJ(long v, const int* off, const unsigned* inc, const P& p, T* o) const {
-        const T* tv = tab + v;
-        T tr[6], pc[6], uc[3];
+        T tr[TS], pc[6];
 #pragma unroll
-        for (int k = 0; k < 6; ++k) { tr[k] = tv[k * tplane]; pc[k] = p(k, v); }
+        for (int k = 0; k < TS; k += 4) load4(tab + v * TS + k, tr + k);
 #pragma unroll
-        for (int k = 0; k < 3; ++k) uc[k] = tv[(6 + k) * tplane];
-        const T fit = tv[9 * tplane];
-        RotM<T> rm; rm.set(tr);
-        T M[3][3]; rm.combine(pc[3], pc[4], pc[5], M);
+        for (int k = 0; k < 6; ++k) pc[k] = p(k, v);
+        const T* uc = tr + 6;
+        T M[3][3];
+        { RotM<T> rm; rm.set(tr); rm.combine(pc[3], pc[4], pc[5], M); }
         T S[3][3] = {{T(0), T(0), T(0)}, {T(0), T(0), T(0)}, {T(0), T(0), T(0)}}, acc[3] = {T(0), T(0), T(0)};
-        const int b0 = off[0], b1 = off[1], b2 = off[2];
-        for (int i = b0; i < b1; ++i) {                      // edges v -> n
-            const long n = inc[i];
-            T u[3], q[3];
+        const int b0 = off[0], b1 = off[1];
+        unsigned e = b0 < b1 ? inc[b0] : 0xffffffffu;
+        for (int i = b0; i < b1; ++i) {
+            const unsigned en = i + 1 < b1 ? inc[i + 1] : 0xffffffffu;     // fetched one neighbour ahead
+            if (e != 0xffffffffu) {
+                const long n = e >> 2;
+                T tn[TS], pn[6], u[3], q[3];
 #pragma unroll
-            for (int k = 0; k < 3; ++k) { u[k] = uc[k] - tab[(6 + k) * tplane + n]; q[k] = pc[k] - p(k, n); }
+                for (int k = 0; k < TS; k += 4) load4(tab + n * TS + k, tn + k);
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const T jp = nfma(M[k][0], u[0], nfma(M[k][1], u[1], nfma(M[k][2], u[2], q[k])));
-                acc[k] += jp;
-                S[k][0] = fma(jp, u[0], S[k][0]); S[k][1] = fma(jp, u[1], S[k][1]); S[k][2] = fma(jp, u[2], S[k][2]);
+                for (int k = 0; k < 3; ++k) pn[k] = p(k, n);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) { u[k] = uc[k] - tn[6 + k]; q[k] = pc[k] - pn[k]; }
+                if (e & 1u) {                                     // edge v -> n
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) {
+                        const T jp = nfma(M[k][0], u[0], nfma(M[k][1], u[1], nfma(M[k][2], u[2], q[k])));
+                        acc[k] += jp;
+                        S[k][0] = fma(jp, u[0], S[k][0]); S[k][1] = fma(jp, u[1], S[k][1]); S[k][2] = fma(jp, u[2], S[k][2]);
+                    }
+                }
+                if (e & 2u) {                                     // edge n -> v: acc -= jp_nv = -(q - M_n u)
+#pragma unroll
+                    for (int k = 3; k < 6; ++k) pn[k] = p(k, n);
+                    RotM<T> rn; rn.set(tn);
+                    T Mn[3][3]; rn.combine(pn[3], pn[4], pn[5], Mn);
+#pragma unroll
+                    for (int k = 0; k < 3; ++k)
+                        acc[k] = nfma(Mn[k][0], u[0], nfma(Mn[k][1], u[1], nfma(Mn[k][2], u[2], acc[k] + q[k])));
+                }
             }
+            e = en;
         }
-        for (int i = b1; i < b2; ++i) {                      // edges n -> v
-            const long n = inc[i];
-            const T* tn = tab + n;
-            T t6[6], u[3], q[3], Mn[3][3];
-#pragma unroll
-            for (int k = 0; k < 6; ++k) t6[k] = tn[k * tplane];
-#pragma unroll
-            for (int k = 0; k < 3; ++k) { u[k] = tn[(6 + k) * tplane] - uc[k]; q[k] = p(k, n) - pc[k]; }
-            RotM<T> rn; rn.set(t6);
-            rn.combine(p(3, n), p(4, n), p(5, n), Mn);
-#pragma unroll
-            for (int k = 0; k < 3; ++k)                       // acc -= jp_nv
-                acc[k] = fma(Mn[k][0], u[0], fma(Mn[k][1], u[1], fma(Mn[k][2], u[2], acc[k] - q[k])));
-        }
-        const T wr2 = w_reg * w_reg, vf = fit * w_fit * w_fit;
+        const T wr2 = w_reg * w_reg, vf = tr[9] * w_fit * w_fit;
+        RotM<T> rm; rm.set(tr);
         T oA[3]; rm.project(S, oA);
 #pragma unroll
         for (int k = 0; k < 3; ++k) { o[k] = vf * pc[k] + wr2 * acc[k]; o[3 + k] = wr2 * oA[k]; }
