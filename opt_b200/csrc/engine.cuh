@@ -16,6 +16,7 @@
 #include <vector>
 #include <nccl.h>
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_select.cuh>
 #include "common.cuh"
 #include "functors/math.cuh"
 #include "optk.h"
@@ -500,16 +501,22 @@ __global__ void k_incidence_keys(F f, long n, unsigned* entries, unsigned* verti
     entries[i] = f.incidence_payload(e, slot) * 2u + (unsigned)slot;
     vertices[i] = (unsigned)f.graph_vertex(e, slot);
 }
-// Merge the two directions of a mesh edge: sorted entries 2n, 2n+1 of the same vertex become (4n + 3, SKIP); a lone
-// entry 2n + slot becomes 4n + 1 (edge v -> n) or 4n + 2 (edge n -> v).  Positions are kept, so no compaction.
+// Merge the two directions of a mesh edge: sorted entries 2n, 2n+1 of the same vertex become one entry 4n + 3 (the
+// second is marked SKIP, in both arrays, and compacted away); a lone entry 2n + slot becomes 4n + 1 (edge v -> n) or
+// 4n + 2 (edge n -> v).
 static constexpr unsigned OPTK_INC_SKIP = 0xffffffffu;
-static __global__ void k_incidence_merge(const unsigned* __restrict__ entries, const unsigned* __restrict__ vertices, long n, unsigned* out) {
+struct IncidenceKept { __host__ __device__ bool operator()(unsigned e) const { return e != OPTK_INC_SKIP; } };
+static __global__ void k_incidence_merge(const unsigned* __restrict__ entries, const unsigned* __restrict__ vertices, long n,
+                                         unsigned* out, unsigned* vout) {
     const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
     if (i >= n) return;
     const unsigned e = entries[i], v = vertices[i];
     const unsigned nb = e >> 1;
-    if (e & 1u) out[i] = (i > 0 && vertices[i - 1] == v && entries[i - 1] == e - 1u) ? OPTK_INC_SKIP : nb * 4u + 2u;
-    else        out[i] = (i + 1 < n && vertices[i + 1] == v && entries[i + 1] == e + 1u) ? nb * 4u + 3u : nb * 4u + 1u;
+    unsigned o;
+    if (e & 1u) o = (i > 0 && vertices[i - 1] == v && entries[i - 1] == e - 1u) ? OPTK_INC_SKIP : nb * 4u + 2u;
+    else        o = (i + 1 < n && vertices[i + 1] == v && entries[i + 1] == e + 1u) ? nb * 4u + 3u : nb * 4u + 1u;
+    out[i] = o;
+    vout[i] = o == OPTK_INC_SKIP ? OPTK_INC_SKIP : v;
 }
 // off[k] = first position whose key is >= k, for k in [0, nkeys]
 static __global__ void k_incidence_offsets(const unsigned* __restrict__ keys, long n, long nkeys, int* off) {
@@ -520,7 +527,7 @@ static __global__ void k_incidence_offsets(const unsigned* __restrict__ keys, lo
     for (long k = lo; k <= hi; ++k) off[k] = (int)i;
 }
 template <class F, bool LM>
-__global__ void __launch_bounds__(128, sizeof(typename F::Scalar) == 4 ? 6 : 2) k_gather_jtj(F f, long N, const int* __restrict__ off, const unsigned* __restrict__ inc,
+__global__ void __launch_bounds__(128, sizeof(typename F::Scalar) == 4 ? 5 : 2) k_gather_jtj(F f, long N, const int* __restrict__ off, const unsigned* __restrict__ inc,
                                                     VecOf<F> dir, VecOf<F> out,
                                                     VecOf<F> CtC, double* den, double* zero_slot) {
     using T = typename F::Scalar;
@@ -710,6 +717,7 @@ struct Engine : OptK_Plan {
     unsigned* inc = nullptr;                                // HAS_GATHER: incidence payloads sorted by (vertex, slot)
     int* inc_off = nullptr;                                 //             N*GV + 1 segment offsets
     void* sort_tmp = nullptr; size_t sort_tmp_bytes = 0;
+    int* inc_count = nullptr;                               //             entries kept after merging edge directions
     unsigned *key_a = nullptr, *key_b = nullptr, *val_a = nullptr;
     bool fuse = true;                                       // fused PCGStep3+PCGStep1 (single rank)
     double* scal = nullptr;
@@ -761,7 +769,7 @@ struct Engine : OptK_Plan {
         f.free_temporaries();
         if (comm) ncclCommDestroy(comm);
         cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFree(active4);
-        cudaFree(inc); cudaFree(inc_off); cudaFree(sort_tmp); cudaFree(key_a); cudaFree(key_b); cudaFree(val_a);
+        cudaFree(inc); cudaFree(inc_off); cudaFree(inc_count); cudaFree(sort_tmp); cudaFree(key_a); cudaFree(key_b); cudaFree(val_a);
         base_destroy();
     }
     int unknown_channels() const override { return U; }
@@ -842,7 +850,11 @@ struct Engine : OptK_Plan {
                 OPTK_CUDA(cudaMalloc(&key_a, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
                 OPTK_CUDA(cudaMalloc(&key_b, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
                 OPTK_CUDA(cudaMalloc(&val_a, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
+                size_t sel_bytes = 0;
+                OPTK_CUDA(cudaMalloc(&inc_count, sizeof(int)));
                 cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp_bytes, key_a, key_b, val_a, inc, (int)n);
+                cub::DeviceSelect::If(nullptr, sel_bytes, key_a, key_b, inc_count, (int)n, IncidenceKept());
+                sort_tmp_bytes = std::max(sort_tmp_bytes, sel_bytes);
                 OPTK_CUDA(cudaMalloc(&sort_tmp, sort_tmp_bytes));
             }
             int vbits = 1;
@@ -854,9 +866,19 @@ struct Engine : OptK_Plan {
                 cub::DeviceRadixSort::SortPairs(sort_tmp, sort_tmp_bytes, key_a, key_b, val_a, inc, (int)n, 0, vbits + 1, stream);   // entries -> key_b, vertices -> inc
                 cub::DeviceRadixSort::SortPairs(sort_tmp, sort_tmp_bytes, inc, key_a, key_b, val_a, (int)n, 0, vbits, stream);      // vertices -> key_a, entries -> val_a
                 this->post_launch();
-                this->launch("graphIncidenceMerge", dim3((unsigned)((n + 255) / 256)), dim3(256), k_incidence_merge, (const unsigned*)val_a, (const unsigned*)key_a, n, inc);
+                this->launch("graphIncidenceMerge", dim3((unsigned)((n + 255) / 256)), dim3(256), k_incidence_merge, (const unsigned*)val_a, (const unsigned*)key_a, n, inc, key_b);
+                this->pre_launch("graphIncidenceCompact");
+                cub::DeviceSelect::If(sort_tmp, sort_tmp_bytes, inc, val_a, inc_count, (int)n, IncidenceKept(), stream);      // entries
+                cub::DeviceSelect::If(sort_tmp, sort_tmp_bytes, key_b, key_a, inc_count, (int)n, IncidenceKept(), stream);    // their vertices
+                this->post_launch();
+                std::swap(inc, val_a);
             }
-            this->launch("graphIncidenceOffsets", dim3((unsigned)((n + 1 + 255) / 256)), dim3(256), k_incidence_offsets, (const unsigned*)key_a, n, nkeys, inc_off);
+            int kept = 0;
+            if (n > 0) {
+                OPTK_CUDA(cudaMemcpyAsync(&kept, inc_count, sizeof(int), cudaMemcpyDeviceToHost, stream));
+                OPTK_CUDA(cudaStreamSynchronize(stream));
+            }
+            this->launch("graphIncidenceOffsets", dim3((unsigned)((kept + 1 + 255) / 256)), dim3(256), k_incidence_offsets, (const unsigned*)key_a, (long)kept, nkeys, inc_off);
         }
     }
     bool use_gather() const { return F::HAS_GATHER && getenv("OPTB200_GRAPH_ATOMICS") == nullptr; }

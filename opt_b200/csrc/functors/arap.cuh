@@ -52,37 +52,44 @@ struct ArapFunctor : FunctorDefaults<T> {
         { RotM<T> rm; rm.set(tr); rm.combine(pc[3], pc[4], pc[5], M); }
         T S[3][3] = {{T(0), T(0), T(0)}, {T(0), T(0), T(0)}, {T(0), T(0), T(0)}}, acc[3] = {T(0), T(0), T(0)};
         const int b0 = off[0], b1 = off[1];
-        unsigned e = b0 < b1 ? inc[b0] : 0xffffffffu;
+        // software pipeline: entry i + 2 and the neighbour data of entry i + 1 are in flight while entry i is evaluated
+        T tn[TS], pn[6];
+        unsigned e = 0, e1 = 0;
+        auto fetch = [&](unsigned ent, T* t, T* q6) {
+            const long n = ent >> 2;
+#pragma unroll
+            for (int k = 0; k < TS; k += 4) load4(tab + n * TS + k, t + k);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) q6[k] = p(k, n);
+        };
+        if (b0 < b1) { e = inc[b0]; fetch(e, tn, pn); }
+        if (b0 + 1 < b1) e1 = inc[b0 + 1];
         for (int i = b0; i < b1; ++i) {
-            const unsigned en = i + 1 < b1 ? inc[i + 1] : 0xffffffffu;     // fetched one neighbour ahead
-            if (e != 0xffffffffu) {
-                const long n = e >> 2;
-                T tn[TS], pn[6], u[3], q[3];
+            T tx[TS], px[6];
+            unsigned e2 = 0;
+            if (i + 1 < b1) fetch(e1, tx, px);
+            if (i + 2 < b1) e2 = inc[i + 2];
+            T u[3], q[3];
 #pragma unroll
-                for (int k = 0; k < TS; k += 4) load4(tab + n * TS + k, tn + k);
+            for (int k = 0; k < 3; ++k) { u[k] = uc[k] - tn[6 + k]; q[k] = pc[k] - pn[k]; }
+            if (e & 1u) {                                     // edge v -> n
 #pragma unroll
-                for (int k = 0; k < 3; ++k) pn[k] = p(k, n);
-#pragma unroll
-                for (int k = 0; k < 3; ++k) { u[k] = uc[k] - tn[6 + k]; q[k] = pc[k] - pn[k]; }
-                if (e & 1u) {                                     // edge v -> n
-#pragma unroll
-                    for (int k = 0; k < 3; ++k) {
-                        const T jp = nfma(M[k][0], u[0], nfma(M[k][1], u[1], nfma(M[k][2], u[2], q[k])));
-                        acc[k] += jp;
-                        S[k][0] = fma(jp, u[0], S[k][0]); S[k][1] = fma(jp, u[1], S[k][1]); S[k][2] = fma(jp, u[2], S[k][2]);
-                    }
-                }
-                if (e & 2u) {                                     // edge n -> v: acc -= jp_nv = -(q - M_n u)
-#pragma unroll
-                    for (int k = 3; k < 6; ++k) pn[k] = p(k, n);
-                    RotM<T> rn; rn.set(tn);
-                    T Mn[3][3]; rn.combine(pn[3], pn[4], pn[5], Mn);
-#pragma unroll
-                    for (int k = 0; k < 3; ++k)
-                        acc[k] = nfma(Mn[k][0], u[0], nfma(Mn[k][1], u[1], nfma(Mn[k][2], u[2], acc[k] + q[k])));
+                for (int k = 0; k < 3; ++k) {
+                    const T jp = nfma(M[k][0], u[0], nfma(M[k][1], u[1], nfma(M[k][2], u[2], q[k])));
+                    acc[k] += jp;
+                    S[k][0] = fma(jp, u[0], S[k][0]); S[k][1] = fma(jp, u[1], S[k][1]); S[k][2] = fma(jp, u[2], S[k][2]);
                 }
             }
-            e = en;
+            if (e & 2u) {                                     // edge n -> v: acc -= jp_nv = -(q - M_n u)
+                T mu[3]; rot_deriv_apply(tn, pn[3], pn[4], pn[5], u, mu);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) acc[k] += q[k] - mu[k];
+            }
+#pragma unroll
+            for (int k = 0; k < TS; ++k) tn[k] = tx[k];
+#pragma unroll
+            for (int k = 0; k < 6; ++k) pn[k] = px[k];
+            e = e1; e1 = e2;
         }
         const T wr2 = w_reg * w_reg, vf = tr[9] * w_fit * w_fit;
         RotM<T> rm; rm.set(tr);

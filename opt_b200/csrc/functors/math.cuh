@@ -94,5 +94,19 @@ struct RotM {
     }
 };
 
+// M u for M = pa dR/dalpha + pb dR/dbeta + pg dR/dgamma of R = Rz(gamma) Ry(beta) Rx(alpha) (lib.t:84-98), from the
+// factors instead of the assembled matrix: with a = Rx u, b = Ry a,  dRx/dalpha u = (0, -a2, a1),
+// dRy/dbeta a = (b2, 0, -b0),  dRz/dgamma b = (-(Rz b)_1, (Rz b)_0, 0).   t = sa ca sb cb sg cg.
+template <class T>
+__device__ __forceinline__ void rot_deriv_apply(const T* t, T pa, T pb, T pg, const T* u, T* o) {
+    const T sa = t[0], ca = t[1], sb = t[2], cb = t[3], sg = t[4], cg = t[5];
+    const T a1 = ca * u[1] - sa * u[2], a2 = sa * u[1] + ca * u[2];
+    const T b0 = cb * u[0] + sb * a2, b2 = cb * a2 - sb * u[0];
+    const T d0 = pa * (sb * a1) + pb * b2, d1 = -pa * a2, d2 = pa * (cb * a1) - pb * b0;
+    const T z0 = cg * b0 - sg * a1, z1 = sg * b0 + cg * a1;               // (Rz b)_0, (Rz b)_1 with b1 = a1
+    o[0] = cg * d0 - sg * d1 - pg * z1;
+    o[1] = sg * d0 + cg * d1 + pg * z0;
+    o[2] = d2;
+}
 
 }  // namespace optk
