@@ -52,9 +52,9 @@ struct ArapFunctor : FunctorDefaults<T> {
         { RotM<T> rm; rm.set(tr); rm.combine(pc[3], pc[4], pc[5], M); }
         T S[3][3] = {{T(0), T(0), T(0)}, {T(0), T(0), T(0)}, {T(0), T(0), T(0)}}, acc[3] = {T(0), T(0), T(0)};
         const int b0 = off[0], b1 = off[1];
-        // software pipeline: entry i + 2 and the neighbour data of entry i + 1 are in flight while entry i is evaluated
-        T tn[TS], pn[6];
-        unsigned e = 0, e1 = 0;
+        // software pipeline: entry i + 2 and the neighbour data of entry i + 1 are in flight while entry i is evaluated;
+        // two buffers alternate (loop unrolled by two) so that nothing is copied between iterations
+        T tA[TS], qA[6], tB[TS], qB[6];
         auto fetch = [&](unsigned ent, T* t, T* q6) {
             const long n = ent >> 2;
 #pragma unroll
@@ -62,13 +62,7 @@ struct ArapFunctor : FunctorDefaults<T> {
 #pragma unroll
             for (int k = 0; k < 6; ++k) q6[k] = p(k, n);
         };
-        if (b0 < b1) { e = inc[b0]; fetch(e, tn, pn); }
-        if (b0 + 1 < b1) e1 = inc[b0 + 1];
-        for (int i = b0; i < b1; ++i) {
-            T tx[TS], px[6];
-            unsigned e2 = 0;
-            if (i + 1 < b1) fetch(e1, tx, px);
-            if (i + 2 < b1) e2 = inc[i + 2];
+        auto eval = [&](unsigned e, const T* tn, const T* pn) {
             T u[3], q[3];
 #pragma unroll
             for (int k = 0; k < 3; ++k) { u[k] = uc[k] - tn[6 + k]; q[k] = pc[k] - pn[k]; }
@@ -85,11 +79,20 @@ struct ArapFunctor : FunctorDefaults<T> {
 #pragma unroll
                 for (int k = 0; k < 3; ++k) acc[k] += q[k] - mu[k];
             }
-#pragma unroll
-            for (int k = 0; k < TS; ++k) tn[k] = tx[k];
-#pragma unroll
-            for (int k = 0; k < 6; ++k) pn[k] = px[k];
-            e = e1; e1 = e2;
+        };
+        unsigned e0 = 0, e1 = 0;
+        if (b0 < b1) { e0 = inc[b0]; fetch(e0, tA, qA); }
+        if (b0 + 1 < b1) e1 = inc[b0 + 1];
+        for (int i = b0; i < b1; i += 2) {
+            unsigned e2 = 0, e3 = 0;
+            if (i + 1 < b1) fetch(e1, tB, qB);
+            if (i + 2 < b1) e2 = inc[i + 2];
+            eval(e0, tA, qA);
+            if (i + 1 >= b1) break;
+            if (i + 2 < b1) fetch(e2, tA, qA);
+            if (i + 3 < b1) e3 = inc[i + 3];
+            eval(e1, tB, qB);
+            e0 = e2; e1 = e3;
         }
         const T wr2 = w_reg * w_reg, vf = tr[9] * w_fit * w_fit;
         RotM<T> rm; rm.set(tr);
