@@ -791,10 +791,24 @@ struct Engine : OptK_Plan {
         f.o_lo = rank > 0 ? halo : 0;
         f.o_hi = rank < nranks - 1 ? L - halo : L;
         if (f.o_hi - f.o_lo < halo) { fprintf(stderr, "Opt: slab thinner than its halo\n"); return -1; }
+        long slow_off = 0;
         if (nranks > 1) {
             ncclUniqueId id; memcpy(&id, uid, sizeof(id));
             OPTK_NCCL(ncclCommInitRank(&comm, nranks, id, rank));
+            // global index of local row 0 = owned rows of the ranks before this one - own ghost rows
+            int* cnt = nullptr;
+            OPTK_CUDA(cudaMalloc(&cnt, (size_t)(nranks + 1) * sizeof(int)));
+            const int own = f.o_hi - f.o_lo;
+            OPTK_CUDA(cudaMemcpyAsync(cnt + nranks, &own, sizeof(int), cudaMemcpyHostToDevice, stream));
+            OPTK_NCCL(ncclAllGather(cnt + nranks, cnt, 1, ncclInt, comm, stream));
+            std::vector<int> h(nranks);
+            OPTK_CUDA(cudaMemcpyAsync(h.data(), cnt, (size_t)nranks * sizeof(int), cudaMemcpyDeviceToHost, stream));
+            OPTK_CUDA(cudaStreamSynchronize(stream));
+            cudaFree(cnt);
+            for (int r2 = 0; r2 < rank; ++r2) slow_off += h[r2];
+            slow_off -= f.o_lo;
         }
+        f.set_slab_geometry(slow_off, rank > 0, rank < nranks - 1);
         return 0;
     }
     void reduce(int slot, int count = 1) {                  // sum over ranks, in place, device-resident
@@ -1109,6 +1123,7 @@ struct FunctorDefaults {
     static constexpr int GV = 0;
     int E = 0;
     int o_lo = 0, o_hi = 0x7fffffff;                       // owned range along the slowest dimension (slab mode)
+    void set_slab_geometry(long, bool, bool) {}            // global index of local row 0, slab continues below / above
     int unknown_images(void**, int*) const { return 0; }   // grid functors list their AoS unknown images (halo exchange)
     void alloc_temporaries(cudaStream_t) {}
     void free_temporaries() {}

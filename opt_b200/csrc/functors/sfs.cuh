@@ -24,14 +24,20 @@ struct SfsFunctor : FunctorDefaults<T> {
     using Scalar = T;
     static constexpr int U = 1, ND = 2;
     static constexpr bool USE_PRE = false, HAS_EXCLUDE = true, HAS_PRECOMPUTE = true;
-    static constexpr bool SLAB_OK = false;     // the expanded-bounds predicates would need global row numbers
+    // slab mode: the expanded-bounds predicate and the back-projection ray need GLOBAL row numbers; the engine passes the
+    // global index of local row 0 and whether the slab continues above / below (set_slab_geometry), halo = 2 rows
+    long y_off = 0;
+    bool lo_open = false, hi_open = false;
+    void set_slab_geometry(long off, bool lo, bool hi) { y_off = off; lo_open = lo; hi_open = hi; }
+    __host__ __device__ int own_lo() const { return this->o_lo; }
+    __host__ __device__ int own_hi() const { return this->o_hi < H ? this->o_hi : H; }
     // marching J^T J apply (k_sfs_march below): a warp owns a strip of STRIP written pixels and a band of bandR rows
     static constexpr bool HAS_FAST_APPLY = true;
     static constexpr int STRIP = 120;
     int bandR = 16;
     bool fast_ok() const { return W % 4 == 0 && getenv("OPTB200_GENERIC_JTJ") == nullptr; }
     __host__ __device__ int strips() const { return (W + STRIP - 1) / STRIP; }
-    long fast_tiles() const { return ((long)strips() * ((H + bandR - 1) / bandR) + 7) / 8; }
+    long fast_tiles() const { return ((long)strips() * ((own_hi() - own_lo() + bandR - 1) / bandR) + 7) / 8; }
     dim3 fast_block() const { return dim3(32, 8, 1); }
     template <bool FUSED, bool LM> static auto fast_kernel();
     static constexpr bool HAS_FAST_INIT = true;        // PCGInit1 by the same pipeline (k_sfs_init)
@@ -72,12 +78,13 @@ struct SfsFunctor : FunctorDefaults<T> {
     __device__ T* xptr(long s, int) const { return X + s; }
 
     __device__ __forceinline__ bool inimg(int x, int y) const { return x >= 0 && y >= 0 && x < W && y < H; }
-    __device__ __forceinline__ bool inbexp1(int x, int y) const { return x >= 1 && y >= 1 && x + 1 < W && y + 1 < H; }
+    __device__ __forceinline__ bool row_inb(int y) const { return (y >= 1 || lo_open) && (y + 1 < H || hi_open); }
+    __device__ __forceinline__ bool inbexp1(int x, int y) const { return x >= 1 && x + 1 < W && row_inb(y); }
     template <class A> __device__ __forceinline__ A get(const A* im, int x, int y) const { return inimg(x, y) ? im[x + (long)W * y] : A(0); }
     __device__ __forceinline__ bool dv(int x, int y) const { return get(Di, x, y) > T(0); }
     __device__ bool exclude(int x, int y, int, long) const { return !dv(x, y); }
     __device__ __forceinline__ T ax(int x) const { return ((T)x - u_x) / f_x; }
-    __device__ __forceinline__ T ay(int y) const { return ((T)y - u_y) / f_y; }
+    __device__ __forceinline__ T ay(int y) const { return ((T)(y + y_off) - u_y) / f_y; }
     // residual weights including their bounds predicates (0 when the instance does not exist)
     __device__ __forceinline__ T kh(int x, int y) const { return inbexp1(x, y) ? w_g * (T)mR[x + (long)W * y] : T(0); }
     __device__ __forceinline__ T kv(int x, int y) const { return inbexp1(x, y) ? w_g * (T)mC[x + (long)W * y] : T(0); }
@@ -86,7 +93,7 @@ struct SfsFunctor : FunctorDefaults<T> {
     // ---- precompute: B_I, its three gradient images, valid -------------------------------------------
     // B(normal(d00, dm0, d0m)) - shading target and its derivatives wrt (d00, dm0, d0m) at pixel (x, y)
     __device__ __forceinline__ void shade(int x, int y, T d00, T dm0, T d0m, T target, T& b, T* g) const {
-        const T ify = T(1) / f_y, ifx = T(1) / f_x, cx = (u_x - (T)x) / f_x, cy = (u_y - (T)y) / f_y, ifxy = T(1) / (f_x * f_y);
+        const T ify = T(1) / f_y, ifx = T(1) / f_x, cx = (u_x - (T)x) / f_x, cy = (u_y - (T)(y + y_off)) / f_y, ifxy = T(1) / (f_x * f_y);
         // n and its derivatives wrt (d00, dm0, d0m)
         T n[3], dn[3][3];
         n[0] = d0m * (d00 - dm0) * ify;
@@ -359,7 +366,8 @@ __device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a,
     constexpr unsigned FULL = 0xffffffffu;
     const int W = f.W, H = f.H, R = f.bandR;
     const int strips = f.strips();
-    const long nitems = (long)strips * ((H + R - 1) / R);
+    const int row_lo = f.own_lo(), row_hi = f.own_hi();             // slab mode: only the owned rows are produced
+    const long nitems = (long)strips * ((row_hi - row_lo + R - 1) / R);
     const long ntiles = (nitems + 7) / 8;
     const int lane = threadIdx.x, warp = threadIdx.y, tid = warp * 32 + lane;
     const T ifx = T(1) / f.f_x, ify = T(1) / f.f_y;
@@ -370,7 +378,7 @@ __device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a,
         if (item >= nitems) continue;                                  // warp-uniform
         const int strip = (int)(item % strips), band = (int)(item / strips);
         const int x0 = strip * F::STRIP - 4 + lane * 4;               // first of this lane's four pixels
-        const int y0 = band * R, y1 = min(y0 + R, H);
+        const int y0 = row_lo + band * R, y1 = min(y0 + R, row_hi);
         const bool col_in = x0 >= 0 && x0 < W;                        // W % 4 == 0: a quad is inside or outside as a whole
         const bool owner = col_in && lane >= 1 && lane <= 30;
         T a0[4], xin[4];
@@ -410,7 +418,7 @@ __device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a,
                 for (int j = 0; j < 4; ++j) pn[j] = z[j] + beta * pn[j];
                 if (owner && n >= y0 && n < y1) st4v(a.p_new + s, pn);
             }
-            const T yin = (n >= 1 && n + 1 < H) ? T(1) : T(0);
+            const T yin = f.row_inb(n) ? T(1) : T(0);
             // ---- shading terms: dB[n], th[n], tv[n-1], T[n-1] ----
             const T pl = __shfl_up_sync(FULL, pn[3], 1);
             T db[4], thn[4], kvn[4], ksn[4], oC[4];
@@ -437,7 +445,7 @@ __device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a,
             if (MODE == 3) {
                 // cost pass: sum of squared residuals centred on non-excluded pixels (k_cost in engine.cuh); rows n and n-1
                 T cs = T(0);
-                const T a1c = ((T)(n - 1) - f.u_y) * ify;
+                const T a1c = ((T)(n - 1 + f.y_off) - f.u_y) * ify;
                 const T p1rc = __shfl_down_sync(FULL, p1[0], 1);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
@@ -477,7 +485,7 @@ __device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a,
             for (int j = 0; j < 4; ++j) oB[j] += j < 3 ? gT[j < 3 ? j + 1 : 3] : gTr;
             // ---- regularisation terms of row q = n-1 ----
             const T p1r = __shfl_down_sync(FULL, p1[0], 1);
-            const T a1q = ((T)(n - 1) - f.u_y) * ify;
+            const T a1q = ((T)(n - 1 + f.y_off) - f.u_y) * ify;
             T w[4], t0x[4], t1y[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {

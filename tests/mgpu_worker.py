@@ -24,6 +24,11 @@ CASES = {
     # rows of 32 sites: blocked solver vectors + packed kernel, ghost planes exchanged as one contiguous slice
     "volumetric_packed": (lambda: examples.volumetric_synthetic(32, 11, 20, n_iter=2, l_iter=10), 1e-5, 1),
     "volumetric_packed_lm": (lambda: examples.volumetric_synthetic(64, 6, 12, n_iter=3, l_iter=8), 1e-5, 1),
+    # shape_from_shading: 5-point regulariser and B_I differences -> halo 2; global row numbers in the bounds
+    # predicates and the back-projection rays.  Rows of whole quads take the marching kernels, the other case the
+    # generic functor kernels.
+    "sfs": (lambda: examples.sfs_synthetic(64, 44, n_iter=2, l_iter=8), 1e-4, 2),
+    "sfs_lm": (lambda: examples.sfs_synthetic(45, 40, n_iter=3, l_iter=8), 1e-4, 2),
     "volumetric_lm_f64": (lambda: examples.volumetric_synthetic(8, 6, 12, n_iter=3, l_iter=12).as_double(), 1e-9, 1),
 }
 
