@@ -21,7 +21,8 @@ struct IntrinsicFunctor : FunctorDefaults<T> {
     using Scalar = T;
     static constexpr int U = 4, ND = 2;
     static constexpr bool USE_PRE = false, HAS_PRECOMPUTE = true;
-    static constexpr bool SLAB_OK = false;      // the weight images would need a halo of r
+    // slab mode with a halo of one row: every predicate is an in-image test, and the weight images are recomputed
+    // locally on the ghost rows from the exchanged r (engine.cuh: precompute runs over every local site)
     int W, H, D;
     T* R; T* S; const T* Im;
     T w_fit, w_alb, w_shd, pnorm;
