@@ -29,6 +29,9 @@ int  OptB200_PlanSetSlab(Opt_Plan* plan, int rank, int nranks, int halo, const v
 
 /* Kernels launched by this plan since it was created (bench.py's "gpu_launches"). */
 long OptB200_PlanLaunchCount(Opt_Plan* plan);
+/* PCG iterations executed by this plan since it was created.  Gauss-Newton always runs nIterations x lIterations;
+ * Levenberg-Marquardt leaves the inner loop when its q_tolerance test fires (solverGPUGaussNewton.t:2180-2200). */
+long OptB200_PlanPcgIterations(Opt_Plan* plan);
 /* With collectPerKernelTimingInfo set: number of launches of `kernel` (the reference's kernel
  * names, e.g. "PCGStep1") since the last reset and their summed cudaEvent duration in ms. */
 int  OptB200_PlanKernelTime(Opt_Plan* plan, const char* kernel, double* total_ms);

@@ -42,6 +42,7 @@ struct OptK_Plan {
     virtual void pcg_begin(int nIter) = 0;
     virtual void pcg_iter(int lIter, int reset) = 0;
     virtual void pcg_run(int lIterations) = 0;
+    virtual int pcg_run_lm(int lIterations, int reset_period, double q_tolerance, double* zeta, int* fired) = 0;
     virtual double fetch_q() = 0;
     virtual double model_cost() = 0;
     virtual void save_unknowns() = 0;
@@ -584,11 +585,13 @@ __global__ void __launch_bounds__(256) k_pcg_step2(long nvec, const unsigned cha
                                                    T* __restrict__ r, const T* __restrict__ Ap,
                                                    const T* __restrict__ pre, const T* __restrict__ b,
                                                    T* __restrict__ z, const double* aNum, const double* aDen,
-                                                   double* bNum, double* q, double* zero_slot) {
+                                                   double* bNum, double* q, double* zero_slot, const double* stop) {
     using V = typename VecIO<T>::V;
     constexpr int VW = VecIO<T>::W;
     const long i0 = blockIdx.x * (long)blockDim.x + threadIdx.x, istride = (long)gridDim.x * blockDim.x;
-    const T alpha = (T)(*aNum) / (T)(*aDen);
+    // LM: once the q_tolerance test has fired, an iteration that was queued ahead of the host's
+    // decision must leave delta untouched (pcg_run_lm); nothing else of it is read afterwards
+    const T alpha = (LM && stop && *stop != 0.0) ? T(0) : (T)(*aNum) / (T)(*aDen);
     if (i0 == 0 && zero_slot) *zero_slot = 0.0;
     double bacc = 0.0, qacc = 0.0;
     for (long i = i0; i < nvec; i += istride)
@@ -646,11 +649,11 @@ __global__ void __launch_bounds__(256) k_pcg_step3(long nvec, const unsigned cha
 template <class T>
 __global__ void __launch_bounds__(256) k_axpy_alpha(long nvec, const unsigned char* __restrict__ active4, long plane,
                                                     T* __restrict__ delta, const T* __restrict__ p,
-                                                    const double* aNum, const double* aDen) {
+                                                    const double* aNum, const double* aDen, const double* stop) {
     using V = typename VecIO<T>::V;
     constexpr int VW = VecIO<T>::W;
     const long i0 = blockIdx.x * (long)blockDim.x + threadIdx.x, istride = (long)gridDim.x * blockDim.x;
-    const T alpha = (T)(*aNum) / (T)(*aDen);
+    const T alpha = (stop && *stop != 0.0) ? T(0) : (T)(*aNum) / (T)(*aDen);
     for (long i = i0; i < nvec; i += istride)
     if (group_active<T>(active4, i, plane)) {
         V d = reinterpret_cast<const V*>(delta)[i];
@@ -699,6 +702,26 @@ __global__ void __launch_bounds__(256) k_residual_reset(long nvec, const unsigne
     block_accumulate(qacc, q);
 }
 
+// LM inner-loop exit test (solver:2180-2200) evaluated on the device.  One thread: zeta = (l+1)(Q1-Q0)/Q1 in
+// opt_float (the same roundings as the reference's host code), sets the stop flag the step kernels of a
+// speculatively queued iteration look at, rolls Q0 forward and posts the result into a pinned host mailbox
+// (payload, system-scope fence, sequence number) that the host polls without any stream synchronisation.
+struct LmMailbox { double zeta, q; long long stop; long long seq; };
+template <class T>
+__global__ void k_lm_begin(const double* q, double* qprev) { *qprev = (double)(T)(*q); }
+template <class T>
+__global__ void k_lm_zeta(int l, double q_tol, const double* q, double* qprev, double* stop, LmMailbox* box, long long seq) {
+    const double Q1 = (double)(T)(*q), Q0 = *qprev;
+    const double zeta = (double)(T)((double)(T)((double)(T)(l + 1) * (double)(T)(Q1 - Q0)) / Q1);
+    const bool was = *stop != 0.0;
+    const bool now = was || zeta < q_tol;
+    if (!was) { *qprev = Q1; if (now) *stop = 1.0; }
+    volatile LmMailbox* b = box;
+    b->zeta = zeta; b->q = Q1; b->stop = now ? 1 : 0;
+    __threadfence_system();
+    b->seq = seq;
+}
+
 // ------------------------------------------------------------------------------ the engine
 template <class F>
 struct Engine : OptK_Plan {
@@ -722,6 +745,8 @@ struct Engine : OptK_Plan {
     bool fuse = true;                                       // fused PCGStep3+PCGStep1 (single rank)
     double* scal = nullptr;
     double* h_scal = nullptr;    // pinned
+    LmMailbox* lm_box = nullptr; // pinned + device-mapped, ring of 2 (pcg_run_lm)
+    long long lm_seq = 0;
     T radius = 0, min_diag = 0, max_diag = 0;
     dim3 sgrid, sblock;
     TileGrid tg;
@@ -754,6 +779,10 @@ struct Engine : OptK_Plan {
         OPTK_CUDA(cudaMalloc(&scal, S_COUNT * sizeof(double)));
         OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
         OPTK_CUDA(cudaMallocHost(&h_scal, S_COUNT * sizeof(double)));
+        if (lm) {
+            OPTK_CUDA(cudaHostAlloc(&lm_box, 2 * sizeof(LmMailbox), cudaHostAllocMapped | cudaHostAllocPortable));
+            memset(lm_box, 0, 2 * sizeof(LmMailbox));
+        }
         if (F::ND == 1) { sblock = dim3(256, 1, 1); }
         else if (F::ND == 2) { sblock = dim3(32, 8, 1); }
         else { sblock = dim3(32, 4, 2); }
@@ -768,7 +797,7 @@ struct Engine : OptK_Plan {
         cudaStreamSynchronize(stream);
         f.free_temporaries();
         if (comm) ncclCommDestroy(comm);
-        cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFree(active4);
+        cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFreeHost(lm_box); cudaFree(active4);
         cudaFree(inc); cudaFree(inc_off); cudaFree(inc_count); cudaFree(sort_tmp); cudaFree(key_a); cudaFree(key_b); cudaFree(val_a);
         base_destroy();
     }
@@ -964,6 +993,7 @@ struct Engine : OptK_Plan {
             if (GRAPH) this->launch("PCGComputeCtC_Graph", edge_grid(), dim3(256), k_graph_ctc<F>, f, E, CtC, inv_radius);
             this->launch_tiles("PCGFinalizeDiagonal", tg.n, sblock, k_finalize_diagonal<F>, f, tg, CtC, SSq, pre, r, b, p, delta, radius, min_diag, max_diag, S(S_RZ0), S(S_Q));
             reduce(S_Q);
+            this->launch("LMBegin", dim3(1), dim3(1), k_lm_begin<T>, (const double*)S(S_Q), S(S_QPREV));   // Q0 (solver:2060)
         }
         reduce(S_RZ0);
         exchange(p);                                        // Step1 reads p over the stencil
@@ -1020,14 +1050,14 @@ struct Engine : OptK_Plan {
     applied:
         reduce(int(aDen - scal));
         if (lm && reset) {
-            this->launch_tiles("PCGStep2_1stHalf", (flat_vecs() + 255) / 256, dim3(256), k_axpy_alpha<T>, nv, act, Npad, delta.d, p.d, aNum, aDen);
+            this->launch_tiles("PCGStep2_1stHalf", (flat_vecs() + 255) / 256, dim3(256), k_axpy_alpha<T>, nv, act, Npad, delta.d, p.d, aNum, aDen, (const double*)S(S_STOP));
             exchange(delta);
             apply_A("computeAdelta", "computeAdelta_Graph", delta, Adelta, S(S_DUMMY), nullptr);
             this->launch_tiles("PCGStep2_2ndHalf", (flat_vecs() + 255) / 256, dim3(256), k_residual_reset<T, F::USE_PRE>, nv, act, Npad, delta.d, r.d, Adelta.d, pre.d, b.d, z.d, bNum, S(S_Q), nextDen);
         } else if (lm) {
-            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, true>, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
+            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, true>, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)S(S_STOP));
         } else {
-            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, false>, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen);
+            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, false>, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)nullptr);
         }
         reduce(int(bNum - scal));
         if (lm) reduce(S_Q);
@@ -1040,6 +1070,43 @@ struct Engine : OptK_Plan {
     }
     void pcg_run(int lIterations) override {
         for (int l = 0; l < lIterations; ++l) pcg_iter(l, 0);
+    }
+    // LM inner loop (solver:2072-2201) without a blocking fetchQ per iteration.  The exit test runs on the
+    // device (k_lm_zeta); the host queues iteration l+1 BEFORE it looks at the verdict of iteration l, so the
+    // GPU never waits for the host.  If iteration l fired the test, iteration l+1 is already in the stream: its
+    // step kernels see the stop flag and use alpha = 0, so delta -- the only result of the loop that is read
+    // afterwards (model cost, linear update; the next PCGInit1 rebuilds everything else) -- is exactly what the
+    // reference has after its `break`.  Returns the number of iterations the reference would have executed.
+    bool wait_box(int slot, long long expect) {
+        for (long spins = 1;; ++spins) {
+            if (__atomic_load_n(&lm_box[slot].seq, __ATOMIC_ACQUIRE) == expect) return true;
+            if ((spins & 0x3fff) == 0) {
+                cudaError_t e = cudaStreamQuery(stream);
+                if (e == cudaSuccess) {                      // stream drained: the mailbox must be visible now
+                    if (__atomic_load_n(&lm_box[slot].seq, __ATOMIC_ACQUIRE) == expect) return true;
+                    printf("Opt: LM mailbox was not written (sequence %lld)\n", expect); fflush(stdout); exit(1);
+                }
+                if (e != cudaErrorNotReady) OPTK_CUDA(e);
+            }
+        }
+    }
+    int pcg_run_lm(int lIterations, int reset_period, double q_tol, double* zeta_out, int* fired) override {
+        long long seq_of[2] = {0, 0};
+        int executed = lIterations;
+        *zeta_out = 0.0; *fired = 0;
+        for (int l = 0; l <= lIterations; ++l) {
+            if (l < lIterations) {
+                pcg_iter(l, ((l + 1) % reset_period) == 0);
+                seq_of[l & 1] = ++lm_seq;
+                this->launch("LMExitTest", dim3(1), dim3(1), k_lm_zeta<T>, l, q_tol, (const double*)S(S_Q), S(S_QPREV), S(S_STOP), lm_box + (l & 1), seq_of[l & 1]);
+            }
+            if (l > 0) {                                    // verdict of iteration l-1, while iteration l runs
+                const int k = (l - 1) & 1;
+                wait_box(k, seq_of[k]);
+                if (lm_box[k].stop) { executed = l; *zeta_out = lm_box[k].zeta; *fired = 1; break; }
+            }
+        }
+        return executed;
     }
 
     static constexpr bool FLAT_X = F::U == 1 && F::VEC_UB == 0 && !GRAPH;

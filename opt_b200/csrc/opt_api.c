@@ -42,6 +42,8 @@ struct Opt_Plan {
     /* LM state the reference keeps as injected problem parameters (o.t:1575-1580) */
     double trust_region_radius, radius_decrease_factor, min_lm_diagonal, max_lm_diagonal;
     int finished_reported;
+    long pcg_iterations;   /* PCG iterations executed since creation (LM leaves the inner loop early) */
+    int lm_host_loop;      /* OPTB200_LM_HOSTLOOP=1: blocking fetchQ per iteration, as the reference does */
 };
 
 /* opt_float rounding: the reference keeps these host scalars in opt_float */
@@ -121,6 +123,7 @@ Opt_Plan* Opt_ProblemPlan(Opt_State* state, Opt_Problem* problem, unsigned int* 
     plan->is_double = state->ip.doublePrecision != 0;
     plan->verbosity = state->ip.verbosityLevel;
     plan->timing = state->ip.collectPerKernelTimingInfo != 0;
+    plan->lm_host_loop = getenv("OPTB200_LM_HOSTLOOP") != NULL;
     default_parameters(&plan->sp);
     return plan;
 }
@@ -184,24 +187,35 @@ int Opt_ProblemStep(Opt_State* state, Opt_Plan* plan, void** problemparams) {
         return 0;
     }
     const double q_tolerance = of(plan, sp->q_tolerance);
-    double Q0 = 0.0, Q1 = 0.0;
     if (plan->is_lm) optk_set_lm(k, plan->trust_region_radius, plan->min_lm_diagonal, plan->max_lm_diagonal);
     optk_pcg_begin(k, sp->nIter);
-    if (plan->is_lm) {
-        Q0 = optk_fetch_q(k);
-        for (int lIter = 0; lIter < sp->lIterations; ++lIter) {
+    if (plan->is_lm && plan->lm_host_loop) {
+        double Q0 = optk_fetch_q(k), Q1 = 0.0;
+        int lIter = 0;
+        for (; lIter < sp->lIterations; ++lIter) {
             int reset = ((lIter + 1) % sp->residual_reset_period) == 0;
             optk_pcg_iter(k, lIter, reset);
             Q1 = optk_fetch_q(k);
             double zeta = of(plan, of(plan, of(plan, (double)(lIter + 1)) * of(plan, Q1 - Q0)) / Q1);
             if (zeta < q_tolerance) {
                 logSolver(plan, "zeta=%.18g < q_tol(%f), breaking at iteration: %d\n", zeta, q_tolerance, lIter + 1);
+                ++lIter;
                 break;
             }
             Q0 = Q1;
         }
+        plan->pcg_iterations += lIter;
+    } else if (plan->is_lm) {
+        /* same loop, exit test on the device, no blocking fetchQ (engine.cuh: pcg_run_lm) */
+        double zeta = 0.0;
+        int fired = 0;
+        int executed = optk_pcg_run_lm(k, sp->lIterations, sp->residual_reset_period, q_tolerance, &zeta, &fired);
+        if (fired)
+            logSolver(plan, "zeta=%.18g < q_tol(%f), breaking at iteration: %d\n", zeta, q_tolerance, executed);
+        plan->pcg_iterations += executed;
     } else {
         optk_pcg_run(k, sp->lIterations); /* no host round trip inside the GN inner loop */
+        plan->pcg_iterations += sp->lIterations;
     }
 
     double model_cost_change = 0.0;
@@ -274,6 +288,7 @@ int OptB200_PlanSetSlab(Opt_Plan* plan, int rank, int nranks, int halo, const vo
     return optk_set_slab(plan->k, rank, nranks, halo, nccl_unique_id);
 }
 long OptB200_PlanLaunchCount(Opt_Plan* plan) { return optk_launch_count(plan->k); }
+long OptB200_PlanPcgIterations(Opt_Plan* plan) { return plan->pcg_iterations; }
 int OptB200_PlanKernelTime(Opt_Plan* plan, const char* kernel, double* total_ms) {
     return optk_kernel_time(plan->k, kernel, total_ms);
 }

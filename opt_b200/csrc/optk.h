@@ -32,6 +32,10 @@ double optk_cost(OptK_Plan*);                 /* computeCost + computeCost_Graph
 void   optk_pcg_begin(OptK_Plan*, int nIter); /* PCGInit1[_Graph,_Finish]; LM: SaveSSq, ComputeCtC[_Graph], FinalizeDiagonal */
 void   optk_pcg_iter(OptK_Plan*, int lIter, int residual_reset);  /* PCGStep1[_Graph], Step2 (or 1stHalf/Adelta/2ndHalf), Step3 */
 void   optk_pcg_run(OptK_Plan*, int lIterations);                  /* GN: the whole inner loop, no host sync */
+/* LM: the whole inner loop with the q_tolerance exit test (solver:2180-2200) evaluated on the device; the host
+ * polls a pinned mailbox one iteration behind the GPU.  Returns the iterations executed (as the reference counts
+ * them); *fired = 1 and *zeta = the value below q_tolerance when the test ended the loop. */
+int    optk_pcg_run_lm(OptK_Plan*, int lIterations, int residual_reset_period, double q_tolerance, double* zeta, int* fired);
 double optk_fetch_q(OptK_Plan*);              /* fetchQ (solver:1480-1501) */
 double optk_model_cost(OptK_Plan*);           /* computeModelCost[_Graph] + D2H (solver:1445-1476) */
 void   optk_save_unknowns(OptK_Plan*);        /* savePreviousUnknowns (solver:882-887) */

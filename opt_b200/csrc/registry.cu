@@ -62,6 +62,7 @@ double optk_cost(OptK_Plan* p) { return p->cost(); }
 void optk_pcg_begin(OptK_Plan* p, int nIter) { p->pcg_begin(nIter); }
 void optk_pcg_iter(OptK_Plan* p, int l, int reset) { p->pcg_iter(l, reset); }
 void optk_pcg_run(OptK_Plan* p, int n) { p->pcg_run(n); }
+int optk_pcg_run_lm(OptK_Plan* p, int n, int reset, double qtol, double* zeta, int* fired) { return p->pcg_run_lm(n, reset, qtol, zeta, fired); }
 double optk_fetch_q(OptK_Plan* p) { return p->fetch_q(); }
 double optk_model_cost(OptK_Plan* p) { return p->model_cost(); }
 void optk_save_unknowns(OptK_Plan* p) { p->save_unknowns(); }

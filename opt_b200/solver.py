@@ -42,6 +42,8 @@ def load_library():
         _lib.OptB200_FreeState.argtypes = [P]
         _lib.OptB200_PlanLaunchCount.restype = C.c_long
         _lib.OptB200_PlanLaunchCount.argtypes = [P]
+        _lib.OptB200_PlanPcgIterations.restype = C.c_long
+        _lib.OptB200_PlanPcgIterations.argtypes = [P]
         _lib.OptB200_PlanKernelTime.restype = C.c_int
         _lib.OptB200_PlanKernelTime.argtypes = [P, C.c_char_p, C.POINTER(C.c_double)]
         _lib.OptB200_PlanResetTiming.argtypes = [P]
@@ -156,6 +158,10 @@ class OptSolver:
     # --- OptB200.h extensions --------------------------------------------------------------------
     def launch_count(self):
         return self.lib.OptB200_PlanLaunchCount(self.plan)
+
+    def pcg_iterations(self):
+        """PCG iterations executed since the plan was created (LM may leave the inner loop early)."""
+        return self.lib.OptB200_PlanPcgIterations(self.plan)
 
     def kernel_time(self, name):
         """(launch count, total ms) of the kernels timed under `name` (needs timing=True)."""

@@ -182,6 +182,7 @@ struct PlanBase {
     int verbosity = 0;
     int threads = 1;
     std::vector<double> cost_history;   // cost after init and after every step (test hook)
+    long pcg_iterations = 0;            // PCG iterations executed since the plan was made (test hook)
     virtual ~PlanBase() {}
     virtual void init(void** params) = 0;
     virtual int step(void** params) = 0;
@@ -510,6 +511,7 @@ struct Solver : PlanBase {
             Q0 = (T)qacc;
         }
         for (int lIter = 0; lIter < sp.lIterations; ++lIter) {
+            ++pcg_iterations;
             aDen = apply_A(p.data(), Ap.data());                 // PCGStep1 (+_Graph)
             // graph scatter accumulates into Ap; the centred pass *overwrites* its own entries first,
             // and the scatter target must start from that (solver:1216-1231) -- see apply_A ordering.

@@ -70,6 +70,7 @@ void OptOracle_ProblemSolve(OptOracle_State* s, OptOracle_Plan* pl, void** pp) {
 double OptOracle_ProblemCurrentCost(OptOracle_State*, OptOracle_Plan* pl) { return pl->impl->cost(); }
 
 long OptOracle_UnknownCount(OptOracle_Plan* pl) { return pl->impl->unknown_count(); }
+long OptOracle_PcgIterations(OptOracle_Plan* pl) { return pl->impl->pcg_iterations; }
 int OptOracle_CostHistory(OptOracle_Plan* pl, double* out, int cap) {
     int n = (int)pl->impl->cost_history.size();
     for (int i = 0; i < n && i < cap; ++i) out[i] = pl->impl->cost_history[i];

@@ -28,6 +28,7 @@ double             OptOracle_ProblemCurrentCost(OptOracle_State*, OptOracle_Plan
 
 /* test hooks (no counterpart in Opt.h) */
 long   OptOracle_UnknownCount(OptOracle_Plan*);                       /* N * U */
+long   OptOracle_PcgIterations(OptOracle_Plan*);                     /* PCG iterations executed so far (LM exits early) */
 int    OptOracle_CostHistory(OptOracle_Plan*, double* out, int cap);  /* cost after Init and after each Step */
 void   OptOracle_ApplyJTJ(OptOracle_Plan*, void** problemparams, const void* p, void* Ap);   /* AoS [site][U] */
 void   OptOracle_EvalJTF(OptOracle_Plan*, void** problemparams, void* minusJTF, void* preconditioner);

@@ -28,6 +28,8 @@ def lib():
         _LIB = C.CDLL(path)
         _LIB.OptOracle_UnknownCount.restype = C.c_long
         _LIB.OptOracle_UnknownCount.argtypes = [C.c_void_p]
+        _LIB.OptOracle_PcgIterations.restype = C.c_long
+        _LIB.OptOracle_PcgIterations.argtypes = [C.c_void_p]
         _LIB.OptOracle_CostHistory.restype = C.c_int
         _LIB.OptOracle_CostHistory.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int]
         _LIB.OptOracle_ApplyJTJ.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p]
@@ -100,6 +102,9 @@ class OracleSolver:
         buf = (C.c_double * 4096)()
         n = lib().OptOracle_CostHistory(self.plan, buf, 4096)
         return [buf[i] for i in range(min(n, 4096))]
+
+    def pcg_iterations(self):
+        return lib().OptOracle_PcgIterations(self.plan)
 
     def unknown_count(self):
         return lib().OptOracle_UnknownCount(self.plan)

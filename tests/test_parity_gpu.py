@@ -210,3 +210,36 @@ def test_solve_equals_init_step_loop(built):
     ca = a.solve_blocking(pr.solver, S.upload(pr))
     gc, _, _, _ = run_gpu(pr)
     assert abs(ca - gc[-1]) <= 1e-6 * abs(ca)
+
+
+LM_EXIT_CASES = {   # LM solves whose q_tolerance test fires (oracle: 112 of 120, 119 of 160, 98 of 120 iterations)
+    "sfs": (examples.sfs_synthetic, (45, 37), dict(n_iter=4, l_iter=30)),
+    "volumetric": (examples.volumetric_synthetic, (11, 9, 7), dict(n_iter=4, l_iter=40)),
+    "poisson": (examples.poisson_synthetic, (67, 45), dict(n_iter=3, l_iter=40)),
+}
+
+
+@pytest.mark.parametrize("double", [False, True])
+@pytest.mark.parametrize("case", sorted(LM_EXIT_CASES))
+def test_lm_device_exit_test(built, case, double, monkeypatch):
+    """The LM inner loop with the exit test on the device (one iteration queued ahead of the verdict, its step
+    neutralised by the stop flag) against the reference-style loop with a blocking fetchQ per iteration and
+    against the oracle: same number of PCG iterations, same costs, same unknowns."""
+    b, args, kw = LM_EXIT_CASES[case]
+    pr = b(*args, **kw)
+    pr.kind = "LMGPU"
+    if double:
+        pr = pr.as_double()
+    gc, gx, sol, _ = run_gpu(pr)
+    rc, rx, o = run_oracle(pr)
+    nominal = kw["n_iter"] * kw["l_iter"]
+    assert o.pcg_iterations() < nominal                  # the test really fires in this case
+    if double:
+        assert sol.pcg_iterations() == o.pcg_iterations()
+    assert_costs_close(gc, rc, double)
+    assert_unknowns_close(gx, rx, double)
+    monkeypatch.setenv("OPTB200_LM_HOSTLOOP", "1")       # read when the plan is made
+    hc, hx, hsol, _ = run_gpu(pr)
+    assert hsol.pcg_iterations() == sol.pcg_iterations()
+    assert_costs_close(gc, hc, double, tol=1e-6 if not double else 1e-12)
+    assert_unknowns_close(gx, hx, double, tol=1e-5 if not double else 1e-11)
