@@ -1,0 +1,112 @@
+"""GPU: the driver pre/post-processing kernels (include/OptB200Drivers.h, through the C ABI) against the numpy
+restatement of the reference's CPU code (oracle/driver_ref.py): bit-exact for the integer/selection work and the
+fixed-order float arithmetic, 1e-6 for the Gaussian (its weights come from two different expf)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import driver_ref as R  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+f32 = np.float32
+
+
+def cuda(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+@pytest.mark.parametrize("shape", [(37, 53), (1, 300), (130, 33), (64, 256), (5, 5)])
+@pytest.mark.parametrize("sigma", [0.7, 1.0, 5.0])
+def test_gaussian(built, shape, sigma):
+    from opt_b200 import drivers as D
+    im = (np.random.default_rng(3).random(shape, dtype=f32) * 255).astype(f32)
+    got = D.filter_gaussian(cuda(im), sigma).cpu().numpy()
+    ref = R.filter_gaussian(im, sigma)
+    assert np.abs(got - ref).max() <= 1e-6 * 255
+
+
+@pytest.mark.parametrize("shape", [(37, 53), (3, 3), (2, 9), (130, 33)])
+def test_prewitt_bit_exact(built, shape):
+    from opt_b200 import drivers as D
+    im = (np.random.default_rng(4).random(shape, dtype=f32) * 255).astype(f32)
+    for horizontal in (True, False):
+        got = D.prewitt(cuda(im), horizontal).cpu().numpy()
+        assert np.array_equal(got, R.prewitt(im, horizontal))
+
+
+def warp_case(H, W, seed, amp):
+    rng = np.random.default_rng(seed)
+    ys, xs = np.mgrid[0:H, 0:W]
+    warp = (np.stack([xs, ys], axis=-1) + amp * rng.standard_normal((H, W, 2))).astype(f32)
+    color = (rng.random((H, W, 3), dtype=f32) * 255).astype(f32)
+    mask = (rng.random((H, W)) < 0.1).astype(f32)
+    return warp, color, mask
+
+
+@pytest.mark.parametrize("H,W,amp", [(9, 11, 0.0), (23, 31, 0.3), (23, 31, 1.5), (16, 16, 6.0)])
+def test_rasteriser_bit_exact(built, H, W, amp):
+    """Overlapping and folded triangles included (amp 1.5, 6): the last triangle in the reference's drawing order
+    must win every contested pixel."""
+    from opt_b200 import drivers as D
+    warp, color, mask = warp_case(H, W, 5, amp)
+    got = D.rasterize_warp(cuda(warp), cuda(color), cuda(mask)).cpu().numpy()
+    assert np.array_equal(got, R.rasterize_warp(warp, color, mask))
+
+
+def test_skinning_bit_exact(built):
+    from opt_b200 import drivers as D
+    dims = (5, 20, 5)
+    rng = np.random.default_rng(6)
+    grid = rng.standard_normal(((dims[0] + 1) * (dims[1] + 1) * (dims[2] + 1), 3)).astype(f32)
+    n = 4001
+    voxel = np.stack([rng.integers(0, d, n) for d in dims], axis=1).astype(np.int32)
+    rel = rng.random((n, 3), dtype=f32)
+    got = D.skin_trilinear(cuda(grid), dims, cuda(voxel), cuda(rel)).cpu().numpy()
+    assert np.array_equal(got, R.skin_trilinear(grid, dims, voxel, rel))
+
+
+def test_flow_lines_bit_exact(built):
+    from opt_b200 import drivers as D
+    H, W = 41, 58
+    rng = np.random.default_rng(7)
+    flow = (rng.standard_normal((H, W, 2)) * 6).astype(f32)
+    n = D.flow_sample_count(W, H)
+    colors = rng.integers(1, 255, (n, 4)).astype(np.uint8)
+    base = rng.integers(0, 255, (H, W, 4)).astype(np.uint8)
+    got = D.render_flow_lines(cuda(base.copy()), cuda(flow), cuda(colors)).cpu().numpy()
+    assert np.array_equal(got, R.render_flow_lines(base, flow, colors))
+
+
+def test_optical_flow_driver_matches_oracle(built):
+    """The hierarchical driver (device pre-processing + solves) against the same sequence run through the numpy
+    pre-processing and the CPU oracle solver."""
+    from opt_b200 import drivers as D
+    from opt_b200 import examples as E
+    from gpu_util import run_oracle
+    H, W = 40, 56
+    ys, xs = np.mgrid[0:H, 0:W].astype(f32)
+    src = (0.5 + 0.5 * np.sin(xs / 5.0) * np.cos(ys / 7.0)).astype(f32)
+    tgt = (0.5 + 0.5 * np.sin((xs - 0.8) / 5.0) * np.cos((ys + 0.5) / 7.0)).astype(f32)
+    drv = D.OpticalFlowDriver(src, tgt, num_iter=2, n_iter=2, l_iter=10)
+    drv.solve_all()
+    ref_costs = []
+    w = f32(10.0)
+    step = f32((f32(50.0) - w) / f32(2 * 2))
+    for sigma in (5.0, 1.0):
+        S_, T_ = R.filter_gaussian(src, sigma), R.filter_gaussian(tgt, sigma)
+        X = np.zeros((H, W, 2), dtype=f32)
+        for _ in range(2):
+            w = f32(w + step)
+            pr = E.Problem("optical_flow.t", [W, H], [np.sqrt(w), np.sqrt(f32(0.1)), X, S_, T_, R.prewitt(T_, True), R.prewitt(T_, False)],
+                           [2], {"nIterations": 2, "lIterations": 10})
+            rc, rx, _ = run_oracle(pr)
+            X = rx[2]
+            ref_costs.append(rc[-1])
+    assert len(drv.costs) == 4
+    for a, b in zip(drv.costs, ref_costs):
+        assert abs(a - b) <= 1e-4 * abs(b), (drv.costs, ref_costs)
