@@ -50,7 +50,7 @@ def _compile(src, verbose):
 
 def build(verbose=False, oracle=True):
     os.makedirs(OBJ, exist_ok=True)
-    srcs = [os.path.join(CSRC, "opt_api.c"), os.path.join(CSRC, "registry.cu"), os.path.join(CSRC, "driver_ops.cu")]
+    srcs = [os.path.join(CSRC, "opt_api.c"), os.path.join(CSRC, "registry.cu"), os.path.join(CSRC, "driver_ops.cu"), os.path.join(CSRC, "formats.c")]
     ex = os.path.join(CSRC, "examples")
     srcs += sorted(os.path.join(ex, f) for f in os.listdir(ex) if f.endswith(".cu"))
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as pool:

@@ -16,37 +16,45 @@ __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b);
 __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
 
 constexpr int GAUSS_MAX_R = 64;
-__constant__ float c_gauss[GAUSS_MAX_R + 1];
+struct GaussKernel { float w[GAUSS_MAX_R + 1]; };            // passed by value: no constant-memory upload, no host sync
 
 // ---- separable Gaussian (ImageHelper.h:68-114) ---------------------------------------------------------------
-// Row pass: a block owns 256 consecutive pixels of one row and stages them plus R pixels either side in shared
-// memory; every pixel of the image is read from DRAM once.
-__global__ void __launch_bounds__(256) k_gauss_rows(const float* __restrict__ in, float* __restrict__ out, int W, int H, int R) {
+// Row pass: a block owns 1024 consecutive pixels of one row (4 per thread, 128-bit stores) and stages them plus R
+// pixels either side in shared memory; every pixel of the image is read from DRAM once.
+constexpr int ROW_PX = 1024;
+__global__ void __launch_bounds__(256) k_gauss_rows(const float* __restrict__ in, float* __restrict__ out, int W, int H, int R, const GaussKernel gk) {
     extern __shared__ float tile[];
-    const int y = blockIdx.y, x0 = blockIdx.x * 256;
+    const int y = blockIdx.y, x0 = blockIdx.x * ROW_PX;
     const float* row = in + (size_t)y * W;
-    for (int t = threadIdx.x; t < 256 + 2 * R; t += 256) {
+    for (int t = threadIdx.x; t < ROW_PX + 2 * R; t += 256) {
         const int x = x0 - R + t;
         tile[t] = (x >= 0 && x < W) ? row[x] : 0.f;
     }
     __syncthreads();
-    const int x = x0 + threadIdx.x;
-    if (x >= W) return;
-    float v = 0.f, w = 0.f;
-    for (int k = -R; k <= R; ++k) {
-        const int xk = x + k;
-        if (xk >= 0 && xk < W) {
-            const float g = c_gauss[k < 0 ? -k : k];
-            v = add(v, mul(g, tile[threadIdx.x + R + k]));
-            w = add(w, g);
+    float res[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int lx = threadIdx.x * 4 + q, x = x0 + lx;
+        float v = 0.f, w = 0.f;
+        for (int k = -R; k <= R; ++k) {
+            const int xk = x + k;
+            if (xk >= 0 && xk < W) {
+                const float g = gk.w[k < 0 ? -k : k];
+                v = add(v, mul(g, tile[lx + R + k]));
+                w = add(w, g);
+            }
         }
+        if (w > 0.f) v = __fdiv_rn(v, w);
+        res[q] = v;
     }
-    if (w > 0.f) v = __fdiv_rn(v, w);
-    out[(size_t)y * W + x] = v;
+    const int x = x0 + threadIdx.x * 4;
+    float* o = out + (size_t)y * W + x;
+    if (x + 3 < W && (((size_t)y * W + x) & 3) == 0) *reinterpret_cast<float4*>(o) = make_float4(res[0], res[1], res[2], res[3]);
+    else for (int q = 0; q < 4; ++q) if (x + q < W) o[q] = res[q];
 }
 // Column pass: a block of 32 x 8 threads owns a 32 x 64 tile (8 output rows per thread) and stages 64 + 2R rows.
 constexpr int COL_ROWS = 64;
-__global__ void __launch_bounds__(256) k_gauss_cols(const float* __restrict__ in, float* __restrict__ out, int W, int H, int R) {
+__global__ void __launch_bounds__(256) k_gauss_cols(const float* __restrict__ in, float* __restrict__ out, int W, int H, int R, const GaussKernel gk) {
     extern __shared__ float tile[];                          // [COL_ROWS + 2R][32]
     const int x = blockIdx.x * 32 + threadIdx.x, y0 = blockIdx.y * COL_ROWS;
     for (int t = threadIdx.y; t < COL_ROWS + 2 * R; t += 8) {
@@ -62,7 +70,7 @@ __global__ void __launch_bounds__(256) k_gauss_cols(const float* __restrict__ in
         for (int k = -R; k <= R; ++k) {
             const int yk = y + k;
             if (yk >= 0 && yk < H) {
-                const float g = c_gauss[k < 0 ? -k : k];
+                const float g = gk.w[k < 0 ? -k : k];
                 v = add(v, mul(g, tile[(j + R + k) * 32 + threadIdx.x]));
                 w = add(w, g);
             }
@@ -226,14 +234,10 @@ int OptB200_FilterGaussian(float* image, unsigned W, unsigned H, float sigma, fl
     cudaStream_t st = (cudaStream_t)stream_;
     const int R = (int)std::ceil(2.0f * sigma);                // math::ceil(2.0f*sigma)
     if (R < 0 || R > GAUSS_MAX_R || W == 0 || H == 0) return (int)cudaErrorInvalidValue;
-    std::vector<float> k(R + 1);
-    for (int i = 0; i <= R; ++i) { const float x = (float)i; k[i] = expf(-((x * x) / (2.0f * sigma * sigma))); }
-    cudaError_t e = cudaMemcpyToSymbolAsync(c_gauss, k.data(), (R + 1) * sizeof(float), 0, cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaStreamSynchronize(st);                              // k is a stack-lifetime host buffer
-    if (e != cudaSuccess) return (int)e;
-    k_gauss_rows<<<dim3((W + 255) / 256, H), 256, (256 + 2 * R) * sizeof(float), st>>>(image, scratch, (int)W, (int)H, R);
-    k_gauss_cols<<<dim3((W + 31) / 32, (H + COL_ROWS - 1) / COL_ROWS), dim3(32, 8), (COL_ROWS + 2 * R) * 32 * sizeof(float), st>>>(scratch, image, (int)W, (int)H, R);
+    GaussKernel gk;
+    for (int i = 0; i <= GAUSS_MAX_R; ++i) { const float x = (float)i; gk.w[i] = i <= R ? expf(-((x * x) / (2.0f * sigma * sigma))) : 0.f; }
+    k_gauss_rows<<<dim3((W + ROW_PX - 1) / ROW_PX, H), 256, (ROW_PX + 2 * R) * sizeof(float), st>>>(image, scratch, (int)W, (int)H, R, gk);
+    k_gauss_cols<<<dim3((W + 31) / 32, (H + COL_ROWS - 1) / COL_ROWS), dim3(32, 8), (COL_ROWS + 2 * R) * 32 * sizeof(float), st>>>(scratch, image, (int)W, (int)H, R, gk);
     return done();
 }
 

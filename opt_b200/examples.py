@@ -66,11 +66,15 @@ def image_warping(mask, constraints, alpha=1.0, n_iter=1, l_iter=1):
                    {"nIterations": n_iter, "lIterations": l_iter})
 
 
-def image_warping_golden(npz):
+def image_warping_golden(npz, outer_iterations=1, n_iter=1, l_iter=1):
+    """(1,1,1): the reference's recorded final cost (test_final_cost.py:58).  (19,8,400): the FIRST outer iteration
+    of the long run (test_example_output.py:64,112,133), whose constraints are moved 1/19 of the way
+    (CombinedSolver.h:155: alpha = (i+1)/numIter)."""
     shape = tuple(npz["shape"])
     is_zero = np.unpackbits(npz["mask_is_zero"])[: shape[0] * shape[1]].reshape(shape).astype(bool)
     mask = np.where(is_zero, 0, 255).astype(np.uint8)
-    return image_warping(mask, npz["constraints"].tolist())
+    alpha = np.float32(1.0) / np.float32(outer_iterations)
+    return image_warping(mask, npz["constraints"].tolist(), alpha=alpha, n_iter=n_iter, l_iter=l_iter)
 
 
 def volumetric(bbox_min, bbox_max, grid=(5, 20, 5), n_iter=1, l_iter=1):
@@ -104,8 +108,21 @@ def volumetric(bbox_min, bbox_max, grid=(5, 20, 5), n_iter=1, l_iter=1):
                    {"nIterations": n_iter, "lIterations": l_iter})
 
 
-def volumetric_golden(npz):
-    return volumetric(npz["bbox_min"], npz["bbox_max"], tuple(int(g) for g in npz["grid"]))
+def volumetric_golden(npz, n_iter=1, l_iter=1):
+    """(1,1): test_final_cost.py:66; (20,60): the long run of test_example_output.py:73,119,140."""
+    return volumetric(npz["bbox_min"], npz["bbox_max"], tuple(int(g) for g in npz["grid"]), n_iter=n_iter, l_iter=l_iter)
+
+
+def sfs_golden(npz, n_iter=60, l_iter=10, kind="gaussNewtonGPU"):
+    """shape_from_shading on the reference's default data set (640 x 480; SFSSolverInput.h:27-62 gives the parameter
+    order, main.cpp:8 the files): the long run of test_example_output.py:72,118,139 (recorded cost 58.968529, 1e-2)."""
+    H, W = (int(v) for v in npz["shape"])
+    D = npz["D"].astype(np.float32)
+    X = D.copy() if bool(npz["X_is_D"]) else npz["X"].astype(np.float32)
+    M = np.unpackbits(npz["masks"])[: 2 * H * W].reshape(2 * H, W).astype(np.uint8)
+    scal = [np.float32(v) for v in npz["scalars"]]
+    return Problem("shape_from_shading.t", [W, H], scal + [X, D, npz["Im"].astype(np.float32), M[:H].copy(), M[H:].copy()], [16],
+                   {"nIterations": n_iter, "lIterations": l_iter}, kind=kind)
 
 
 # ---------------------------------------------------------------------------------------------

@@ -243,3 +243,16 @@ def test_lm_device_exit_test(built, case, double, monkeypatch):
     assert hsol.pcg_iterations() == sol.pcg_iterations()
     assert_costs_close(gc, hc, double, tol=1e-6 if not double else 1e-12)
     assert_unknowns_close(gx, hx, double, tol=1e-5 if not double else 1e-11)
+
+
+@pytest.mark.parametrize("name", ["shape_from_shading", "volumetric_mesh_deformation", "image_warping"])
+def test_reference_long_run_cost(built, golden_dir, name):
+    """examples/test_example_output.py: the recorded long-run costs with the reference's own tolerances (58.968529
+    +- 1e-2 after GN 60x10 on the 640x480 shape-from-shading data; 19.287743 +- 1e-6 after GN 20x60; 0.078505 +- 1e-4
+    after the first of 19 outer iterations of GN 8x400)."""
+    from test_oracle_golden import LONG_RUNS
+    fname, builder, kw, golden, tol = LONG_RUNS[name]
+    pr = builder(np.load(os.path.join(golden_dir, fname)), **kw)
+    gc, _, sol, _ = run_gpu(pr)
+    assert abs(gc[-1] - golden) / golden < tol, (gc[-1], golden)
+    assert sol.pcg_iterations() == kw["n_iter"] * kw["l_iter"]

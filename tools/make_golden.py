@@ -159,8 +159,34 @@ def poisson():
                         unknown=np.packbits(unknown), shape=np.array([H, W]), golden_cost=np.float64(1530364.25))
 
 
+def sfs():
+    # examples/shape_from_shading/src/main.cpp:8,41 + SFSSolverInput.h:27-90: the four .imagedump files and the raw
+    # parameter struct of the default data set (640 x 480), read with the library's own loaders
+    # (include/OptB200Formats.h; SimpleBuffer's infinity clamp applied).  The recorded cost is the long-run value of
+    # examples/test_example_output.py:118,139 (GN, nIterations 60, lIterations 10, relative tolerance 1e-2).
+    sys.path.insert(0, os.path.dirname(OUT.rstrip("/").rsplit("/tests", 1)[0] + "/"))
+    from opt_b200 import formats as F
+    pre = f"{REF}/data/shape_from_shading/default"
+    X, D, Im = (F.read_imagedump(f"{pre}_{n}.imagedump") for n in ("initialUnknown", "targetDepth", "targetIntensity"))
+    M = F.read_imagedump(f"{pre}_maskEdgeMap.imagedump")
+    H, W = X.shape
+    assert M.shape == (2 * H, W) and set(np.unique(M)) <= {0, 1}
+    p = F.read_sfs_parameters(f"{pre}.SFSSolverParameters")
+    scal = np.array([p.weightFitting, p.weightRegularizer, p.weightShading, p.fx, p.fy, p.ux, p.uy] + list(p.lightingCoefficients), dtype=np.float32)
+    same = np.array_equal(X, D)
+    np.savez_compressed(f"{OUT}/sfs_default.npz", X=(np.zeros(0, np.float32) if same else X), X_is_D=np.array(same), D=D, Im=Im,
+                        masks=np.packbits(M), shape=np.array([H, W]), scalars=scal,
+                        golden_cost_60x10=np.float64(58.968529), golden_rtol=np.float64(1e-2))
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1:
+        for name in sys.argv[1:]:
+            globals()[name]()
+        print("wrote", sorted(os.listdir(OUT)))
+        sys.exit(0)
+    sfs()
     image_warping()
     volumetric()
     intrinsic()
