@@ -573,7 +573,7 @@ __global__ void k_active4(F f, long ngroups, unsigned char* active4) {
         const long s = g * 4 + j;
         if (s < N) {
             const int x = (int)(s % f.W), y = (int)((s / f.W) % f.H), z = (int)(s / ((long)f.W * f.H));
-            if (!f.exclude(x, y, z, s)) a = 1;
+            if (!f.exclude(x, y, z, s)) a |= (unsigned char)(1u << j);     // one bit per site of the group
         }
     }
     active4[g] = a;
@@ -967,11 +967,22 @@ struct Engine : OptK_Plan {
     }
     double fetch_q() override { return (double)(T)read_scalar(S_Q); }
 
+    // active4 (one bit per site of a group of 4) and, for functors whose J^T J kernel walks a work list, that list
+    void active_groups() {
+        if (!F::HAS_EXCLUDE) return;
+        this->launch("activeGroups", dim3((unsigned)((Npad / 4 + 255) / 256)), dim3(256), k_active4<F>, f, Npad / 4, active4);
+        if constexpr (F::HAS_ACTIVE_ITEMS) {
+            if (f.fast_ok()) {
+                this->pre_launch("activeItems");
+                f.build_active_items(stream, active4);
+                this->post_launch();
+            }
+        }
+    }
     void pcg_begin(int nIter) override {
         OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
         if (nIter == 0 && use_gather()) build_incidence();
-        if (F::HAS_EXCLUDE)                                 // Exclude() may read inputs the caller changed
-            this->launch("activeGroups", dim3((unsigned)((Npad / 4 + 255) / 256)), dim3(256), k_active4<F>, f, Npad / 4, active4);
+        active_groups();                                    // Exclude() may read inputs the caller changed
         bool fast_init = false;
         if constexpr (F::HAS_FAST_INIT) {
             if (f.fast_ok()) {
@@ -1163,8 +1174,7 @@ struct Engine : OptK_Plan {
         OPTK_CUDA(cudaMemsetAsync(Ap.d, 0, tmp.size() * sizeof(T), stream));
         bool saved = lm; lm = false;
         if (use_gather()) build_incidence();
-        if (F::HAS_EXCLUDE)
-            this->launch("activeGroups", dim3((unsigned)((Npad / 4 + 255) / 256)), dim3(256), k_active4<F>, f, Npad / 4, active4);
+        active_groups();
         apply_A("PCGStep1", "PCGStep1_Graph", p, Ap, S(S_DUMMY), nullptr);
         lm = saved;
         debug_read("Ap", host_out);
@@ -1178,6 +1188,7 @@ struct FunctorDefaults {
     static constexpr bool HAS_CUSTOM_PRECOMPUTE = false; // precompute is a functor-launched kernel (own table layout)
     static constexpr bool HAS_EXCLUDE = false;           // functors with an Exclude() override this
     static constexpr bool HAS_FAST_APPLY = false;        // functors with a specialised J^T J kernel override this
+    static constexpr bool HAS_ACTIVE_ITEMS = false;      // ... whose kernel walks a compacted list of work items (poisson)
     static constexpr bool HAS_FAST_INIT = false;         // ... and with a specialised PCGInit1 (fast_init_kernel())
     static constexpr bool HAS_FAST_COST = false;         // ... and computeCost (fast_cost_kernel())
     static constexpr bool HAS_FAST_PRECOMPUTE = false;   // ... and precompute (fast_precompute(stream, nsm))

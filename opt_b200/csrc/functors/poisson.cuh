@@ -16,17 +16,48 @@ struct PoissonFunctor : FunctorDefaults<T> {
     static constexpr bool USE_PRE = false;
     int W, H, D;
     T* X; const T* Tm; const T* M;
-    void plan(const unsigned* d) { W = d[0]; H = d[1]; D = 1; }
+    void plan(const unsigned* d) {
+        W = d[0]; H = d[1]; D = 1;
+        tiled = getenv("OPTB200_POISSON_TILED") != nullptr;
+        // (channel, strip, band) items are dealt round-robin to the resident warps (8 per CTA, 3 CTAs per SM in fp32,
+        // 2 in fp64); items without unknowns are dropped from the list (build_active_items), so the others cost about
+        // the same and ~8 of them per warp keep the quantisation loss small.  A band re-reads 2 neighbour rows.
+        int dev = 0, nsm = 148;
+        cudaGetDevice(&dev); cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+        const long slots = (long)nsm * 8 * (sizeof(T) == 4 ? 3 : 2) * 8;
+        bandR = (int)std::min<long>(256, std::max<long>(16, ((long)H * 4 * strips() + slots - 1) / slots));
+    }
     void bind(void** pp) { X = (T*)pp[0]; Tm = (const T*)pp[1]; M = (const T*)pp[2]; }
     __device__ bool exclude(int, int, int, long s) const { return M[s] != T(0); }
     __device__ T* xptr(long s, int u) const { return X + s * 4 + u; }
     int unknown_images(void** ptrs, int* ch) const { ptrs[0] = X; ch[0] = 4; return 1; }
-    // vectorised / fused J^T J apply (k_poisson_apply below); needs rows that are a multiple of 4 pixels
+    // vectorised / fused J^T J apply; needs rows that are a multiple of 4 pixels.  Two kernels: k_poisson_march (a
+    // warp marches one channel plane down a band of rows, rows prefetched by cp.async; the default) and the older
+    // tile kernel k_poisson_apply (OPTB200_POISSON_TILED=1 when the plan is made; tests compare the two).
     static constexpr bool HAS_FAST_APPLY = true;
+    static constexpr bool HAS_ACTIVE_ITEMS = true;
+    bool tiled = false;
+    int bandR = 16;
+    unsigned* items = nullptr;       // (band * strips + strip) of every item that holds an unknown, compacted
+    unsigned* nactive = nullptr;     // their number
+    void alloc_temporaries(cudaStream_t) {
+        OPTK_CUDA(cudaMalloc(&items, sizeof(unsigned) * ((size_t)strips() * ((H + bandR - 1) / bandR) + 1)));
+        OPTK_CUDA(cudaMalloc(&nactive, sizeof(unsigned)));
+    }
+    void free_temporaries() { cudaFree(items); cudaFree(nactive); items = nullptr; nactive = nullptr; }
+    void build_active_items(cudaStream_t stream, const unsigned char* active4) const;
     bool fast_ok() const { return W % 4 == 0; }
-    long fast_tiles() const { return (long)((W / 4 + 31) / 32) * ((H + 7) / 8); }
+    __host__ __device__ int own_lo() const { return this->o_lo > 0 ? this->o_lo : 0; }
+    __host__ __device__ int own_hi() const { return this->o_hi < H ? this->o_hi : H; }
+    __host__ __device__ int strips() const { return (W / 4 + 31) / 32; }
+    __host__ __device__ int bands() const { return (own_hi() - own_lo() + bandR - 1) / bandR; }
+    long fast_tiles() const {
+        if (tiled) return (long)((W / 4 + 31) / 32) * ((H + 7) / 8);
+        return ((long)4 * strips() * bands() + 7) / 8;
+    }
     dim3 fast_block() const { return dim3(32, 8, 1); }
-    template <bool FUSED, bool LM> static auto fast_kernel();
+    size_t fast_smem() const;
+    template <bool FUSED, bool LM> auto fast_kernel() const;
 
     template <class Fn> __device__ __forceinline__ void neighbours(int x, int y, long s, Fn&& fn) const {
         if (x + 1 < W) fn(s + 1);
@@ -182,6 +213,199 @@ __global__ void __launch_bounds__(256) k_poisson_apply(PoissonFunctor<T> f, Vec<
     block_accumulate(acc, den);
 }
 
-template <class T> template <bool FUSED, bool LM> auto PoissonFunctor<T>::fast_kernel() { return &k_poisson_apply<T, FUSED, LM>; }
+// ---------------------------------------------------------------------------------------------
+// Marching J^T J apply (optionally fused with PCGStep3).  The tile kernel above reads every row of p (and z) three
+// times (as centre, upper and lower neighbour: 6 LDG.128 per quad and channel, 4 of them L1/L2 hits) and is bound by
+// memory latency at 4.0 TB/s (profiles/r1i).  Here the four channel planes are separate work items -- they are
+// independent 5-point Laplacians -- and a warp owns (plane, strip of 128 pixels, band of bandR rows): lane = 4
+// consecutive pixels, the warp marches down the band holding rows n-2, n-1, n of the search direction in registers,
+// so every quad is fetched once (plus 2 / bandR for the band's first and last neighbour rows).  Rows are prefetched
+// D-1 steps ahead by per-thread cp.async (zero-filled for quads without unknowns and for rows outside the image)
+// into a shared-memory ring that only the issuing thread reads back: no barriers, nothing in flight holds registers.
+// Lateral neighbours come from the adjacent lanes by shuffle; lanes 0 and 31 fetch the pixel beyond the strip.
+// The per-pixel mask M is not read at all: active4 holds one bit per pixel of a quad (k_active4, engine.cuh).
+template <class T, bool FUSED, bool LM>
+struct PoissonMarch {
+    static constexpr int QB = 4 * (int)sizeof(T);
+    static constexpr int NA = 1 + (FUSED ? 1 : 0) + (LM ? 1 : 0);
+    static constexpr int STAGE = NA * 256 * QB + 2 * 256 * (int)sizeof(T);
+    static constexpr int D = sizeof(T) == 4 ? 4 : 3;
+    static constexpr int A_P = 0, A_Z = 1, A_C = 1 + (FUSED ? 1 : 0);
+    static __device__ __forceinline__ unsigned char* slot(unsigned char* ring, int st, int arr, int tid) {
+        return ring + (size_t)st * STAGE + (size_t)arr * 256 * QB + (size_t)tid * QB;
+    }
+    static __device__ __forceinline__ unsigned char* eslot(unsigned char* ring, int st, int arr, int tid) {
+        return ring + (size_t)st * STAGE + (size_t)NA * 256 * QB + (size_t)arr * 256 * sizeof(T) + (size_t)tid * sizeof(T);
+    }
+    static __device__ __forceinline__ void cp16(void* dst, const void* src, bool on) {
+        const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+        const int n = on ? 16 : 0;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(n) : "memory");
+    }
+    static __device__ __forceinline__ void cp1(void* dst, const T* src, bool on) {          // one scalar
+        const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+        if constexpr (sizeof(T) == 4) { const int n = on ? 4 : 0; asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(src), "r"(n) : "memory"); }
+        else                          { const int n = on ? 8 : 0; asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(src), "r"(n) : "memory"); }
+    }
+    static __device__ __forceinline__ void cpq(unsigned char* dst, const T* src, bool on) {
+#pragma unroll
+        for (int k = 0; k < QB / 16; ++k) cp16(dst + 16 * k, (const unsigned char*)src + 16 * k, on);
+    }
+};
+
+template <class T, bool FUSED, bool LM>
+__global__ void __launch_bounds__(256, sizeof(T) == 4 ? 3 : 2)
+k_poisson_march(PoissonFunctor<T> f, Vec<T> z, Vec<T> p, Vec<T> p_new, Vec<T> out, Vec<T> CtC,
+                const unsigned char* __restrict__ active4, const double* bNum, const double* aNum, double* den,
+                double* zero_a, double* zero_b) {
+    using PM = PoissonMarch<T, FUSED, LM>;
+    constexpr int D = PM::D;
+    extern __shared__ __align__(16) unsigned char pm_ring[];
+    const int W = f.W, H = f.H, qpr = W / 4;
+    const int tid = linear_tid(), lane = tid & 31;
+    const T beta = FUSED ? (T)(*bNum) / (T)(*aNum) : T(0);
+    if (blockIdx.x == 0 && tid == 0) {
+        if (zero_a) *zero_a = 0.0;
+        if (zero_b) *zero_b = 0.0;
+    }
+    const int strips = f.strips(), bandR = f.bandR, row_lo = f.own_lo(), row_hi = f.own_hi();
+    const long nitems = (long)4 * (*f.nactive);
+    double acc = 0.0;
+    for (long item = blockIdx.x * 8L + (tid >> 5); item < nitems; item += (long)gridDim.x * 8) {     // warp-uniform
+        const int c = (int)(item & 3);
+        const unsigned sb = f.items[item >> 2];
+        const int strip = (int)(sb % strips), band = (int)(sb / strips);
+        const int q = strip * 32 + lane, gx = q * 4;
+        const bool col_in = q < qpr;
+        const int y0 = row_lo + band * bandR, y1 = (y0 + bandR < row_hi) ? y0 + bandR : row_hi;
+        const T* pc = p.d + (long)c * p.plane;
+        const T* zc = z.d + (long)c * z.plane;
+        const T* cc = CtC.d + (long)c * CtC.plane;
+        const bool has_l = lane == 0 && gx > 0, has_r = lane == 31 && gx + 4 < W;
+        const long eoff = lane == 0 ? -1 : 4;                               // pixel beyond the strip's end
+        auto flag_of = [&](int row) -> unsigned { return (col_in && row >= 0 && row < H) ? active4[((long)row * W + gx) >> 2] : 0u; };
+        // issue row `row` into its ring stage; fl = active bits of this lane's quad in that row
+        auto issue = [&](int row, unsigned fl) {
+            const int st = (row + D) % D;                                   // row >= -1
+            const bool on = fl != 0;
+            const long s = on ? (long)row * W + gx : 0;
+            PM::cpq(PM::slot(pm_ring, st, PM::A_P, tid), pc + s, on);
+            if (FUSED) PM::cpq(PM::slot(pm_ring, st, PM::A_Z, tid), zc + s, on);
+            if (LM) PM::cpq(PM::slot(pm_ring, st, PM::A_C, tid), cc + s, on);
+            if (lane == 0 || lane == 31) {
+                // the neighbour quad may be inactive (all zeros) -- loading it is still correct
+                const bool eon = on && (lane == 0 ? has_l : has_r);
+                PM::cp1(PM::eslot(pm_ring, st, 0, tid), pc + (eon ? s + eoff : 0), eon);
+                if (FUSED) PM::cp1(PM::eslot(pm_ring, st, 1, tid), zc + (eon ? s + eoff : 0), eon);
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        const int nbeg = y0 - 1, nend = y1;                                  // rows y0-1 .. y1 pass through the pipeline
+        // fq[k] = active bits of row n+k at the top of step n: fq[D-1] gates the issue of row n+D-1, fq[0] is consumed
+        // with row n; the flag of row n+D is loaded at the top of the step and shifted in at its end
+        auto flag_in = [&](int row) -> unsigned { return row <= nend ? flag_of(row) : 0u; };
+        unsigned fq[D];
+#pragma unroll
+        for (int k = 0; k < D; ++k) fq[k] = flag_in(nbeg + k);
+#pragma unroll
+        for (int k = 0; k < D - 1; ++k) issue(nbeg + k, fq[k]);
+        T prev[4] = {T(0), T(0), T(0), T(0)}, cur[4] = {T(0), T(0), T(0), T(0)}, ccur[4] = {T(0), T(0), T(0), T(0)};
+        T ecur = T(0);
+        unsigned fcur = 0;
+        for (int n = nbeg; n <= nend; ++n) {
+            const unsigned f_next = flag_in(n + D);
+            issue(n + D - 1, fq[D - 1]);
+            if constexpr (D == 4) asm volatile("cp.async.wait_group 3;" ::: "memory");
+            else                  asm volatile("cp.async.wait_group 2;" ::: "memory");
+            // row n has landed
+            const int st = (n + D) % D;
+            const unsigned fnew = fq[0];
+            T nw[4] = {T(0), T(0), T(0), T(0)}, cnew[4] = {T(0), T(0), T(0), T(0)};
+            T enew = T(0);
+            {
+                T a[4]; load4(reinterpret_cast<const T*>(PM::slot(pm_ring, st, PM::A_P, tid)), a);
+                if (FUSED) {
+                    T b[4]; load4(reinterpret_cast<const T*>(PM::slot(pm_ring, st, PM::A_Z, tid)), b);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) nw[j] = b[j] + beta * a[j];
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) nw[j] = a[j];
+                }
+                if (LM) load4(reinterpret_cast<const T*>(PM::slot(pm_ring, st, PM::A_C, tid)), cnew);
+                if (lane == 0 || lane == 31) {
+                    const T ea = *reinterpret_cast<const T*>(PM::eslot(pm_ring, st, 0, tid));
+                    enew = FUSED ? *reinterpret_cast<const T*>(PM::eslot(pm_ring, st, 1, tid)) + beta * ea : ea;
+                }
+            }
+            // output row y = n-1 (cur) with prev above and nw below
+            const int y = n - 1;
+            T lft = __shfl_up_sync(0xffffffffu, cur[3], 1);
+            T rgt = __shfl_down_sync(0xffffffffu, cur[0], 1);
+            if (lane == 0) lft = ecur;
+            if (lane == 31) rgt = ecur;
+            if (y >= y0 && y < y1 && fcur != 0) {
+                const bool up = y > 0, dn = y + 1 < H;
+                T o[4], pn[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const T v = cur[j];
+                    T a = T(0);
+                    if (gx + j + 1 < W) a += v - (j < 3 ? cur[j + 1] : rgt);      // {1,0}
+                    if (gx + j > 0) a += v - (j > 0 ? cur[j - 1] : lft);          // {-1,0}
+                    if (dn) a += v - nw[j];                                       // {0,1}
+                    if (up) a += v - prev[j];                                     // {0,-1}
+                    a = T(2) * a;
+                    const bool exj = ((fcur >> j) & 1u) == 0;
+                    pn[j] = exj ? T(0) : v;
+                    o[j] = exj ? T(0) : a;
+                    if (LM) { if (!exj) o[j] += ccur[j] * pn[j]; }
+                    acc += (double)(pn[j] * o[j]);
+                }
+                const long s = (long)y * W + gx;
+                if (FUSED) st4v(p_new.d + (long)c * p_new.plane + s, pn);
+                st4v(out.d + (long)c * out.plane + s, o);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { prev[j] = cur[j]; cur[j] = nw[j]; ccur[j] = cnew[j]; }
+            ecur = enew; fcur = fnew;
+#pragma unroll
+            for (int k = 0; k + 1 < D; ++k) fq[k] = fq[k + 1];
+            fq[D - 1] = f_next;
+        }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    block_accumulate(acc, den);
+}
+
+// One warp per (strip, band): does any quad of its owned rows hold an unknown?  Kept items are appended to the list
+// (the four channel planes of an item stay adjacent in the march kernel's item numbering).
+template <class T>
+__global__ void __launch_bounds__(256) k_poisson_items(PoissonFunctor<T> f, const unsigned char* __restrict__ active4) {
+    const int lane = threadIdx.x & 31;
+    const long w = (blockIdx.x * (long)blockDim.x + threadIdx.x) >> 5;
+    const int strips = f.strips(), bands = f.bands();
+    if (w >= (long)strips * bands) return;
+    const int strip = (int)(w % strips), band = (int)(w / strips);
+    const int q = strip * 32 + lane, y0 = f.own_lo() + band * f.bandR, y1 = min(y0 + f.bandR, f.own_hi());
+    unsigned any = 0;
+    if (q < f.W / 4)
+        for (int y = y0; y < y1; ++y) any |= active4[((long)y * f.W >> 2) + q];
+    any = __any_sync(0xffffffffu, any != 0);
+    if (any && lane == 0) f.items[atomicAdd(f.nactive, 1u)] = (unsigned)w;
+}
+template <class T> void PoissonFunctor<T>::build_active_items(cudaStream_t stream, const unsigned char* active4) const {
+    OPTK_CUDA(cudaMemsetAsync(nactive, 0, sizeof(unsigned), stream));
+    const long warps = (long)strips() * bands();
+    k_poisson_items<T><<<(unsigned)((warps * 32 + 255) / 256), 256, 0, stream>>>(*this, active4);
+}
+
+template <class T> size_t PoissonFunctor<T>::fast_smem() const {
+    if (tiled) return 0;
+    return (size_t)PoissonMarch<T, true, true>::STAGE * PoissonMarch<T, true, true>::D;
+}
+template <class T> template <bool FUSED, bool LM> auto PoissonFunctor<T>::fast_kernel() const {
+    return tiled ? &k_poisson_apply<T, FUSED, LM> : &k_poisson_march<T, FUSED, LM>;
+}
 
 }  // namespace optk

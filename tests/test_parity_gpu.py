@@ -13,6 +13,8 @@ pytestmark = pytest.mark.gpu
 CASES = {
     "poisson": (examples.poisson_synthetic, (67, 45), dict(n_iter=2, l_iter=12)),
     "poisson_aligned": (examples.poisson_synthetic, (128, 64), dict(n_iter=1, l_iter=20)),
+    # rows of whole quads, two strips (the second one ragged: 37 quads) and six bands of the marching J^T J kernel
+    "poisson_strips": (examples.poisson_synthetic, (148, 83), dict(n_iter=2, l_iter=12)),
     "image_warping": (examples.image_warping_synthetic, (61, 47), dict(n_iter=3, l_iter=10)),
     "volumetric": (examples.volumetric_synthetic, (11, 9, 7), dict(n_iter=3, l_iter=10)),
     # several 30x4x4 (fp32) / 30x4x2 (fp64) tiles of the tiled J^T J kernel per dimension, ragged edges
@@ -111,6 +113,31 @@ def test_volumetric_tiled_jtj_equals_generic(built, case, double, monkeypatch):
     generic = sol.debug_apply_jtj(named, p)
     assert not np.array_equal(fast, generic)          # really two code paths
     assert np.abs(fast - generic).max() <= OP_RTOL[double] * np.abs(generic).max()
+
+
+@pytest.mark.parametrize("double", [False, True])
+@pytest.mark.parametrize("case", ["poisson_aligned", "poisson_strips"])
+def test_poisson_marching_jtj_equals_tile_kernel(built, case, double, monkeypatch):
+    """k_poisson_march (one channel plane per warp, rows carried in registers, cp.async ring, per-pixel bits of
+    active4 instead of the mask image) against the tile kernel k_poisson_apply, GN and LM solves included."""
+    from opt_b200 import solver as S
+    pr = make(case, double=double)
+    rng = np.random.default_rng(9)
+    unknown = (pr.params[2].reshape(-1) == 0)
+    p = (rng.standard_normal((int(np.prod(pr.dims)), 4)) * unknown[:, None]).astype(np.float64 if double else np.float32)
+    march = S.OptSolver(pr.dims, pr.energy, pr.kind, double=double).debug_apply_jtj(S.upload(pr), p)
+    monkeypatch.setenv("OPTB200_POISSON_TILED", "1")          # read when the plan is made
+    tiled = S.OptSolver(pr.dims, pr.energy, pr.kind, double=double).debug_apply_jtj(S.upload(pr), p)
+    assert np.abs(march).max() > 0
+    assert np.abs(march - tiled).max() <= OP_RTOL[double] * np.abs(tiled).max()
+    for kind in ("gaussNewtonGPU", "LMGPU"):
+        q = make(case, kind, double)
+        ct, xt, _, _ = run_gpu(q)
+        monkeypatch.delenv("OPTB200_POISSON_TILED")
+        cm, xm, _, _ = run_gpu(q)
+        monkeypatch.setenv("OPTB200_POISSON_TILED", "1")
+        assert_costs_close(cm, ct, double)
+        assert_unknowns_close(xm, xt, double)
 
 
 @pytest.mark.parametrize("double", [False, True])
