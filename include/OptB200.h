@@ -27,6 +27,17 @@ void OptB200_FreeState(Opt_State* state);
 void OptB200_GetNcclUniqueId(void* out128);
 int  OptB200_PlanSetSlab(Opt_Plan* plan, int rank, int nranks, int halo, const void* nccl_unique_id);
 
+/* ---- energy-file verification (a restricted front end; the reference compiles the file, o.t:3305-3309) ----------
+ * OptB200_EnergyDescribe parses the Lua/Terra energy file at `path` far enough to list what fixes the C-ABI binding
+ * -- Dim / Unknown / Array / Param / Graph declarations with types and problemparams indices, ComputedArrays,
+ * UsePreconditioner, Exclude -- followed by a fingerprint of the comment- and space-free source, one item per line
+ * into `out`.  Returns 0, 1 if the file cannot be read, -1 on overflow / parse failure.  OptB200_EnergyExpected
+ * returns the description the built-in functor of `energy` (basename without ".t") was written for, or NULL.
+ * Opt_ProblemDefine rejects a readable file whose description differs (OPTB200_ALLOW_MODIFIED_ENERGY=1 accepts a file
+ * whose declarations match but whose expressions were edited); a path that cannot be read is bound by its name. */
+int OptB200_EnergyDescribe(const char* path, char* out, unsigned long cap);
+const char* OptB200_EnergyExpected(const char* energy);
+
 /* Kernels launched by this plan since it was created (bench.py's "gpu_launches"). */
 long OptB200_PlanLaunchCount(Opt_Plan* plan);
 /* PCG iterations executed by this plan since it was created.  Gauss-Newton always runs nIterations x lIterations;

@@ -22,7 +22,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 def _headers():
     out = []
     for d, _, fs in os.walk(CSRC):
-        out += [os.path.join(d, f) for f in fs if f.endswith((".cuh", ".h"))]
+        out += [os.path.join(d, f) for f in fs if f.endswith((".cuh", ".h", ".inc"))]
     out += [os.path.join(ROOT, "include", f) for f in os.listdir(os.path.join(ROOT, "include"))]
     return out
 
@@ -50,7 +50,7 @@ def _compile(src, verbose):
 
 def build(verbose=False, oracle=True):
     os.makedirs(OBJ, exist_ok=True)
-    srcs = [os.path.join(CSRC, "opt_api.c"), os.path.join(CSRC, "registry.cu"), os.path.join(CSRC, "driver_ops.cu"), os.path.join(CSRC, "formats.c")]
+    srcs = [os.path.join(CSRC, "opt_api.c"), os.path.join(CSRC, "registry.cu"), os.path.join(CSRC, "driver_ops.cu"), os.path.join(CSRC, "formats.c"), os.path.join(CSRC, "energy_check.c")]
     ex = os.path.join(CSRC, "examples")
     srcs += sorted(os.path.join(ex, f) for f in os.listdir(ex) if f.endswith(".cu"))
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as pool:

@@ -18,6 +18,8 @@
 #include "../../include/OptB200.h"
 #include "optk.h"
 
+int optb200_energy_verify(const char* path, const char* energy, char* msg, size_t cap);   /* energy_check.c */
+
 struct Opt_State {
     Opt_InitializationParameters ip;
 };
@@ -86,6 +88,21 @@ Opt_Problem* Opt_ProblemDefine(Opt_State* state, const char* filename, const cha
                         "supported (there is no energy compiler in this library)\n", filename);
         free(p);
         return NULL;
+    }
+    /* The reference compiles the file; here it is checked against the description the functor was written for
+       (energy_check.c).  A path that cannot be read (drivers run from other directories, tests pass bare names) is
+       bound by its name alone. */
+    {
+        char why[512];
+        const int v = optb200_energy_verify(filename, p->energy, why, sizeof(why));
+        if (v == -2 && getenv("OPTB200_ALLOW_MODIFIED_ENERGY")) {
+            fprintf(stderr, "Opt: warning: energy file '%s': %s (accepted: OPTB200_ALLOW_MODIFIED_ENERGY is set)\n", filename, why);
+        } else if (v < 0) {
+            fprintf(stderr, "Opt: energy file '%s' is not the one the built-in functor set for '%s' implements: %s\n",
+                    filename, p->energy, why);
+            free(p);
+            return NULL;
+        }
     }
     p->is_lm = strstr(solverkind, "LM") != NULL; /* o.t:474 */
     return p;
