@@ -65,6 +65,22 @@ def build(verbose=False, oracle=True):
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed: %s\n%s" % (" ".join(cmd), r.stderr))
+    # the C drivers that show the library behind the unchanged Opt.h (drivers_c/): plain C, linked like the reference's
+    bindir = os.path.join(ROOT, "opt_b200", "bin")
+    os.makedirs(bindir, exist_ok=True)
+    ddir = os.path.join(ROOT, "drivers_c")
+    for f in sorted(os.listdir(ddir)):
+        if not f.endswith(".c"):
+            continue
+        exe = os.path.join(bindir, f[:-2])
+        if _stale(exe, [os.path.join(ddir, f), LIB] + _headers()):
+            cuda = os.path.dirname(os.path.dirname(NVCC))
+            cmd = [HOST_CC, "-O2", "-std=c11", "-Wall", "-I" + os.path.join(cuda, "include"), os.path.join(ddir, f), "-o", exe,
+                   "-L" + os.path.dirname(LIB), "-lOptB200", "-L" + os.path.join(cuda, "lib64"), "-lcudart",
+                   "-Wl,-rpath,$ORIGIN/..", "-Wl,-rpath," + os.path.join(cuda, "lib64")]
+            r = subprocess.run(cmd, capture_output=True, text=True)
+            if r.returncode != 0:
+                raise RuntimeError("driver build failed: %s\n%s" % (" ".join(cmd), r.stderr))
     if oracle:
         subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
     return LIB
