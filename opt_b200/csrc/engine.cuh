@@ -645,6 +645,25 @@ __global__ void __launch_bounds__(256) k_pcg_step3(long nvec, const unsigned cha
     }
 }
 
+// Slab mode with the fused PCGStep3+PCGStep1 kernel: the new search direction p' = z + beta p of the owned rows next to a
+// neighbouring slab, computed ahead of the fused kernel so that it can be sent into the neighbour's ghost rows of p'
+// (the fused kernel then takes its ghost rows from p' instead of forming z + beta p there).  SoA vectors only.
+template <class T>
+__global__ void __launch_bounds__(256) k_boundary_dir(const T* __restrict__ z, const T* __restrict__ p, T* __restrict__ p_new, long plane, int U,
+                                                      long rowsz, int lo, int hi, int halo, int has_lo, int has_hi,
+                                                      const double* bNum, const double* aNum) {
+    const T beta = (T)(*bNum) / (T)(*aNum);
+    const long per_side = rowsz * halo, total = per_side * 2 * U;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int u = (int)(i / (2 * per_side));
+        const long r = i % (2 * per_side);
+        const bool upper = r >= per_side;
+        if (upper ? !has_hi : !has_lo) continue;
+        const long e = (long)u * plane + (upper ? (long)(hi - halo) * rowsz + (r - per_side) : (long)lo * rowsz + r);
+        p_new[e] = z[e] + beta * p[e];
+    }
+}
+
 // PCGStep2_1stHalf (solver:738-762): delta += alpha p
 template <class T>
 __global__ void __launch_bounds__(256) k_axpy_alpha(long nvec, const unsigned char* __restrict__ active4, long plane,
@@ -722,6 +741,91 @@ __global__ void k_lm_zeta(int l, double q_tol, const double* q, double* qprev, d
     b->seq = seq;
 }
 
+// ---- scalar all-reduce over NVLink peer memory ------------------------------------------------------------
+// The PCG loop needs two dependent scalar all-reduces per iteration (alphaDen after PCGStep1, betaNum after PCGStep2).
+// ncclAllReduce of 8 bytes costs a full collective launch each (~10-15 us); here every rank stores its partial sums
+// straight into a mailbox in EVERY peer's memory (cudaIpc-mapped at OptB200_PlanSetSlab; NVSwitch gives every pair a
+// direct path), fences, publishes an epoch number, and then waits for the N epochs in its own mailbox: one tiny
+// kernel, one NVLink store latency.  Sums are formed in rank order, so every rank gets the bit-identical result.
+// Two mailbox sets alternate by epoch parity: a rank cannot run two epochs ahead of a peer that has not finished
+// reading, because finishing epoch k+1 needs that peer's epoch-k+1 contribution.
+constexpr int XR_MAX_RANKS = 16, XR_MAX_VALS = 4;
+struct XSlot { double v[XR_MAX_VALS]; long long epoch; long long pad[3]; };
+struct XPeers { XSlot* p[XR_MAX_RANKS]; };
+static __global__ void k_xreduce(double* vals, int count, XPeers peers, int rank, int nranks, long long epoch, int* error_flag) {
+    if (threadIdx.x != 0) return;
+    const int par = (int)(epoch & 1);
+    for (int t = 0; t < nranks; ++t) {
+        volatile XSlot* dst = peers.p[t] + par * XR_MAX_RANKS + rank;
+        for (int c = 0; c < count; ++c) dst->v[c] = vals[c];
+    }
+    __threadfence_system();
+    for (int t = 0; t < nranks; ++t) {
+        volatile XSlot* dst = peers.p[t] + par * XR_MAX_RANKS + rank;
+        dst->epoch = epoch;
+    }
+    double sum[XR_MAX_VALS] = {0.0, 0.0, 0.0, 0.0};
+    for (int t = 0; t < nranks; ++t) {
+        volatile XSlot* src = peers.p[rank] + par * XR_MAX_RANKS + t;
+        long long spins = 0;
+        while (src->epoch != epoch) {
+            if (++spins > (1LL << 28)) { *error_flag = 1; return; }     // minutes: a peer died; give up instead of hanging the GPU
+        }
+        __threadfence_system();
+        for (int c = 0; c < count; ++c) sum[c] += src->v[c];
+    }
+    for (int c = 0; c < count; ++c) vals[c] = sum[c];
+}
+
+// Halo exchange of the fused slab path through peer memory: the new search direction of the owned boundary rows is
+// computed and stored STRAIGHT into the neighbours' ghost rows (their solver-vector pools are cudaIpc-mapped); the
+// last block to finish publishes an epoch in both neighbours' mailboxes and waits for theirs (system-scope fences order
+// every block's data stores before the flag store); the fused kernel is queued behind this one.
+template <class T>
+struct HaloPeer { T* base; long plane; long row; };          // neighbour's p' vector, its plane stride, first ghost row to fill
+__device__ __forceinline__ void halo_signal_and_wait(const XPeers& peers, int rank, int nranks, long long epoch, int* error_flag) {
+    // mailbox words: slot [2*XR_MAX_RANKS + 1].v[0..1] reinterpreted as two epochs: [0] written by rank-1, [1] by rank+1
+    __threadfence_system();
+    if (rank > 0) ((volatile long long*)peers.p[rank - 1][2 * XR_MAX_RANKS + 1].v)[1] = epoch;
+    if (rank < nranks - 1) ((volatile long long*)peers.p[rank + 1][2 * XR_MAX_RANKS + 1].v)[0] = epoch;
+    volatile long long* mine = (volatile long long*)peers.p[rank][2 * XR_MAX_RANKS + 1].v;
+    for (int side = 0; side < 2; ++side) {
+        if (side == 0 ? rank == 0 : rank == nranks - 1) continue;
+        long long spins = 0;
+        while (mine[side] < epoch) { if (++spins > (1LL << 28)) { *error_flag = 1; return; } }
+    }
+    __threadfence_system();
+}
+// One launch: every block stores its share of the boundary rows into the neighbours' ghost rows; the block that
+// finishes last (device-wide counter) publishes the epoch and waits for the neighbours' epochs.
+template <class T>
+__global__ void __launch_bounds__(256) k_boundary_push(const T* __restrict__ z, const T* __restrict__ p, long plane, int U, long rowsz,
+                                                       int lo, int hi, int halo, HaloPeer<T> below, HaloPeer<T> above,
+                                                       const double* bNum, const double* aNum,
+                                                       XPeers peers, int rank, int nranks, long long epoch, int* error_flag, unsigned* done_counter) {
+    const T beta = (T)(*bNum) / (T)(*aNum);
+    const long per_side = rowsz * halo, total = per_side * 2 * U;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int u = (int)(i / (2 * per_side));
+        const long r = i % (2 * per_side);
+        const bool upper = r >= per_side;
+        const HaloPeer<T>& nb = upper ? above : below;
+        if (!nb.base) continue;
+        const long off = upper ? r - per_side : r;
+        const long e = (long)u * plane + (upper ? (long)(hi - halo) * rowsz : (long)lo * rowsz) + off;
+        nb.base[(long)u * nb.plane + nb.row * rowsz + off] = z[e] + beta * p[e];
+    }
+    __threadfence_system();                                  // this thread's remote stores before the block's arrival
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned arrived = atomicAdd(done_counter, 1u);
+        if (arrived == gridDim.x - 1) {
+            *done_counter = 0;                               // next launch
+            halo_signal_and_wait(peers, rank, nranks, epoch, error_flag);
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------ the engine
 template <class F>
 struct Engine : OptK_Plan {
@@ -754,6 +858,13 @@ struct Engine : OptK_Plan {
     // slab decomposition along the slowest dimension; nranks == 1: single GPU
     int rank = 0, nranks = 1, halo = 0;
     ncclComm_t comm = nullptr;
+    // scalar all-reduce through peer memory (k_xreduce); xr_on == false: ncclAllReduce
+    bool xr_on = false;
+    XSlot* xr_buf = nullptr; XPeers xr_peers{}; long long xr_epoch = 0; int* xr_error = nullptr;
+    std::vector<void*> xr_opened;
+    // halo exchange through peer memory (fused slab path): neighbours' pools and geometry
+    bool xh_on = false; long long xh_epoch = 0;
+    T* nb_pool[2] = {nullptr, nullptr}; long nb_npad[2] = {0, 0}; long nb_row[2] = {0, 0};
 
     Engine(const unsigned* dims, bool is_lm, bool collect_timing) : lm(is_lm) {
         base_init(collect_timing);
@@ -796,6 +907,8 @@ struct Engine : OptK_Plan {
     ~Engine() override {
         cudaStreamSynchronize(stream);
         f.free_temporaries();
+        for (void* q : xr_opened) cudaIpcCloseMemHandle(q);
+        cudaFree(xr_buf); cudaFree(xr_error);
         if (comm) ncclCommDestroy(comm);
         cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFreeHost(lm_box); cudaFree(active4);
         cudaFree(inc); cudaFree(inc_off); cudaFree(inc_count); cudaFree(sort_tmp); cudaFree(key_a); cudaFree(key_b); cudaFree(val_a);
@@ -816,7 +929,9 @@ struct Engine : OptK_Plan {
         if (F::ND < 2 || GRAPH || !F::SLAB_OK) { fprintf(stderr, "Opt: slab decomposition is not available for this energy\n"); return -1; }
         const int L = F::ND == 3 ? f.D : f.H;
         rank = rk; nranks = nr; halo = h;
-        if (nranks > 1) fuse = false;                       // ghost rows of p are refreshed after PCGStep3
+        // ghost rows of p are refreshed after PCGStep3; the fused PCGStep3+1 kernel stays on only for functors whose
+        // kernel takes its ghost rows from the exchanged p' (FUSE_SLAB, see k_boundary_dir)
+        if (nranks > 1 && !(F::FUSE_SLAB && F::VEC_UB == 0 && f.fuse_slab_ok())) fuse = false;
         f.o_lo = rank > 0 ? halo : 0;
         f.o_hi = rank < nranks - 1 ? L - halo : L;
         if (f.o_hi - f.o_lo < halo) { fprintf(stderr, "Opt: slab thinner than its halo\n"); return -1; }
@@ -834,6 +949,7 @@ struct Engine : OptK_Plan {
             OPTK_CUDA(cudaMemcpyAsync(h.data(), cnt, (size_t)nranks * sizeof(int), cudaMemcpyDeviceToHost, stream));
             OPTK_CUDA(cudaStreamSynchronize(stream));
             cudaFree(cnt);
+            setup_peer_reduce();
             for (int r2 = 0; r2 < rank; ++r2) slow_off += h[r2];
             slow_off -= f.o_lo;
         }
@@ -841,7 +957,96 @@ struct Engine : OptK_Plan {
         return 0;
     }
     void reduce(int slot, int count = 1) {                  // sum over ranks, in place, device-resident
-        if (nranks > 1) { OPTK_NCCL(ncclAllReduce(scal + slot, scal + slot, count, ncclDouble, ncclSum, comm, stream)); }
+        if (nranks <= 1) return;
+        if (xr_on && count <= XR_MAX_VALS) {
+            this->launch("AllReduceP2P", dim3(1), dim3(32), k_xreduce, scal + slot, count, xr_peers, rank, nranks, ++xr_epoch, xr_error);
+            return;
+        }
+        OPTK_NCCL(ncclAllReduce(scal + slot, scal + slot, count, ncclDouble, ncclSum, comm, stream));
+    }
+    // Map a mailbox of every peer (one process per GPU on one node): the cudaIpc handles travel through an NCCL
+    // all-gather; a magic number written by the owner is read back through the mapping before the path is enabled.
+    void setup_peer_reduce() {
+        if (getenv("OPTB200_NO_P2P") || nranks > XR_MAX_RANKS) return;
+        const size_t bytes = 4u << 20;                      // its own allocation block: the IPC handle maps the block base
+        OPTK_CUDA(cudaMalloc(&xr_buf, bytes));
+        OPTK_CUDA(cudaMemsetAsync(xr_buf, 0, bytes, stream));
+        OPTK_CUDA(cudaMalloc(&xr_error, 2 * sizeof(int)));   // [0] error flag, [1] arrival counter of k_boundary_push
+        OPTK_CUDA(cudaMemsetAsync(xr_error, 0, 2 * sizeof(int), stream));
+        const long long magic = 0x4f70744232303000LL + rank;
+        OPTK_CUDA(cudaMemcpyAsync(&xr_buf[2 * XR_MAX_RANKS].epoch, &magic, sizeof(magic), cudaMemcpyHostToDevice, stream));
+        cudaIpcMemHandle_t mine;
+        OPTK_CUDA(cudaIpcGetMemHandle(&mine, xr_buf));
+        char* dh = nullptr;
+        OPTK_CUDA(cudaMalloc(&dh, sizeof(mine) * (size_t)(nranks + 1)));
+        OPTK_CUDA(cudaMemcpyAsync(dh + sizeof(mine) * (size_t)nranks, &mine, sizeof(mine), cudaMemcpyHostToDevice, stream));
+        OPTK_NCCL(ncclAllGather(dh + sizeof(mine) * (size_t)nranks, dh, sizeof(mine), ncclChar, comm, stream));
+        std::vector<cudaIpcMemHandle_t> all(nranks);
+        OPTK_CUDA(cudaMemcpyAsync(all.data(), dh, sizeof(mine) * (size_t)nranks, cudaMemcpyDeviceToHost, stream));
+        OPTK_CUDA(cudaStreamSynchronize(stream));
+        cudaFree(dh);
+        bool ok = true;
+        for (int r2 = 0; r2 < nranks && ok; ++r2) {
+            if (r2 == rank) { xr_peers.p[r2] = xr_buf; continue; }
+            void* ptr = nullptr;
+            if (cudaIpcOpenMemHandle(&ptr, all[r2], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+            xr_opened.push_back(ptr);
+            xr_peers.p[r2] = (XSlot*)ptr;
+            long long seen = 0;
+            if (cudaMemcpy(&seen, &xr_peers.p[r2][2 * XR_MAX_RANKS].epoch, sizeof(seen), cudaMemcpyDeviceToHost) != cudaSuccess ||
+                seen != 0x4f70744232303000LL + r2) { cudaGetLastError(); ok = false; }
+        }
+        // every rank must take the same path
+        int* flag = nullptr;
+        OPTK_CUDA(cudaMalloc(&flag, sizeof(int)));
+        const int mine_ok = ok ? 1 : 0;
+        OPTK_CUDA(cudaMemcpyAsync(flag, &mine_ok, sizeof(int), cudaMemcpyHostToDevice, stream));
+        OPTK_NCCL(ncclAllReduce(flag, flag, 1, ncclInt, ncclMin, comm, stream));
+        int all_ok = 0;
+        OPTK_CUDA(cudaMemcpyAsync(&all_ok, flag, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        OPTK_CUDA(cudaStreamSynchronize(stream));
+        cudaFree(flag);
+        xr_on = all_ok == 1;
+        if (!xr_on && rank == 0) fprintf(stderr, "Opt: peer-memory all-reduce unavailable, using ncclAllReduce\n");
+        if (xr_on && fuse && F::VEC_UB == 0) setup_peer_halo();
+    }
+    // neighbours' solver-vector pools (for k_boundary_push) and where their ghost rows are
+    void setup_peer_halo() {
+        struct Geo { cudaIpcMemHandle_t h; long npad; long ghost_from_below; long ghost_from_above; };
+        Geo mine;
+        OPTK_CUDA(cudaIpcGetMemHandle(&mine.h, pool));
+        mine.npad = Npad;
+        mine.ghost_from_below = f.o_lo - halo;              // rows [o_lo - halo, o_lo) are filled by rank - 1
+        mine.ghost_from_above = f.o_hi;                     // rows [o_hi, o_hi + halo) by rank + 1
+        char* dg = nullptr;
+        OPTK_CUDA(cudaMalloc(&dg, sizeof(Geo) * (size_t)(nranks + 1)));
+        OPTK_CUDA(cudaMemcpyAsync(dg + sizeof(Geo) * (size_t)nranks, &mine, sizeof(Geo), cudaMemcpyHostToDevice, stream));
+        OPTK_NCCL(ncclAllGather(dg + sizeof(Geo) * (size_t)nranks, dg, sizeof(Geo), ncclChar, comm, stream));
+        std::vector<Geo> all(nranks);
+        OPTK_CUDA(cudaMemcpyAsync(all.data(), dg, sizeof(Geo) * (size_t)nranks, cudaMemcpyDeviceToHost, stream));
+        OPTK_CUDA(cudaStreamSynchronize(stream));
+        cudaFree(dg);
+        bool ok = true;
+        for (int side = 0; side < 2 && ok; ++side) {
+            const int nb = side == 0 ? rank - 1 : rank + 1;
+            if (nb < 0 || nb >= nranks) continue;
+            void* ptr = nullptr;
+            if (cudaIpcOpenMemHandle(&ptr, all[nb].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+            xr_opened.push_back(ptr);
+            nb_pool[side] = (T*)ptr;
+            nb_npad[side] = all[nb].npad;
+            nb_row[side] = side == 0 ? all[nb].ghost_from_above : all[nb].ghost_from_below;   // I am above rank-1, below rank+1
+        }
+        int* flag = nullptr;
+        OPTK_CUDA(cudaMalloc(&flag, sizeof(int)));
+        const int mine_ok = ok ? 1 : 0;
+        OPTK_CUDA(cudaMemcpyAsync(flag, &mine_ok, sizeof(int), cudaMemcpyHostToDevice, stream));
+        OPTK_NCCL(ncclAllReduce(flag, flag, 1, ncclInt, ncclMin, comm, stream));
+        int all_ok = 0;
+        OPTK_CUDA(cudaMemcpyAsync(&all_ok, flag, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        OPTK_CUDA(cudaStreamSynchronize(stream));
+        cudaFree(flag);
+        xh_on = all_ok == 1;
     }
     // ghost rows/planes of a contiguous array with `nplanes` planes of stride `pstride` elements,
     // `rowsz` elements per row (2-D) or per plane (3-D) of the slowest dimension
@@ -878,7 +1083,13 @@ struct Engine : OptK_Plan {
 
     double read_scalar(int slot) {                          // blocking D2H (backend_cuda.t:353-355)
         OPTK_CUDA(cudaMemcpyAsync(h_scal, scal + slot, sizeof(double), cudaMemcpyDeviceToHost, stream));
+        if (xr_on) OPTK_CUDA(cudaMemcpyAsync(h_scal + 1, xr_error, sizeof(int), cudaMemcpyDeviceToHost, stream));
         OPTK_CUDA(cudaStreamSynchronize(stream));
+        if (xr_on && *(const int*)(h_scal + 1) != 0) {
+            printf("Opt: a peer rank never arrived at a scalar all-reduce (rank %d of %d)\n", rank, nranks);
+            fflush(stdout);
+            exit(3);
+        }
         return h_scal[0];
     }
 
@@ -1043,6 +1254,25 @@ struct Engine : OptK_Plan {
         if (fuse && l > 0) {
             // p' = z + beta p with beta = RZ[l%3] / RZ[(l-1)%3] (the PCGStep3 of iteration l-1), then Ap'
             double* prevA = S(S_RZ0 + (l + 2) % 3);
+            if (nranks > 1) {                               // only reached with F::FUSE_SLAB
+                const long rowsz = (long)slow_rowsz();
+                const long total = rowsz * halo * 2 * U;
+                if (xh_on) {
+                    // which of the two p buffers is p' this iteration: the same slot on every rank (they swap in lockstep)
+                    const long slot = (long)((p_alt.d - pool) / ((long)U * Npad));
+                    HaloPeer<T> below{nullptr, 0, 0}, above{nullptr, 0, 0};
+                    if (rank > 0) below = HaloPeer<T>{nb_pool[0] + slot * U * nb_npad[0], nb_npad[0], nb_row[0]};
+                    if (rank < nranks - 1) above = HaloPeer<T>{nb_pool[1] + slot * U * nb_npad[1], nb_npad[1], nb_row[1]};
+                    this->launch("PCGStep3_BoundaryPush", dim3((unsigned)std::min<long>((total + 255) / 256, (long)nsm * 4)), dim3(256), k_boundary_push<T>,
+                                 (const T*)z.d, (const T*)p.d, (long)p.plane, (int)U, rowsz, f.o_lo, f.o_hi, halo, below, above,
+                                 (const double*)aNum, (const double*)prevA, xr_peers, rank, nranks, ++xh_epoch, xr_error, (unsigned*)(xr_error + 1));
+                } else {
+                this->launch("PCGStep3_Boundary", dim3((unsigned)std::min<long>((total + 255) / 256, (long)nsm * 4)), dim3(256), k_boundary_dir<T>,
+                             (const T*)z.d, (const T*)p.d, p_alt.d, (long)p.plane, (int)U, rowsz, f.o_lo, f.o_hi, halo, (int)(rank > 0), (int)(rank < nranks - 1),
+                             (const double*)aNum, (const double*)prevA);
+                exchange(p_alt);
+                }
+            }
             if constexpr (F::HAS_FAST_APPLY) {
                 if (f.fast_ok()) {
                     if (lm) this->launch_tiles_smem("PCGStep3+1", f.fast_tiles(), f.fast_block(), f.fast_smem(), f.template fast_kernel<true, true>(), f, z, p, p_alt, Ap, CtC, (const unsigned char*)active4, (const double*)aNum, (const double*)prevA, aDen, bNum, S(S_Q));
@@ -1188,6 +1418,8 @@ struct FunctorDefaults {
     static constexpr bool HAS_CUSTOM_PRECOMPUTE = false; // precompute is a functor-launched kernel (own table layout)
     static constexpr bool HAS_EXCLUDE = false;           // functors with an Exclude() override this
     static constexpr bool HAS_FAST_APPLY = false;        // functors with a specialised J^T J kernel override this
+    static constexpr bool FUSE_SLAB = false;             // ... whose fused kernel reads ghost rows from the exchanged p' (slab mode)
+    bool fuse_slab_ok() const { return false; }
     static constexpr bool HAS_ACTIVE_ITEMS = false;      // ... whose kernel walks a compacted list of work items (poisson)
     static constexpr bool HAS_FAST_INIT = false;         // ... and with a specialised PCGInit1 (fast_init_kernel())
     static constexpr bool HAS_FAST_COST = false;         // ... and computeCost (fast_cost_kernel())

@@ -36,6 +36,8 @@ struct PoissonFunctor : FunctorDefaults<T> {
     // tile kernel k_poisson_apply (OPTB200_POISSON_TILED=1 when the plan is made; tests compare the two).
     static constexpr bool HAS_FAST_APPLY = true;
     static constexpr bool HAS_ACTIVE_ITEMS = true;
+    static constexpr bool FUSE_SLAB = true;          // k_poisson_march takes ghost rows from the exchanged p' (engine.cuh k_boundary_dir)
+    bool fuse_slab_ok() const { return fast_ok() && !tiled; }
     bool tiled = false;
     int bandR = 16;
     unsigned* items = nullptr;       // (band * strips + strip) of every item that holds an unknown, compacted
@@ -280,6 +282,7 @@ k_poisson_march(PoissonFunctor<T> f, Vec<T> z, Vec<T> p, Vec<T> p_new, Vec<T> ou
         const int y0 = row_lo + band * bandR, y1 = (y0 + bandR < row_hi) ? y0 + bandR : row_hi;
         const T* pc = p.d + (long)c * p.plane;
         const T* zc = z.d + (long)c * z.plane;
+        const T* nc = p_new.d + (long)c * p_new.plane;                       // FUSED, slab mode: ghost rows of p' (exchanged)
         const T* cc = CtC.d + (long)c * CtC.plane;
         const bool has_l = lane == 0 && gx > 0, has_r = lane == 31 && gx + 4 < W;
         const long eoff = lane == 0 ? -1 : 4;                               // pixel beyond the strip's end
@@ -289,14 +292,18 @@ k_poisson_march(PoissonFunctor<T> f, Vec<T> z, Vec<T> p, Vec<T> p_new, Vec<T> ou
             const int st = (row + D) % D;                                   // row >= -1
             const bool on = fl != 0;
             const long s = on ? (long)row * W + gx : 0;
-            PM::cpq(PM::slot(pm_ring, st, PM::A_P, tid), pc + s, on);
-            if (FUSED) PM::cpq(PM::slot(pm_ring, st, PM::A_Z, tid), zc + s, on);
+            // rows of a neighbouring slab (slab mode, fused): the direction is the received p' itself; it goes through
+            // the z slot with a zero-filled p slot, so the consumer's z + beta p yields it unchanged
+            const bool ghost = FUSED && (row < row_lo || row >= row_hi);
+            const T* zsrc = ghost ? nc : zc;
+            PM::cpq(PM::slot(pm_ring, st, PM::A_P, tid), pc + s, on && !ghost);
+            if (FUSED) PM::cpq(PM::slot(pm_ring, st, PM::A_Z, tid), zsrc + s, on);
             if (LM) PM::cpq(PM::slot(pm_ring, st, PM::A_C, tid), cc + s, on);
             if (lane == 0 || lane == 31) {
                 // the neighbour quad may be inactive (all zeros) -- loading it is still correct
                 const bool eon = on && (lane == 0 ? has_l : has_r);
-                PM::cp1(PM::eslot(pm_ring, st, 0, tid), pc + (eon ? s + eoff : 0), eon);
-                if (FUSED) PM::cp1(PM::eslot(pm_ring, st, 1, tid), zc + (eon ? s + eoff : 0), eon);
+                PM::cp1(PM::eslot(pm_ring, st, 0, tid), pc + (eon ? s + eoff : 0), eon && !ghost);
+                if (FUSED) PM::cp1(PM::eslot(pm_ring, st, 1, tid), zsrc + (eon ? s + eoff : 0), eon);
             }
             asm volatile("cp.async.commit_group;" ::: "memory");
         };

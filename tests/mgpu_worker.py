@@ -18,6 +18,8 @@ from opt_b200 import examples, slab, solver as S  # noqa: E402
 # flow vector (data-dependent stencil radius), the pairwise-difference energies need one row.
 CASES = {
     "poisson": (lambda: examples.poisson_synthetic(64, 96, n_iter=2, l_iter=15), 1e-5, 1),
+    # two strips (one ragged) of the marching kernel, fused with PCGStep3 in slab mode (ghost rows from the exchanged p'), LM
+    "poisson_lm": (lambda: examples.poisson_synthetic(148, 90, n_iter=2, l_iter=12), 1e-5, 1),
     "image_warping": (lambda: examples.image_warping_synthetic(48, 64, n_iter=3, l_iter=10), 1e-4, 1),
     "optical_flow_lm": (lambda: examples.optical_flow_synthetic(40, 60, n_iter=3, l_iter=12, kind="LMGPU"), 1e-4, 4),
     "volumetric": (lambda: examples.volumetric_synthetic(12, 10, 16, n_iter=2, l_iter=10), 1e-5, 1),
