@@ -104,20 +104,28 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
+        """Samples that arrived inside [t0, t1] (the timed region).  nvidia-smi needs a few hundred ms to come up, so the
+        sampler is started before the warm-up steps; if the timed region is shorter than one sampling period, the
+        samples of the warm-up steps (same load, immediately before) are reported instead and the window says so."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.12)
         self.proc.terminate()
         self.thread.join(timeout=2)
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        ok = [(t, r) for t, r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        inside = [r for t, r in ok if t0 is None or (t0 <= t <= (t1 or t) + 0.12)]
+        window = "timed region"
+        if not inside:
+            inside, window = [r for _, r in ok], "warm-up + timed region (timed region shorter than one sampling period)"
+        sm = [float(r[0]) for r in inside]
+        mx = [float(r[1]) for r in inside if r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for k, n in enumerate(names) if any(len(r) >= 6 and r[2 + k] == "Active" for r in self.rows)]
+        reasons = [n for k, n in enumerate(names) if any(r[2 + k] == "Active" for r in inside)]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "window": window}
 
 
 SLAB = {   # workloads that run domain-decomposed at N > 1 (the others run as independent replicas)
@@ -310,12 +318,13 @@ def run_ours(args, pr, w, rank, world, mode):
         return cost
 
     def timed(fn, steps, warmup, sample_clocks):
+        clk = ClockSampler(dev.index or 0) if sample_clocks else None
+        if clk:
+            clk.start()                      # before the warm-up: nvidia-smi takes a few hundred ms to deliver its first sample
         for _ in range(warmup):
             fn()
         barrier()
-        clk = ClockSampler(dev.index or 0) if sample_clocks else None
-        if clk:
-            clk.start()
+        t_begin = time.time()
         l0 = sol.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -329,7 +338,7 @@ def run_ours(args, pr, w, rank, world, mode):
             t = torch.tensor([ms], device=dev, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
-        return ms, cost, (clk.stop() if clk else None), sol.launch_count() - l0
+        return ms, cost, (clk.stop(t_begin, time.time()) if clk else None), sol.launch_count() - l0
 
     ms, cost, clocks, launches = timed(step_resident, args.steps, args.warmup, True)
     e2e_steps = max(1, args.steps)

@@ -23,7 +23,10 @@ void OptB200_FreeState(Opt_State* state);
  * halo = 1 for every shipped grid example except shape_from_shading (2).
  * Usage: rank 0 calls OptB200_GetNcclUniqueId and sends the 128 bytes to every rank (MPI,
  * torch.distributed, a file ...); then EVERY rank calls OptB200_PlanSetSlab (collective) once,
- * after Opt_ProblemPlan and before Opt_ProblemInit.  Returns 0 on success. */
+ * after Opt_ProblemPlan and before Opt_ProblemInit.  Returns 0 on success.
+ * The ranks are expected on one node: PlanSetSlab maps a mailbox (and, for energies whose fused kernel supports it, the
+ * solver-vector pool) of every peer with cudaIpc and then all-reduces the PCG scalars and pushes boundary rows by direct
+ * stores over NVLink; if the mapping fails on any rank, all ranks fall back to NCCL (OPTB200_NO_P2P=1 forces that). */
 void OptB200_GetNcclUniqueId(void* out128);
 int  OptB200_PlanSetSlab(Opt_Plan* plan, int rank, int nranks, int halo, const void* nccl_unique_id);
 

@@ -753,28 +753,31 @@ constexpr int XR_MAX_RANKS = 16, XR_MAX_VALS = 4;
 struct XSlot { double v[XR_MAX_VALS]; long long epoch; long long pad[3]; };
 struct XPeers { XSlot* p[XR_MAX_RANKS]; };
 static __global__ void k_xreduce(double* vals, int count, XPeers peers, int rank, int nranks, long long epoch, int* error_flag) {
-    if (threadIdx.x != 0) return;
+    // one warp, lane t talks to rank t: stores and polls of the N peers proceed in parallel
+    const int t = threadIdx.x;
     const int par = (int)(epoch & 1);
-    for (int t = 0; t < nranks; ++t) {
+    __shared__ double got[XR_MAX_RANKS][XR_MAX_VALS];
+    if (t < nranks) {
         volatile XSlot* dst = peers.p[t] + par * XR_MAX_RANKS + rank;
         for (int c = 0; c < count; ++c) dst->v[c] = vals[c];
-    }
-    __threadfence_system();
-    for (int t = 0; t < nranks; ++t) {
-        volatile XSlot* dst = peers.p[t] + par * XR_MAX_RANKS + rank;
+        __threadfence_system();
         dst->epoch = epoch;
-    }
-    double sum[XR_MAX_VALS] = {0.0, 0.0, 0.0, 0.0};
-    for (int t = 0; t < nranks; ++t) {
         volatile XSlot* src = peers.p[rank] + par * XR_MAX_RANKS + t;
         long long spins = 0;
+        bool dead = false;
         while (src->epoch != epoch) {
-            if (++spins > (1LL << 28)) { *error_flag = 1; return; }     // minutes: a peer died; give up instead of hanging the GPU
+            if (++spins > (1LL << 28)) { dead = true; break; }             // minutes: a peer died; give up instead of hanging the GPU
         }
         __threadfence_system();
-        for (int c = 0; c < count; ++c) sum[c] += src->v[c];
+        if (dead) *error_flag = 1;
+        for (int c = 0; c < count; ++c) got[t][c] = dead ? 0.0 : src->v[c];
     }
-    for (int c = 0; c < count; ++c) vals[c] = sum[c];
+    __syncwarp();
+    if (t < count) {                                                        // rank order: identical bits on every rank
+        double s = 0.0;
+        for (int r2 = 0; r2 < nranks; ++r2) s += got[r2][t];
+        vals[t] = s;
+    }
 }
 
 // Halo exchange of the fused slab path through peer memory: the new search direction of the owned boundary rows is
