@@ -284,65 +284,99 @@ k_poisson_march(PoissonFunctor<T> f, Vec<T> z, Vec<T> p, Vec<T> p_new, Vec<T> ou
         const T* zc = z.d + (long)c * z.plane;
         const T* nc = p_new.d + (long)c * p_new.plane;                       // FUSED, slab mode: ghost rows of p' (exchanged)
         const T* cc = CtC.d + (long)c * CtC.plane;
-        const bool has_l = lane == 0 && gx > 0, has_r = lane == 31 && gx + 4 < W;
+        T* pnew_c = p_new.d + (long)c * p_new.plane;
+        T* out_c = out.d + (long)c * out.plane;
+        const bool has_left = gx > 0, has_right = gx + 4 < W;
+        const bool has_l = lane == 0 && has_left, has_r = lane == 31 && has_right;
         const long eoff = lane == 0 ? -1 : 4;                               // pixel beyond the strip's end
-        auto flag_of = [&](int row) -> unsigned { return (col_in && row >= 0 && row < H) ? active4[((long)row * W + gx) >> 2] : 0u; };
-        // issue row `row` into its ring stage; fl = active bits of this lane's quad in that row
-        auto issue = [&](int row, unsigned fl) {
-            const int st = (row + D) % D;                                   // row >= -1
+        // Everything that moves with the row is a running offset / pointer (no per-step 64-bit multiplies, no modulo):
+        //   issue side: row ri, element offset oi = ri*W + gx, ring stage si at shared address shi
+        //   consume side: stage sc at byte offset shc of the ring; output row y = n-1 at element offset s_out
+        const int nbeg = y0 - 1, nend = y1;                                  // rows y0-1 .. y1 pass through the pipeline
+        const int flo = nbeg < 0 ? 0 : nbeg, fhi = nend < H - 1 ? nend : H - 1;   // rows whose flags exist
+        const unsigned char* fbase = active4 + (gx >> 2);
+        const long Wq = W >> 2;
+        auto flag_in = [&](int row) -> unsigned { return (col_in && row >= flo && row <= fhi) ? fbase[(long)row * Wq] : 0u; };
+        const unsigned sh_base = (unsigned)__cvta_generic_to_shared(pm_ring) + (unsigned)tid * PM::QB;
+        const unsigned sh_ebase = (unsigned)__cvta_generic_to_shared(pm_ring) + (unsigned)(PM::NA * 256 * PM::QB) + (unsigned)tid * (unsigned)sizeof(T);
+        int ri = nbeg, si = 0;
+        long oi = (long)nbeg * W + gx;
+        auto cp16a = [](unsigned dst, const void* src, bool on) {
+            const int nb = on ? 16 : 0;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nb) : "memory");
+        };
+        auto cpqa = [&](unsigned dst, const T* src, bool on) {
+#pragma unroll
+            for (int k = 0; k < PM::QB / 16; ++k) cp16a(dst + 16 * k, (const unsigned char*)src + 16 * k, on);
+        };
+        auto cp1a = [](unsigned dst, const T* src, bool on) {
+            if constexpr (sizeof(T) == 4) { const int nb = on ? 4 : 0; asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(nb) : "memory"); }
+            else                          { const int nb = on ? 8 : 0; asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst), "l"(src), "r"(nb) : "memory"); }
+        };
+        // issue the next row (ri) into ring stage si; fl = active bits of this lane's quad in that row
+        auto issue = [&](unsigned fl) {
             const bool on = fl != 0;
-            const long s = on ? (long)row * W + gx : 0;
             // rows of a neighbouring slab (slab mode, fused): the direction is the received p' itself; it goes through
             // the z slot with a zero-filled p slot, so the consumer's z + beta p yields it unchanged
-            const bool ghost = FUSED && (row < row_lo || row >= row_hi);
+            const bool ghost = FUSED && (ri < row_lo || ri >= row_hi);
+            const long o = on ? oi : 0;                                      // a zero-size copy still gets a valid address
             const T* zsrc = ghost ? nc : zc;
-            PM::cpq(PM::slot(pm_ring, st, PM::A_P, tid), pc + s, on && !ghost);
-            if (FUSED) PM::cpq(PM::slot(pm_ring, st, PM::A_Z, tid), zsrc + s, on);
-            if (LM) PM::cpq(PM::slot(pm_ring, st, PM::A_C, tid), cc + s, on);
+            const unsigned sh = sh_base + (unsigned)si * PM::STAGE;
+            cpqa(sh + PM::A_P * 256 * PM::QB, pc + o, on && !ghost);
+            if (FUSED) cpqa(sh + PM::A_Z * 256 * PM::QB, zsrc + o, on);
+            if (LM) cpqa(sh + PM::A_C * 256 * PM::QB, cc + o, on);
             if (lane == 0 || lane == 31) {
                 // the neighbour quad may be inactive (all zeros) -- loading it is still correct
                 const bool eon = on && (lane == 0 ? has_l : has_r);
-                PM::cp1(PM::eslot(pm_ring, st, 0, tid), pc + (eon ? s + eoff : 0), eon && !ghost);
-                if (FUSED) PM::cp1(PM::eslot(pm_ring, st, 1, tid), zsrc + (eon ? s + eoff : 0), eon);
+                const long eo = eon ? o + eoff : 0;
+                const unsigned she = sh_ebase + (unsigned)si * PM::STAGE;
+                cp1a(she, pc + eo, eon && !ghost);
+                if (FUSED) cp1a(she + 256 * (unsigned)sizeof(T), zsrc + eo, eon);
             }
             asm volatile("cp.async.commit_group;" ::: "memory");
+            ++ri; oi += W; si = si + 1 == D ? 0 : si + 1;
         };
-        const int nbeg = y0 - 1, nend = y1;                                  // rows y0-1 .. y1 pass through the pipeline
         // fq[k] = active bits of row n+k at the top of step n: fq[D-1] gates the issue of row n+D-1, fq[0] is consumed
         // with row n; the flag of row n+D is loaded at the top of the step and shifted in at its end
-        auto flag_in = [&](int row) -> unsigned { return row <= nend ? flag_of(row) : 0u; };
         unsigned fq[D];
 #pragma unroll
         for (int k = 0; k < D; ++k) fq[k] = flag_in(nbeg + k);
 #pragma unroll
-        for (int k = 0; k < D - 1; ++k) issue(nbeg + k, fq[k]);
+        for (int k = 0; k < D - 1; ++k) issue(fq[k]);
         T prev[4] = {T(0), T(0), T(0), T(0)}, cur[4] = {T(0), T(0), T(0), T(0)}, ccur[4] = {T(0), T(0), T(0), T(0)};
         T ecur = T(0);
         unsigned fcur = 0;
+        long s_out = (long)(nbeg - 1) * W + gx;                              // offset of output row n-1
+        int sc = 0;
+        const unsigned char* fnext_p = fbase + (long)(nbeg + D) * Wq;        // flag of row n+D
         for (int n = nbeg; n <= nend; ++n) {
-            const unsigned f_next = flag_in(n + D);
-            issue(n + D - 1, fq[D - 1]);
+            const int rn = n + D;
+            const unsigned f_next = (col_in && rn >= flo && rn <= fhi) ? *fnext_p : 0u;
+            fnext_p += Wq;
+            issue(fq[D - 1]);
             if constexpr (D == 4) asm volatile("cp.async.wait_group 3;" ::: "memory");
             else                  asm volatile("cp.async.wait_group 2;" ::: "memory");
-            // row n has landed
-            const int st = (n + D) % D;
+            // row n has landed in stage sc
+            const unsigned char* stage = pm_ring + (size_t)sc * PM::STAGE + (size_t)tid * PM::QB;
+            const unsigned char* estage = pm_ring + (size_t)sc * PM::STAGE + (size_t)(PM::NA * 256 * PM::QB) + (size_t)tid * sizeof(T);
+            sc = sc + 1 == D ? 0 : sc + 1;
             const unsigned fnew = fq[0];
             T nw[4] = {T(0), T(0), T(0), T(0)}, cnew[4] = {T(0), T(0), T(0), T(0)};
             T enew = T(0);
             {
-                T a[4]; load4(reinterpret_cast<const T*>(PM::slot(pm_ring, st, PM::A_P, tid)), a);
+                T a[4]; load4(reinterpret_cast<const T*>(stage + PM::A_P * 256 * PM::QB), a);
                 if (FUSED) {
-                    T b[4]; load4(reinterpret_cast<const T*>(PM::slot(pm_ring, st, PM::A_Z, tid)), b);
+                    T b[4]; load4(reinterpret_cast<const T*>(stage + PM::A_Z * 256 * PM::QB), b);
 #pragma unroll
                     for (int j = 0; j < 4; ++j) nw[j] = b[j] + beta * a[j];
                 } else {
 #pragma unroll
                     for (int j = 0; j < 4; ++j) nw[j] = a[j];
                 }
-                if (LM) load4(reinterpret_cast<const T*>(PM::slot(pm_ring, st, PM::A_C, tid)), cnew);
+                if (LM) load4(reinterpret_cast<const T*>(stage + PM::A_C * 256 * PM::QB), cnew);
                 if (lane == 0 || lane == 31) {
-                    const T ea = *reinterpret_cast<const T*>(PM::eslot(pm_ring, st, 0, tid));
-                    enew = FUSED ? *reinterpret_cast<const T*>(PM::eslot(pm_ring, st, 1, tid)) + beta * ea : ea;
+                    const T ea = *reinterpret_cast<const T*>(estage);
+                    enew = FUSED ? *reinterpret_cast<const T*>(estage + 256 * sizeof(T)) + beta * ea : ea;
                 }
             }
             // output row y = n-1 (cur) with prev above and nw below
@@ -353,13 +387,17 @@ k_poisson_march(PoissonFunctor<T> f, Vec<T> z, Vec<T> p, Vec<T> p_new, Vec<T> ou
             if (lane == 31) rgt = ecur;
             if (y >= y0 && y < y1 && fcur != 0) {
                 const bool up = y > 0, dn = y + 1 < H;
+                // gx is a multiple of 4: only the first pixel of a row lacks its left neighbour and only the last one its
+                // right neighbour (two item-invariant predicates instead of eight per step)
+                const T nbr[4] = {cur[1], cur[2], cur[3], rgt}, nbl[4] = {lft, cur[0], cur[1], cur[2]};
                 T o[4], pn[4];
+                T rowdot = T(0);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const T v = cur[j];
                     T a = T(0);
-                    if (gx + j + 1 < W) a += v - (j < 3 ? cur[j + 1] : rgt);      // {1,0}
-                    if (gx + j > 0) a += v - (j > 0 ? cur[j - 1] : lft);          // {-1,0}
+                    if (j < 3 || has_right) a += v - nbr[j];                      // {1,0}
+                    if (j > 0 || has_left) a += v - nbl[j];                       // {-1,0}
                     if (dn) a += v - nw[j];                                       // {0,1}
                     if (up) a += v - prev[j];                                     // {0,-1}
                     a = T(2) * a;
@@ -367,12 +405,13 @@ k_poisson_march(PoissonFunctor<T> f, Vec<T> z, Vec<T> p, Vec<T> p_new, Vec<T> ou
                     pn[j] = exj ? T(0) : v;
                     o[j] = exj ? T(0) : a;
                     if (LM) { if (!exj) o[j] += ccur[j] * pn[j]; }
-                    acc += (double)(pn[j] * o[j]);
+                    rowdot += pn[j] * o[j];
                 }
-                const long s = (long)y * W + gx;
-                if (FUSED) st4v(p_new.d + (long)c * p_new.plane + s, pn);
-                st4v(out.d + (long)c * out.plane + s, o);
+                acc += (double)rowdot;
+                if (FUSED) st4v(pnew_c + s_out, pn);
+                st4v(out_c + s_out, o);
             }
+            s_out += W;
 #pragma unroll
             for (int j = 0; j < 4; ++j) { prev[j] = cur[j]; cur[j] = nw[j]; ccur[j] = cnew[j]; }
             ecur = enew; fcur = fnew;
