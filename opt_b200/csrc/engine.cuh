@@ -551,6 +551,38 @@ __global__ void __launch_bounds__(128, sizeof(typename F::Scalar) == 4 ? 5 : 2) 
     block_accumulate(acc, den);
 }
 
+// The same gather fused with PCGStep3: the direction p' = z + beta p is formed on the fly for the vertex and for every
+// neighbour it reads (FusedDir), written once at the thread's own vertex into the other p buffer, and Ap' = J^T J p' is
+// produced in the same pass (one kernel and one pass over z, p less per PCG iteration).
+template <class F, bool LM>
+__global__ void __launch_bounds__(128, sizeof(typename F::Scalar) == 4 ? 5 : 2) k_gather_jtj_fused(F f, long N, const int* __restrict__ off, const unsigned* __restrict__ inc,
+                                                    VecOf<F> z, VecOf<F> p_old, VecOf<F> p_new, VecOf<F> out, VecOf<F> CtC,
+                                                    const double* bNum, const double* aNum, double* den, double* zero_a, double* zero_b) {
+    using T = typename F::Scalar;
+    constexpr int U = F::U;
+    double acc = 0.0;
+    FusedDir<VecOf<F>, T> dir{z, p_old, (T)(*bNum) / (T)(*aNum)};
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (zero_a) *zero_a = 0.0;
+        if (zero_b) *zero_b = 0.0;
+    }
+    for (long v = blockIdx.x * (long)blockDim.x + threadIdx.x; v < N; v += (long)gridDim.x * blockDim.x) {
+        T o[U];
+        f.gatherJTJ(v, off + v, inc, dir, o);
+        T dsum = T(0);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const T pv = dir(u, v);
+            p_new(u, v) = pv;
+            if (LM) o[u] += CtC(u, v) * pv;
+            out(u, v) = o[u];
+            dsum += pv * o[u];
+        }
+        acc += (double)dsum;
+    }
+    block_accumulate(acc, den);
+}
+
 // ------------------------------------------------------------------------------ flat streaming kernels
 // PCGStep2 (solver:665-731): alpha = aNum/aDen; delta += alpha p; r -= alpha Ap; z = M^-1 r;
 // betaNum += z.r ; LM: q += 0.5 delta.(r+b).   One 128-bit vector per thread and array.
@@ -889,7 +921,9 @@ struct Engine : OptK_Plan {
             OPTK_CUDA(cudaMalloc(&active4, Npad / 4));
             OPTK_CUDA(cudaMemsetAsync(active4, 0, Npad / 4, stream));
         }
-        if (getenv("OPTB200_NO_FUSE") || !F::FUSE_STEP3 || use_gather()) fuse = false;
+        // the gather kernel is issue-bound: forming z + beta p for every neighbour costs what the separate PCGStep3 pass costs
+        // (arap 1 M vertices: 0.0683 ms fused vs 0.0535 + 0.0148 ms; r1s), so it stays unfused unless OPTB200_GATHER_FUSED is set
+        if (getenv("OPTB200_NO_FUSE") || !F::FUSE_STEP3 || (use_gather() && !getenv("OPTB200_GATHER_FUSED"))) fuse = false;
         OPTK_CUDA(cudaMalloc(&scal, S_COUNT * sizeof(double)));
         OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
         OPTK_CUDA(cudaMallocHost(&h_scal, S_COUNT * sizeof(double)));
@@ -1274,6 +1308,15 @@ struct Engine : OptK_Plan {
                              (const T*)z.d, (const T*)p.d, p_alt.d, (long)p.plane, (int)U, rowsz, f.o_lo, f.o_hi, halo, (int)(rank > 0), (int)(rank < nranks - 1),
                              (const double*)aNum, (const double*)prevA);
                 exchange(p_alt);
+                }
+            }
+            if constexpr (F::HAS_GATHER) {
+                if (use_gather()) {
+                    const long nb = (N + 127) / 128;
+                    if (lm) this->launch_tiles("PCGStep3+1", nb, dim3(128), k_gather_jtj_fused<F, true>, f, N, (const int*)inc_off, (const unsigned*)inc, z, p, p_alt, Ap, CtC, (const double*)aNum, (const double*)prevA, aDen, bNum, S(S_Q));
+                    else    this->launch_tiles("PCGStep3+1", nb, dim3(128), k_gather_jtj_fused<F, false>, f, N, (const int*)inc_off, (const unsigned*)inc, z, p, p_alt, Ap, CtC, (const double*)aNum, (const double*)prevA, aDen, bNum, (double*)nullptr);
+                    std::swap(p.d, p_alt.d);
+                    goto applied;
                 }
             }
             if constexpr (F::HAS_FAST_APPLY) {
