@@ -303,3 +303,15 @@ def test_tiny_grids(built, name, builder, size):
     gc, gx, _, _ = run_gpu(pr)
     assert_costs_close(gc, rc, True)
     assert_unknowns_close(gx, rx, True)
+
+
+@pytest.mark.parametrize("kind", ["gaussNewtonGPU", "LMGPU"])
+def test_arap_fused_gather_equals_unfused(built, kind, monkeypatch):
+    """k_gather_jtj_fused (PCGStep3 folded into the per-vertex gather; off by default because it does not pay on B200)
+    against the default gather + separate PCGStep3."""
+    pr = make("arap", kind)
+    cu, xu, _, _ = run_gpu(pr)
+    monkeypatch.setenv("OPTB200_GATHER_FUSED", "1")           # read when the plan is made
+    cf, xf, _, _ = run_gpu(pr)
+    assert_costs_close(cf, cu, False)
+    assert_unknowns_close(xf, xu, False)
