@@ -612,7 +612,7 @@ __global__ void k_active4(F f, long ngroups, unsigned char* active4) {
 }
 
 template <class T, bool USE_PRE, bool LM>
-__global__ void __launch_bounds__(256) k_pcg_step2(long nvec, const unsigned char* __restrict__ active4, long plane,
+__global__ void __launch_bounds__(256) k_pcg_step2(long i_begin, long nvec, const unsigned char* __restrict__ active4, long plane,
                                                    T* __restrict__ delta, const T* __restrict__ p,
                                                    T* __restrict__ r, const T* __restrict__ Ap,
                                                    const T* __restrict__ pre, const T* __restrict__ b,
@@ -626,7 +626,7 @@ __global__ void __launch_bounds__(256) k_pcg_step2(long nvec, const unsigned cha
     const T alpha = (LM && stop && *stop != 0.0) ? T(0) : (T)(*aNum) / (T)(*aDen);
     if (i0 == 0 && zero_slot) *zero_slot = 0.0;
     double bacc = 0.0, qacc = 0.0;
-    for (long i = i0; i < nvec; i += istride)
+    for (long i = i_begin + i0; i < nvec; i += istride)
     if (group_active<T>(active4, i, plane)) {
         V d = reinterpret_cast<const V*>(delta)[i];
         V pv = reinterpret_cast<const V*>(p)[i];
@@ -659,7 +659,7 @@ __global__ void __launch_bounds__(256) k_pcg_step2(long nvec, const unsigned cha
 
 // PCGStep3 (solver:814-845): beta = bNum/aNum; p = z + beta p
 template <class T>
-__global__ void __launch_bounds__(256) k_pcg_step3(long nvec, const unsigned char* __restrict__ active4, long plane,
+__global__ void __launch_bounds__(256) k_pcg_step3(long i_begin, long nvec, const unsigned char* __restrict__ active4, long plane,
                                                    const T* __restrict__ z, T* __restrict__ p,
                                                    const double* bNum, const double* aNum, double* zero_slot) {
     using V = typename VecIO<T>::V;
@@ -667,7 +667,7 @@ __global__ void __launch_bounds__(256) k_pcg_step3(long nvec, const unsigned cha
     const long i0 = blockIdx.x * (long)blockDim.x + threadIdx.x, istride = (long)gridDim.x * blockDim.x;
     const T beta = (T)(*bNum) / (T)(*aNum);
     if (i0 == 0 && zero_slot) *zero_slot = 0.0;
-    for (long i = i0; i < nvec; i += istride)
+    for (long i = i_begin + i0; i < nvec; i += istride)
     if (group_active<T>(active4, i, plane)) {
         V zv = reinterpret_cast<const V*>(z)[i];
         V pv = reinterpret_cast<const V*>(p)[i];
@@ -698,14 +698,14 @@ __global__ void __launch_bounds__(256) k_boundary_dir(const T* __restrict__ z, c
 
 // PCGStep2_1stHalf (solver:738-762): delta += alpha p
 template <class T>
-__global__ void __launch_bounds__(256) k_axpy_alpha(long nvec, const unsigned char* __restrict__ active4, long plane,
+__global__ void __launch_bounds__(256) k_axpy_alpha(long i_begin, long nvec, const unsigned char* __restrict__ active4, long plane,
                                                     T* __restrict__ delta, const T* __restrict__ p,
                                                     const double* aNum, const double* aDen, const double* stop) {
     using V = typename VecIO<T>::V;
     constexpr int VW = VecIO<T>::W;
     const long i0 = blockIdx.x * (long)blockDim.x + threadIdx.x, istride = (long)gridDim.x * blockDim.x;
     const T alpha = (stop && *stop != 0.0) ? T(0) : (T)(*aNum) / (T)(*aDen);
-    for (long i = i0; i < nvec; i += istride)
+    for (long i = i_begin + i0; i < nvec; i += istride)
     if (group_active<T>(active4, i, plane)) {
         V d = reinterpret_cast<const V*>(delta)[i];
         V pv = reinterpret_cast<const V*>(p)[i];
@@ -717,7 +717,7 @@ __global__ void __launch_bounds__(256) k_axpy_alpha(long nvec, const unsigned ch
 
 // PCGStep2_2ndHalf (solver:766-799): r = b - A delta; z = M^-1 r; betaNum += z.r; q += 0.5 delta.(r+b)
 template <class T, bool USE_PRE>
-__global__ void __launch_bounds__(256) k_residual_reset(long nvec, const unsigned char* __restrict__ active4, long plane,
+__global__ void __launch_bounds__(256) k_residual_reset(long i_begin, long nvec, const unsigned char* __restrict__ active4, long plane,
                                                         const T* __restrict__ delta, T* __restrict__ r,
                                                         const T* __restrict__ Adelta, const T* __restrict__ pre,
                                                         const T* __restrict__ b, T* __restrict__ z,
@@ -727,7 +727,7 @@ __global__ void __launch_bounds__(256) k_residual_reset(long nvec, const unsigne
     const long i0 = blockIdx.x * (long)blockDim.x + threadIdx.x, istride = (long)gridDim.x * blockDim.x;
     if (i0 == 0 && zero_slot) *zero_slot = 0.0;
     double bacc = 0.0, qacc = 0.0;
-    for (long i = i0; i < nvec; i += istride)
+    for (long i = i_begin + i0; i < nvec; i += istride)
     if (group_active<T>(active4, i, plane)) {
         V d = reinterpret_cast<const V*>(delta)[i];
         V av = reinterpret_cast<const V*>(Adelta)[i];
@@ -856,6 +856,29 @@ __global__ void __launch_bounds__(256) k_boundary_push(const T* __restrict__ z, 
         const unsigned arrived = atomicAdd(done_counter, 1u);
         if (arrived == gridDim.x - 1) {
             *done_counter = 0;                               // next launch
+            halo_signal_and_wait(peers, rank, nranks, epoch, error_flag);
+        }
+    }
+}
+
+// Halo exchange of a blocked solver vector (one contiguous slice per face) through peer memory: the owned boundary
+// slices are copied straight into the neighbours' ghost slices, then the same last-block handshake as k_boundary_push.
+template <class V4>
+__global__ void __launch_bounds__(256) k_halo_push(const V4* __restrict__ src, long cnt, long src_lo, long src_hi, V4* dst_below, V4* dst_above,
+                                                   XPeers peers, int rank, int nranks, long long epoch, int* error_flag, unsigned* done_counter) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < 2 * cnt; i += (long)gridDim.x * blockDim.x) {
+        const bool upper = i >= cnt;
+        V4* dst = upper ? dst_above : dst_below;
+        if (!dst) continue;
+        const long k = upper ? i - cnt : i;
+        dst[k] = src[(upper ? src_hi : src_lo) + k];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned arrived = atomicAdd(done_counter, 1u);
+        if (arrived == gridDim.x - 1) {
+            *done_counter = 0;
             halo_signal_and_wait(peers, rank, nranks, epoch, error_flag);
         }
     }
@@ -1045,7 +1068,7 @@ struct Engine : OptK_Plan {
         cudaFree(flag);
         xr_on = all_ok == 1;
         if (!xr_on && rank == 0) fprintf(stderr, "Opt: peer-memory all-reduce unavailable, using ncclAllReduce\n");
-        if (xr_on && fuse && F::VEC_UB == 0) setup_peer_halo();
+        if (xr_on && ((fuse && F::VEC_UB == 0) || F::VEC_UB > 0)) setup_peer_halo();
     }
     // neighbours' solver-vector pools (for k_boundary_push) and where their ghost rows are
     void setup_peer_halo() {
@@ -1108,7 +1131,22 @@ struct Engine : OptK_Plan {
     }
     size_t slow_rowsz() const { return F::ND == 3 ? (size_t)f.W * f.H : (size_t)f.W; }
     void exchange(V v) {
-        if constexpr (F::VEC_UB > 0) exchange_raw(v.d, 1, 0, slow_rowsz() * U);     // blocked layout: a slow-dimension slice is contiguous
+        if constexpr (F::VEC_UB > 0) {                      // blocked layout: a slow-dimension slice is contiguous
+            const long slice = (long)slow_rowsz() * U;
+            if (xh_on && nranks > 1 && v.d >= pool && (slice * halo) % VecIO<T>::W == 0) {
+                using V4 = typename VecIO<T>::V;
+                const long per = slice / VecIO<T>::W * 1;   // vectors per slow index (slice is a multiple of the vector width: rows of 32 sites)
+                const long slot = (long)((v.d - pool) / ((long)U * Npad));
+                V4* below = rank > 0 ? (V4*)(nb_pool[0] + slot * U * nb_npad[0]) + nb_row[0] * per : nullptr;
+                V4* above = rank < nranks - 1 ? (V4*)(nb_pool[1] + slot * U * nb_npad[1]) + nb_row[1] * per : nullptr;
+                const long cnt = per * halo;
+                this->launch("HaloPushP2P", dim3((unsigned)std::min<long>((2 * cnt + 255) / 256, (long)nsm * 8)), dim3(256), k_halo_push<V4>,
+                             (const V4*)v.d, cnt, (long)f.o_lo * per, (long)(f.o_hi - halo) * per, below, above,
+                             xr_peers, rank, nranks, ++xh_epoch, xr_error, (unsigned*)(xr_error + 1));
+                return;
+            }
+            exchange_raw(v.d, 1, 0, slow_rowsz() * U);
+        }
         else exchange_raw(v.d, U, (size_t)v.plane, slow_rowsz());
     }
     void exchange_unknowns() {
@@ -1285,7 +1323,14 @@ struct Engine : OptK_Plan {
         double* nextB = S(S_RZ0 + (l + 2) % 3);
         double* aDen = S(S_ADEN0 + (l & 1));
         double* nextDen = S(S_ADEN0 + ((l + 1) & 1));
-        const long nv = flat_vecs();
+        // flat streaming range: everything, except for blocked vectors in slab mode, where a slab's owned planes are one
+        // contiguous element range and the ghost planes are left to the halo exchange alone (nothing else may write
+        // them once neighbours push into them directly)
+        long fb = 0, nv = flat_vecs();
+        if (F::VEC_UB > 0 && nranks > 1) {
+            const long per = (long)slow_rowsz() * U / VecIO<T>::W;
+            fb = f.o_lo * per; nv = f.o_hi * per;
+        }
         const unsigned char* act = active4;
         // PCGStep1 also clears q for this iteration (solver:2090)
         if (fuse && l > 0) {
@@ -1337,19 +1382,19 @@ struct Engine : OptK_Plan {
     applied:
         reduce(int(aDen - scal));
         if (lm && reset) {
-            this->launch_tiles("PCGStep2_1stHalf", (flat_vecs() + 255) / 256, dim3(256), k_axpy_alpha<T>, nv, act, Npad, delta.d, p.d, aNum, aDen, (const double*)S(S_STOP));
+            this->launch_tiles("PCGStep2_1stHalf", (flat_vecs() + 255) / 256, dim3(256), k_axpy_alpha<T>, fb, nv, act, Npad, delta.d, p.d, aNum, aDen, (const double*)S(S_STOP));
             exchange(delta);
             apply_A("computeAdelta", "computeAdelta_Graph", delta, Adelta, S(S_DUMMY), nullptr);
-            this->launch_tiles("PCGStep2_2ndHalf", (flat_vecs() + 255) / 256, dim3(256), k_residual_reset<T, F::USE_PRE>, nv, act, Npad, delta.d, r.d, Adelta.d, pre.d, b.d, z.d, bNum, S(S_Q), nextDen);
+            this->launch_tiles("PCGStep2_2ndHalf", (flat_vecs() + 255) / 256, dim3(256), k_residual_reset<T, F::USE_PRE>, fb, nv, act, Npad, delta.d, r.d, Adelta.d, pre.d, b.d, z.d, bNum, S(S_Q), nextDen);
         } else if (lm) {
-            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, true>, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)S(S_STOP));
+            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, true>, fb, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)S(S_STOP));
         } else {
-            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, false>, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)nullptr);
+            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, false>, fb, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)nullptr);
         }
         reduce(int(bNum - scal));
         if (lm) reduce(S_Q);
         if (!fuse) {
-            this->launch_tiles("PCGStep3", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step3<T>, nv, act, Npad, z.d, p.d, bNum, aNum, nextB);
+            this->launch_tiles("PCGStep3", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step3<T>, fb, nv, act, Npad, z.d, p.d, bNum, aNum, nextB);
             exchange(p);
         }
         // fused mode: PCGStep3 of this iteration happens inside the next iteration's first kernel; after
