@@ -605,19 +605,26 @@ def sqrt3_subdivide(v, faces):
     return np.concatenate([relaxed, cent], 0), adj
 
 
-def arap_golden(npz, n_iter=1, l_iter=1):
+def arap_golden(npz, n_iter=1, l_iter=1, outer_iterations=1):
     """arap_mesh_deformation on small_armadillo after one sqrt(3) subdivision: examples/arap_mesh_deformation/src/
     main.cpp:45-81 and CombinedSolver.h:23-24 (weights 4 / 1), :84-135 (angles start at 0.1, offsets = rest shape =
-    subdivided positions, marker vertices constrained, everything else -inf)."""
+    subdivided positions, marker vertices constrained, everything else -inf).  outer_iterations = 10 with (20, 100)
+    is the FIRST outer iteration of the long run (test_example_output.py:59,110,131): the markers are moved
+    alpha = 1/10 of the way from the current vertex position to their target (CombinedSolver.h:66-68, 84-101)."""
     f32 = np.float32
     P, adj = sqrt3_subdivide(npz["vertices"], npz["faces"])
     n = len(P)
+    cons = _marker_constraints(n, npz)
+    if outer_iterations != 1:
+        alpha = f32(1.0) / f32(outer_iterations)
+        idx = npz["marker_vertex"]
+        cons[idx] = (f32(1.0) - alpha) * P[idx] + alpha * cons[idx]
     v0 = np.array([a for a in range(n) for _ in adj[a]], dtype=np.int32)
     v1 = np.array([b for a in range(n) for b in sorted(adj[a])], dtype=np.int32)
     E = len(v0)
     return Problem("arap_mesh_deformation.t", [n, E],
                    [np.sqrt(f32(4.0)), np.sqrt(f32(1.0)), P.copy(), np.full((n, 3), 1e-1, dtype=f32), P.copy(),
-                    _marker_constraints(n, npz), np.array([E], dtype=np.int32), v0, v1], [2, 3],
+                    cons, np.array([E], dtype=np.int32), v0, v1], [2, 3],
                    {"nIterations": n_iter, "lIterations": l_iter})
 
 

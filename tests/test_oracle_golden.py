@@ -183,6 +183,7 @@ LONG_RUNS = {
     "shape_from_shading": ("sfs_default.npz", examples.sfs_golden, dict(n_iter=60, l_iter=10), 58.968529, 1e-2),
     "volumetric_mesh_deformation": ("volumetric_head.npz", examples.volumetric_golden, dict(n_iter=20, l_iter=60), 19.287743, 1e-6),
     "image_warping": ("image_warping_cat512.npz", examples.image_warping_golden, dict(outer_iterations=19, n_iter=8, l_iter=400), 0.078505, 1e-4),
+    "arap_mesh_deformation": ("arap_small_armadillo.npz", examples.arap_golden, dict(outer_iterations=10, n_iter=20, l_iter=100), 3.929534, 1e-5),
 }
 
 
