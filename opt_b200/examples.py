@@ -419,15 +419,28 @@ def _prewitt8(im, horizontal):
     return r
 
 
-def optical_flow_golden(npz, n_iter=1, l_iter=1):
+def gray_from_rgb(rgb):
+    """mLib baseImage.h:1461-1471 (convertToGrayscale of an 8-bit colour image), in fp32."""
+    f32 = np.float32
+    a = rgb.astype(f32)
+    return ((f32(0.299) * a[..., 0] + f32(0.587) * a[..., 1] + f32(0.114) * a[..., 2]) / f32(255.0)).astype(f32)
+
+
+def optical_flow_golden(npz, n_iter=1, l_iter=1, outer_iterations=1):
     """The FIRST solve of the reference's golden run of optical_flow (test_final_cost.py:62, stride 16, oIterations 1):
     the coarse level of the driver's 2-level pyramid (sigma = 5, CombinedSolver.h:25-37, solved first :47-66) with zero
-    flow, fit weight 10 + (50 - 10) / (1 * 2) = 30 (:69-93) and regularisation weight 0.1."""
+    flow, fit weight 10 + (50 - 10) / (oIterations * 2) (:69-93; 30 for oIterations 1) and regularisation weight 0.1.
+    The fixture holds either the strided grey images or, for the full-size long run, the 8-bit colour frames."""
     f32 = np.float32
-    S, T = _filter_gaussian(npz["source"], 5.0), _filter_gaussian(npz["target"], 5.0)
+    if "source_rgb" in npz:
+        src, tar = gray_from_rgb(npz["source_rgb"]), gray_from_rgb(npz["target_rgb"])
+    else:
+        src, tar = npz["source"], npz["target"]
+    S, T = _filter_gaussian(src, 5.0), _filter_gaussian(tar, 5.0)
     H, W = S.shape
     X = np.zeros((H, W, 2), dtype=f32)
-    return Problem("optical_flow.t", [W, H], [np.sqrt(f32(30.0)), np.sqrt(f32(0.1)), X, S, T, _prewitt8(T, True), _prewitt8(T, False)],
+    w_fit = f32(10.0) + (f32(50.0) - f32(10.0)) / f32(outer_iterations * 2)
+    return Problem("optical_flow.t", [W, H], [np.sqrt(f32(w_fit)), np.sqrt(f32(0.1)), X, S, T, _prewitt8(T, True), _prewitt8(T, False)],
                    [2], {"nIterations": n_iter, "lIterations": l_iter})
 
 

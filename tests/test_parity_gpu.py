@@ -272,12 +272,14 @@ def test_lm_device_exit_test(built, case, double, monkeypatch):
     assert_unknowns_close(gx, hx, double, tol=1e-5 if not double else 1e-11)
 
 
-@pytest.mark.parametrize("name", ["shape_from_shading", "volumetric_mesh_deformation", "image_warping", "arap_mesh_deformation"])
+@pytest.mark.parametrize("name", ["shape_from_shading", "volumetric_mesh_deformation", "image_warping", "arap_mesh_deformation",
+                                  "optical_flow", "poisson_image_editing", "intrinsic_image_decomposition"])
 def test_reference_long_run_cost(built, golden_dir, name):
     """examples/test_example_output.py: the recorded long-run costs with the reference's own tolerances (58.968529
     +- 1e-2 after GN 60x10 on the 640x480 shape-from-shading data; 19.287743 +- 1e-6 after GN 20x60; 0.078505 +- 1e-4
     after the first of 19 outer iterations of GN 8x400; 3.929534 +- 1e-5 after the first of 10 outer iterations of ARAP
-    GN 20x100)."""
+    GN 20x100; 4055.09033 +- 1e-5 after the first solve of full-size optical flow GN 1x50), and the two full-size image
+    runs whose reference tolerance is one fp32 ulp, held to 2e-6 / 5e-6 (see test_oracle_golden.LONG_RUNS)."""
     from test_oracle_golden import LONG_RUNS
     fname, builder, kw, golden, tol = LONG_RUNS[name]
     pr = builder(np.load(os.path.join(golden_dir, fname)), **kw)

@@ -159,6 +159,35 @@ def poisson():
                         unknown=np.packbits(unknown), shape=np.array([H, W]), golden_cost=np.float64(1530364.25))
 
 
+def poisson_full():
+    # The same driver at its default stride 1 (448 x 320), the setting of the long run in examples/
+    # test_example_output.py:65,116 (GN 1 x 100, recorded cost 139582.609375).  At stride 1 the twice-strided mask read
+    # described above stays inside the buffer, so the unknown-pixel mask is simply "mask image == 255".
+    a = np.array(Image.open(f"{REF}/data/poisson0.png").convert("RGBA"))
+    b = np.array(Image.open(f"{REF}/data/poisson1.png").convert("RGBA"))
+    m = np.array(Image.open(f"{REF}/data/poisson_mask.png").convert("RGBA"))[..., 0]
+    H, W = a.shape[:2]
+    assert (a[..., 3] == 255).all() and (b[..., 3] == 255).all() and set(np.unique(m)) <= {0, 255}
+    np.savez_compressed(f"{OUT}/poisson_full.npz", image=a[..., :3], target=b[..., :3], unknown=np.packbits(m == 255),
+                        shape=np.array([H, W]), golden_cost_1x100=np.float64(139582.609375))
+
+
+def intrinsic_full():
+    # stride 1 (640 x 360), the setting of the long run in examples/test_example_output.py:63,114 (GN 7 x 10, 26004924)
+    img = np.array(Image.open(f"{REF}/data/ye_high2.png"))[..., :3]
+    np.savez_compressed(f"{OUT}/intrinsic_ye_high2_full.npz", rgb=img, golden_cost_7x10=np.float64(26004924))
+
+
+def optical_flow_full():
+    # stride 1 (640 x 480): the 8-bit frames themselves; grey conversion, Gaussian pyramid and derivatives are the
+    # driver restatement's job (opt_b200/examples.py).  Long run of examples/test_example_output.py:64,115: oIterations 3,
+    # GN 1 x 50, the cost printed by the FIRST solve (coarse level, first outer iteration) = 4055.0903320312.
+    a = np.array(Image.open(f"{REF}/data/dogdance0.png"))[..., :3]
+    b = np.array(Image.open(f"{REF}/data/dogdance1.png"))[..., :3]
+    np.savez_compressed(f"{OUT}/optical_flow_dogdance_full.npz", source_rgb=a, target_rgb=b,
+                        golden_cost_first_solve=np.float64(4055.0903320312))
+
+
 def sfs():
     # examples/shape_from_shading/src/main.cpp:8,41 + SFSSolverInput.h:27-90: the four .imagedump files and the raw
     # parameter struct of the default data set (640 x 480), read with the library's own loaders
@@ -195,4 +224,7 @@ if __name__ == "__main__":
     embedded()
     arap()
     poisson()
+    poisson_full()
+    intrinsic_full()
+    optical_flow_full()
     print("wrote", sorted(os.listdir(OUT)))
