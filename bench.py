@@ -4,17 +4,27 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
 
 A "step" is one complete Opt_ProblemSolve of the workload (Init, nIterations Gauss-Newton steps of
-lIterations PCG iterations each, final cost).  Default workload at N=1 is BASELINE.json configs[1]:
-poisson_image_editing on a synthetic 4096x4096 float4 image, Gauss-Newton + PCG, fp32
-(nIterations=1, lIterations=100).  Rank 0 prints ONE JSON line.
+lIterations PCG iterations each, final cost).  The default workload is the configuration BASELINE.json's
+north_star states its targets on and the largest single-GPU configuration: volumetric_mesh_deformation on
+a synthetic 512^3 grid (configs[4]; SURVEY.md section 8d C5: GN, 60 linear iterations per nonlinear step as
+examples/volumetric_mesh_deformation/src/main.cpp:32-36), STRONG-scaled: at --gpus N the same 512^3 grid is
+cut into N slabs of planes.  The other BASELINE configurations are selected with --workload
+(tools/bench_all.sh writes one line per configuration under profiles/).  Rank 0 prints ONE JSON line.
 
   value      PCG iterations/s with every input already resident in HBM (device arrays handed to
              the C-ABI); the unknown image is restored by a device-to-device copy each step.
   e2e        same metric through the same C-ABI call sequence but starting from pinned HOST
              buffers: H2D of every image and D2H of the solved unknown inside the timed region, every
-             step; consecutive steps are double-buffered so the copies overlap the previous solve.
-  roofline   dominant kernel (PCGStep1 = J^T J p): algorithmic bytes / cudaEvent duration measured
-             live by the library's per-kernel timer, against MEASURED_PEAKS.json.
+             step; consecutive steps are double-buffered so the copies overlap the previous solve
+             (pipeline throughput; `e2e.cold_solve_ms` is one un-overlapped upload + solve + download).
+  roofline   dominant kernel (PCGStep1 = J^T J p, fused with PCGStep3 where the engine fuses them):
+             algorithmic bytes / cudaEvent duration measured live by the library's per-kernel timer,
+             against MEASURED_PEAKS.json.
+  parity     the CUDA path against the CPU oracle inside this run: the oracle solve the cpu_baseline leg
+             times is repeated on the GPU with the same iteration counts (cost and unknowns compared), and for
+             workloads whose full-size oracle solve does not fit the time budget (512^3) the operators
+             r = -J^T F, the preconditioner and J^T J p of the FULL-SIZE plan are read back on sampled plane
+             ranges and compared with the oracle evaluated on those sub-volumes.
   cpu_baseline  the CPU oracle (a port of the reference's backend_cpu/_mt path; the reference
              itself is Terra and cannot be built here) timed on this box's host cores.
 """
@@ -43,25 +53,25 @@ from opt_b200 import examples  # noqa: E402
 # all-sites figure of the SURVEY table is reported next to it as `survey_formula`.
 WORKLOADS = {
     "poisson_4096": dict(builder=examples.poisson_synthetic, args=(4096, 4096), kw=dict(n_iter=1, l_iter=100),
-                         U=4, ijtj=0, iexcl=1, extra=0, mask=2,
+                         U=4, ijtj=0, iexcl=1, extra=0, mask=2, ref_sample=(1024, 1024),
                          desc="poisson_image_editing 4096x4096 float4, GN 1x100 PCG, fp32"),
     "image_warping_512": dict(builder=examples.image_warping_synthetic, args=(512, 512), kw=dict(n_iter=8, l_iter=400),
-                              U=3, ijtj=8, iexcl=1, extra=0, mask=4,
+                              U=3, ijtj=8, iexcl=1, extra=0, mask=4, ref_sample=(128, 128),
                               desc="image_warping 512x512, GN 8x400 PCG, fp32"),
     "optical_flow_2048": dict(builder=examples.optical_flow_synthetic, args=(2048, 2048), kw=dict(n_iter=10, l_iter=50),
-                              U=2, ijtj=4, iexcl=0, extra=0, mask=None,
+                              U=2, ijtj=4, iexcl=0, extra=0, mask=None, ref_sample=(512, 512),
                               desc="optical_flow 2048x2048, GN 10x50 PCG, fp32"),
     "sfs_2048": dict(builder=examples.sfs_synthetic, args=(2048, 2048), kw=dict(n_iter=10, l_iter=10, holes=False),
-                     U=1, ijtj=5.5, iexcl=1, extra=0, mask=None,
+                     U=1, ijtj=5.5, iexcl=1, extra=0, mask=None, ref_sample=(512, 512),
                      desc="shape_from_shading 2048x2048, GN 10x10 PCG, fp32"),
     "volumetric_512": dict(builder=examples.volumetric_synthetic, args=(512, 512, 512), kw=dict(n_iter=2, l_iter=60),
-                           U=6, ijtj=9, iexcl=0, extra=0, mask=None,
+                           U=6, ijtj=9, iexcl=0, extra=0, mask=None, cpu_sample=(512, 512, 8), ref_sample=(64, 64, 16),
                            desc="volumetric_mesh_deformation 512^3, GN 2x60 PCG (the driver's 60 linear iterations per nonlinear step, main.cpp:32-36), fp32"),
     "volumetric_256": dict(builder=examples.volumetric_synthetic, args=(256, 256, 256), kw=dict(n_iter=2, l_iter=60),
-                           U=6, ijtj=9, iexcl=0, extra=0, mask=None,
+                           U=6, ijtj=9, iexcl=0, extra=0, mask=None, cpu_sample=(256, 256, 16), ref_sample=(64, 64, 16),
                            desc="volumetric_mesh_deformation 256^3, GN 2x60 PCG, fp32"),
     "arap_1m": dict(builder=examples.arap_synthetic, args=(1024, 1024), kw=dict(n_iter=2, l_iter=100),
-                    U=6, ijtj=9, iexcl=0, extra=48, mask=None,
+                    U=6, ijtj=9, iexcl=0, extra=48, mask=None, ref_sample=(192, 192),
                     desc="arap_mesh_deformation 1024x1024-vertex mesh (6.28M directed edges), GN 2x100 PCG, fp32"),
 }
 
@@ -161,29 +171,51 @@ def pcg_iterations(pr):
 
 
 # ------------------------------------------------------------------------------ CPU oracle legs
-def cpu_pcg_rate(pr, threads, budget_s=20.0):
-    """PCG iterations/s of the CPU oracle on the full-size workload.  Two bounded solves with L1 and
-    L2 PCG iterations are timed; the rate is (L2-L1)/(t2-t1), which removes the per-solve overhead
-    (cost evaluation, PCGInit1, update) that a 100-iteration solve would amortise."""
+def sample_problem(name, key, size=None):
+    """A bounded sample of the workload for the CPU legs: the same builder on `cpu_sample` / `ref_sample` dims (3-D:
+    a slab of planes from the middle of the full volume, so positions and constraints are those of the full problem).
+    Returns (problem, sites of the sample / sites of the full workload, description); no `key` entry: the full size."""
+    w = WORKLOADS[name]
+    full = tuple(size) if size else w["args"]
+    dims = w.get(key)
+    if not dims or size:
+        return w["builder"](*full, **w["kw"]), 1.0, "full-size workload"
+    if len(full) == 3 and dims[:2] == full[:2]:
+        z0 = (full[2] - dims[2]) // 2
+        pr = w["builder"](*full, planes=(z0, z0 + dims[2]), **w["kw"])
+        what = "planes [%d, %d) of the %s volume" % (z0, z0 + dims[2], "x".join(map(str, full)))
+    else:
+        pr = w["builder"](*dims, **w["kw"])
+        what = "the same builder at %s instead of %s" % ("x".join(map(str, dims)), "x".join(map(str, full)))
+    frac = float(np.prod(dims)) / float(np.prod(full))
+    return pr, frac, "%s (%.4g of the sites; rates scaled by that factor)" % (what, frac)
+
+
+def oracle_solve(pr, threads, n_iter, l_iter):
+    """One whole oracle solve; returns (seconds, cost history, solved problem copy)."""
     from oracle_api import OracleSolver
+    q = pr.clone()
+    o = OracleSolver(q.dims, q.energy, q.kind, double=q.double, threads=threads)
+    o.set_params(nIterations=int(n_iter), lIterations=int(l_iter))
+    t = time.perf_counter()
+    o.solve(q.params)
+    dt = time.perf_counter() - t
+    costs = o.cost_history()
+    o.close()
+    return dt, costs, q
 
-    def timed(l_iter):
-        q = pr.clone()
-        o = OracleSolver(q.dims, q.energy, q.kind, double=q.double, threads=threads)
-        o.set_params(nIterations=1, lIterations=l_iter)
-        t = time.perf_counter()
-        o.solve(q.params)
-        dt = time.perf_counter() - t
-        o.close()
-        return dt
 
-    t1 = timed(1)
+def cpu_pcg_rate(pr, threads, budget_s=20.0):
+    """PCG iterations/s of the CPU oracle on `pr`.  Two bounded solves with 1 and L2 PCG iterations are timed; the
+    rate is (L2-1)/(t2-t1), which removes the per-solve overhead (cost evaluation, PCGInit1, update) that a long
+    solve would amortise.  The second solve is returned so that the GPU can be checked against it."""
+    t1, _, _ = oracle_solve(pr, threads, 1, 1)
     per_iter_guess = max(t1 / 4.0, 1e-4)
     l2 = int(min(40, max(3, 1 + (budget_s - 2 * t1) / per_iter_guess)))
-    t2 = timed(l2)
+    t2, costs, solved = oracle_solve(pr, threads, 1, l2)
     rate = (l2 - 1) / max(t2 - t1, 1e-9)
-    sample = "full-size workload, 2 solves with lIterations=1 and %d (%.1fs + %.1fs); rate=(%d-1)/(t2-t1)" % (l2, t1, t2, l2)
-    return rate, sample, t1 + t2
+    sample = "2 solves with lIterations=1 and %d (%.1fs + %.1fs); rate=(%d-1)/(t2-t1)" % (l2, t1, t2, l2)
+    return rate, sample, l2, costs, solved
 
 
 def host_threads():
@@ -193,29 +225,64 @@ def host_threads():
         return os.cpu_count() or 1
 
 
-def run_reference(args, pr, w):
-    """--impl reference: the reference's CPU solver path on the host cores.  The reference is
-    Lua/Terra and cannot be built in this image, so this is the oracle port (kind "port")."""
+def parallelism(world, mode):
+    if world == 1:
+        return "1 GPU"
+    if not mode:
+        return "%d ranks, independent replicas" % world
+    return ("%d ranks, slab decomposition along the slowest dimension (%s scaling): boundary planes of the search direction "
+            "and the PCG scalars move by direct stores into peer memory over NVLink (NCCL for set-up and the "
+            "once-per-nonlinear-step unknown exchange)" % (world, mode))
+
+
+def config_of(args, w, world):
+    """Identical for both arms (the driver compares them): the workload, not the implementation."""
+    dims = [int(d) for d in (args.size or w["args"])]
+    kind = args.kind or w["kw"].get("kind", "gaussNewtonGPU")
+    mode = SLAB.get(args.workload) if world > 1 else None
+    return {"workload": w["desc"], "dims": dims, "solver": kind, "precision": "f64" if args.double else "f32",
+            "nIterations": int(w["kw"]["n_iter"]), "lIterations": int(w["kw"]["l_iter"]),
+            "pcg_iterations_nominal": int(w["kw"]["n_iter"]) * int(w["kw"]["l_iter"]),
+            "l2": "inputs larger than L2 (each solver vector is %.0f MB)" % (w["U"] * float(np.prod(dims)) * (8 if args.double else 4) / 1e6),
+            "parallelism": parallelism(world, mode)}
+
+
+def run_reference(args, w):
+    """--impl reference: the reference's CPU solver path on the host cores.  The reference is Lua/Terra and cannot be
+    built in this image, so this is the oracle port (kind "port").  Every step is one WHOLE solve (the workload's
+    nIterations x lIterations) of a bounded sample of the workload, timed by the host clock; `value` is the sample's
+    PCG iterations/s scaled by (sample sites / workload sites), i.e. the rate of full-size iterations at the measured
+    per-site cost ("sampled": true)."""
     threads = host_threads()
-    rates, samples = [], []
-    for _ in range(args.warmup):
-        pass                                            # nothing to warm on the CPU path
-    t0 = time.perf_counter()
+    pr, frac, what = sample_problem(args.workload, "ref_sample", args.size)
+    if args.kind:
+        pr.kind = args.kind
+    if args.double:
+        pr = pr.as_double()
+    n_iter, l_iter = int(pr.solver["nIterations"]), int(pr.solver["lIterations"])
+    for _ in range(min(1, args.warmup)):
+        oracle_solve(pr, threads, 1, 2)                 # page in the library, spin up the OpenMP team
+    times = []
     for _ in range(max(1, args.steps)):
-        rate, sample, _ = cpu_pcg_rate(pr, threads, budget_s=max(4.0, 40.0 / max(1, args.steps)))
-        rates.append(rate)
-        samples.append(sample)
-    wall = time.perf_counter() - t0
-    rate = float(np.median(rates))
+        dt, costs, _ = oracle_solve(pr, threads, n_iter, l_iter)
+        times.append(dt)
+    total = float(np.sum(times))
+    iters = n_iter * l_iter
+    rate_sample = iters * len(times) / total
+    rate = rate_sample * frac
     line = {
         "impl": "reference", "metric": "pcg_iterations_per_second", "value": rate, "unit": "PCG iters/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": 1000.0 * pcg_iterations(pr) / rate, "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": 1000.0 * total / len(times), "higher_is_better": True,
+        "scaling": "strong" if SLAB.get(args.workload) == "strong" else "weak",
         "vs_baseline": None, "dtype": "f64" if pr.double else "f32", "data": "synthetic",
-        "config": {"workload": w["desc"], "dims": pr.dims, "solver": pr.kind, "timing": "host wall clock", "wall_s": wall},
-        "cpu_baseline": {"value": rate, "unit": "PCG iters/s", "cores": threads, "kind": "port", "sample": samples[0]},
+        "config": config_of(args, w, args.gpus), "sampled": frac != 1.0,
+        "cpu_baseline": {"value": rate, "unit": "PCG iters/s", "cores": threads, "kind": "port",
+                         "sample": "%s; every step is one whole GN %dx%d solve of the sample (%.2f s each), value = sample "
+                                   "iterations/s x %.4g" % (what, n_iter, l_iter, total / len(times), frac),
+                         "sample_rate": rate_sample, "sample_dims": [int(d) for d in pr.dims], "final_cost_of_sample": costs[-1] if costs else None},
         "e2e": {"value": rate, "unit": "PCG iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "timing": "host wall clock around each whole solve",
     }
     print(json.dumps(line))
 
@@ -343,6 +410,7 @@ def run_ours(args, pr, w, rank, world, mode):
     ms, cost, clocks, launches = timed(step_resident, args.steps, args.warmup, True)
     e2e_steps = max(1, args.steps)
     run_e2e(1)
+    ms_cold, _, _, _ = timed(lambda: run_e2e(1), 1, 0, False)          # one upload + solve + download, nothing overlapped
     ms_e2e, cost_e2e, _, _ = timed(lambda: run_e2e(e2e_steps), 1, 0, False)
     h2d = sum(host[i].numel() * host[i].element_size() for i in img_idx)
     d2h = sum(out_host[i].numel() * out_host[i].element_size() for i in pr.unknowns) + 8
@@ -410,30 +478,127 @@ def run_ours(args, pr, w, rank, world, mode):
     value = mult * iters * args.steps / (ms * 1e-3)
     if rank != 0:
         return
-    cpu = None
+    cpu, parity = None, None
     if not args.no_cpu and world == 1:
         threads = host_threads()
-        rate, sample, _ = cpu_pcg_rate(pr, threads, budget_s=args.cpu_budget)
-        cpu = {"value": rate, "unit": "PCG iters/s", "cores": threads, "kind": "port", "sample": sample}
+        spr, frac, what = sample_problem(args.workload, "cpu_sample", args.size)
+        spr.kind = pr.kind
+        if pr.double:
+            spr = spr.as_double()
+        rate, sample, l2, ocosts, solved = cpu_pcg_rate(spr, threads, budget_s=args.cpu_budget)
+        cpu = {"value": rate * frac, "unit": "PCG iters/s", "cores": threads, "kind": "port",
+               "sample": "%s; %s" % (what, sample), "sample_rate": rate, "sample_dims": [int(d) for d in spr.dims]}
+        parity = solve_parity(S, spr, l2, ocosts, solved)
+        parity["problem"] = what
+        if frac != 1.0 and len(pr.dims) == 3:
+            parity["full_size_operators"] = operator_parity_3d(S, sol, named, pr, devt, pristine, threads)
+            parity["ok"] = bool(parity["ok"] and parity["full_size_operators"]["ok"])
+    it_ms = ms / args.steps / iters
+    kern_ms = None
+    if roof:
+        km = roof["kernel_ms"]
+        kern_ms = sum(v for k, v in km.items() if v and k in ("PCGStep1", "PCGStep3+1", "PCGStep1_Graph", "PCGStep2", "PCGStep3")
+                      and not (k == "PCGStep1" and km.get("PCGStep3+1")))
     line = {
         "metric": "pcg_iterations_per_second", "value": value, "unit": "PCG iters/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "strong" if mode == "strong" else "weak", "vs_baseline": None,
+        "scaling": "strong" if mode == "strong" or (world == 1 and SLAB.get(args.workload) == "strong") else "weak", "vs_baseline": None,
         "dtype": "f32" if not pr.double else "f64", "data": "synthetic",
-        "config": {"workload": w["desc"], "dims": pr.dims, "solver": pr.kind, "pcg_iterations_per_step": iters,
-                   "l2": "inputs larger than L2 (each solver vector is %.0f MB)" % (w["U"] * sol.site_count() * sz_of(pr) / 1e6),
-                   "pcg_iterations_nominal": pcg_iterations(pr), "final_cost": cost, "parallelism": "1 GPU" if world == 1 else ("%d ranks, %s" % (world, (
-                       "slab decomposition along the slowest dim (%s scaling), NCCL halo exchange + all-reduced PCG scalars" % mode)
-                       if mode else "independent replicas"))},
+        "config": config_of(args, w, world),
+        "pcg_iterations_per_step": iters, "final_cost": cost,
+        "iteration_ms": {"total": it_ms, "kernels": kern_ms, "overhead": (it_ms - kern_ms) if kern_ms else None,
+                         "note": "total = timed region / PCG iterations; kernels = live cudaEvent time of the per-iteration kernels "
+                                 "(J^T J apply + PCGStep2 [+ PCGStep3]); overhead = launch gaps, per-nonlinear-step kernels and, at N > 1, "
+                                 "the cross-GPU handshakes"},
         "clocks": clocks,
         "e2e": {"value": mult * iters * e2e_steps / (ms_e2e * 1e-3),
                 "unit": "PCG iters/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": ms_e2e / e2e_steps, "final_cost": cost_e2e},
+                "ms_per_step": ms_e2e / e2e_steps, "final_cost": cost_e2e, "cold_solve_ms": ms_cold,
+                "note": "pipeline throughput: step k+1's upload and step k-1's download overlap step k's solve; cold_solve_ms is one "
+                        "un-overlapped upload + solve + download"},
         "gpu_launches": launches,
         "roofline": roof,
+        "parity": parity,
         "cpu_baseline": cpu,
     }
     print(json.dumps(line))
+
+
+PARITY_GATES = {False: {"cost": 1e-4, "unknowns": 2e-4, "operator": 2e-5}, True: {"cost": 1e-9, "unknowns": 1e-8, "operator": 1e-11}}
+
+
+def solve_parity(S, spr, l_iter, ocosts, solved):
+    """The oracle solve `solved` (nIterations=1, lIterations=l_iter on `spr`) repeated through the C ABI on the GPU."""
+    import torch
+    named = S.upload(spr)
+    sol = S.OptSolver(spr.dims, spr.energy, spr.kind, double=spr.double)
+    gcosts = []
+    sol.solve({"nIterations": 1, "lIterations": int(l_iter)}, named, gcosts)
+    torch.cuda.synchronize()
+    gate = PARITY_GATES[bool(spr.double)]
+    ok = len(gcosts) == len(ocosts)
+    rel_cost = max([abs(a - b) / max(abs(b), 1e-300) for a, b in zip(gcosts, ocosts)] or [float("inf")])
+    rel_x = 0.0
+    for i in spr.unknowns:
+        ref = solved.params[i].reshape(-1).astype(np.float64)
+        got = named.values[i].cpu().numpy().reshape(-1).astype(np.float64)
+        fin = np.isfinite(ref)
+        rel_x = max(rel_x, float(np.abs(got[fin] - ref[fin]).max() / (np.abs(ref[fin]).max() + 1e-30)))
+    sol.close()
+    ok = bool(ok and np.isfinite(rel_cost) and rel_cost <= gate["cost"] and rel_x <= gate["unknowns"])
+    return {"iters": int(l_iter), "rel_err_cost": float(rel_cost), "max_rel_err_unknowns": float(rel_x),
+            "costs_gpu": gcosts, "costs_oracle": list(ocosts), "gate": gate, "ok": ok}
+
+
+def operator_parity_3d(S, sol, named, pr, devt, pristine, threads, planes=6):
+    """FULL-SIZE check of a 3-D workload whose oracle solve does not fit the time budget: the full-size plan runs one PCG
+    iteration from the initial unknowns; p0 = M^-1 (-J^T F), M^-1 and Ap = J^T J p0 are read back on three ranges of
+    `planes` planes (bottom, middle, top of the volume) and compared with the oracle evaluated on those sub-volumes
+    (r, the preconditioner and J^T J p are local: radius-1 stencils, so a plane that has both its z-neighbours inside
+    the sub-volume -- or lies on the boundary of the full grid -- is exact)."""
+    from oracle_api import OracleSolver
+    import torch
+    W, H, D = [int(d) for d in pr.dims]
+    plane = W * H
+    for i in pr.unknowns:
+        devt[i].copy_(pristine[i])
+    saved = dict(pr.solver)
+    sol.set_solver_parameters({"nIterations": 1, "lIterations": 1})
+    sol.init(named)
+    while sol.step():
+        pass
+    torch.cuda.synchronize()
+    sol.set_solver_parameters(saved)
+    gate = PARITY_GATES[bool(pr.double)]["operator"]
+    dt = np.float64 if pr.double else np.float32
+    out = {"planes": [], "max_rel_err_p0": 0.0, "max_rel_err_pre": 0.0, "max_rel_err_JTJp": 0.0, "gate": gate,
+           "what": "p0 = M^-1(-J^T F), M^-1 and J^T J p0 of the full-size plan vs the oracle on sub-volumes"}
+    for za in sorted({0, max(0, D // 2 - planes // 2), max(0, D - planes)}):
+        zb = min(D, za + planes)
+        n = (zb - za) * plane
+        p0 = sol.debug_read_range("p", za * plane, n)
+        pre = sol.debug_read_range("pre", za * plane, n)
+        ap = sol.debug_read_range("Ap", za * plane, n)
+        sub = [np.ascontiguousarray(q.reshape(D * plane, -1)[za * plane:zb * plane]) if isinstance(q, np.ndarray) else q for q in pr.params]
+        o = OracleSolver([W, H, zb - za], pr.energy, pr.kind, double=pr.double, threads=threads)
+        r_ref, pre_ref = o.eval_jtf(sub, dt)
+        ap_ref = o.apply_jtj(sub, np.ascontiguousarray(p0.reshape(-1)))
+        o.close()
+        U = p0.shape[1]
+        r_ref, pre_ref, ap_ref = r_ref.reshape(-1, U), pre_ref.reshape(-1, U), ap_ref.reshape(-1, U)
+        lo = 0 if za == 0 else 1                       # first / last plane of the sub-volume miss a z-neighbour unless
+        hi = (zb - za) if zb == D else (zb - za - 1)    # they are the boundary of the full grid
+        sl = slice(lo * plane, hi * plane)
+        p0_ref = (pre_ref * r_ref).astype(dt)
+        e_p = float(np.abs(p0[sl] - p0_ref[sl]).max() / np.abs(p0_ref[sl]).max())
+        e_m = float(np.abs(pre[sl] - pre_ref[sl]).max() / np.abs(pre_ref[sl]).max())
+        e_a = float(np.abs(ap[sl] - ap_ref[sl]).max() / np.abs(ap_ref[sl]).max())
+        out["planes"].append({"range": [za + lo, za + hi], "rel_err_p0": e_p, "rel_err_pre": e_m, "rel_err_JTJp": e_a})
+        out["max_rel_err_p0"] = max(out["max_rel_err_p0"], e_p)
+        out["max_rel_err_pre"] = max(out["max_rel_err_pre"], e_m)
+        out["max_rel_err_JTJp"] = max(out["max_rel_err_JTJp"], e_a)
+    out["ok"] = bool(max(out["max_rel_err_p0"], out["max_rel_err_pre"], out["max_rel_err_JTJp"]) <= gate)
+    return out
 
 
 def main():
@@ -442,7 +607,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="poisson_4096", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="volumetric_512", choices=sorted(WORKLOADS))
     ap.add_argument("--size", type=int, nargs="+", default=None, help="override the workload's grid size")
     ap.add_argument("--double", action="store_true", help="run the workload in fp64 (doublePrecision = 1)")
     ap.add_argument("--kind", default=None, choices=["gaussNewtonGPU", "LMGPU"], help="override the workload's solver kind")
@@ -459,8 +624,7 @@ def main():
 
     if args.impl == "reference":
         if rank == 0:
-            pr, w, _ = make_problem(args.workload, args.size)
-            run_reference(args, variant(pr), w)
+            run_reference(args, WORKLOADS[args.workload])
         return
     pr, w, mode = make_problem(args.workload, args.size, rank, world)
     pr = variant(pr)

@@ -56,6 +56,8 @@ long OptB200_PlanSiteCount(Opt_Plan* plan);         /* N */
 /* Test hooks.  `name` is one of "delta","r","p","Ap","z","pre","CtC","b","prevX"; the vector is
  * written to host memory as AoS [site][U] of opt_float.  Returns 0 on success. */
 int  OptB200_DebugReadVector(Opt_Plan* plan, const char* name, void* host_out);
+/* The same for the sites [first_site, first_site + nsites) only: full-size checks (512^3) read a few planes. */
+int  OptB200_DebugReadVectorRange(Opt_Plan* plan, const char* name, long first_site, long nsites, void* host_out);
 /* host_out = J^T J host_p at the current unknowns (host AoS [site][U]); runs the PCGStep1 kernel(s). */
 void OptB200_DebugApplyJTJ(Opt_Plan* plan, void** problemparams, const void* host_p, void* host_out);
 /* Runs PCGInit1 (+graph/finish, +LM diagonal) at the current unknowns so that r = -J^T F, pre, p can be read back. */

@@ -15,6 +15,7 @@
 #include <string>
 #include <vector>
 #include <nccl.h>
+#include <nvtx3/nvToolsExt.h>      // header-only; ranges are no-ops unless a profiler injects itself
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_select.cuh>
 #include "common.cuh"
@@ -51,6 +52,7 @@ struct OptK_Plan {
     virtual int unknown_channels() const = 0;
     virtual long site_count() const = 0;
     virtual int debug_read(const char* name, void* host_out) = 0;
+    virtual int debug_read_range(const char* name, long first_site, long nsites, void* host_out) = 0;
     virtual void debug_apply_jtj(const void* host_p, void* host_out) = 0;
     virtual int set_slab(int rank, int nranks, int halo, const void* nccl_unique_id) = 0;
 
@@ -153,7 +155,27 @@ struct OptK_Plan {
         kernel<<<grid, block, smem, stream>>>(args...);
         post_launch();
     }
-    void print_timing() {                                    // backend_cuda.t:262-297
+    // The reference brackets a whole solve with an event pair called "overall" (solver:1813, 1906): started at Init,
+    // appended to the event list when the solve is cleaned up, so it is the last row of the table.
+    Timed overall_{nullptr, nullptr, nullptr};
+    void overall_begin() {
+        if (!timing) return;
+        if (overall_.a) { cudaEventDestroy(overall_.a); cudaEventDestroy(overall_.b); }
+        overall_.name = "overall";
+        OPTK_CUDA(cudaEventCreate(&overall_.a)); OPTK_CUDA(cudaEventCreate(&overall_.b));
+        OPTK_CUDA(cudaEventRecord(overall_.a, stream));
+    }
+    void overall_end() {
+        if (!timing || !overall_.a) return;
+        OPTK_CUDA(cudaEventRecord(overall_.b, stream));
+        timed.push_back(overall_);
+        overall_ = Timed{nullptr, nullptr, nullptr};
+    }
+    // Timer:evaluate (backend_cuda.t:231-297): the kernel table, the `TIMING` line (totals of the kernels whose name starts
+    // with PCGInit1 / PCGStep1 / overall, in table order) and `Per-iter times ms (nonlinear,linear)` with the reference's own
+    // aggregation rule: the summed totals of all kernels launched as often as PCGInit1, and as often as PCGStep1
+    // (examples/outParse.py reads these two lines).
+    void print_timing() {
         if (!timing || timed.empty()) return;
         OPTK_CUDA(cudaStreamSynchronize(stream));
         std::map<std::string, std::pair<int, double>> agg;
@@ -163,12 +185,30 @@ struct OptK_Plan {
             if (!agg.count(t.name)) order.push_back(t.name);
             agg[t.name].first++; agg[t.name].second += ms;
         }
+        auto prefix = [](const char* pre, const std::string& s) { return s.compare(0, strlen(pre), pre) == 0; };
         printf("--------------------------------------------------------\n");
         printf("        Kernel        |   Count  |   Total   | Average \n");
         printf("----------------------+----------+-----------+----------\n");
-        for (auto& n : order)
+        for (auto& n : order) {
+            printf("----------------------+----------+-----------+----------\n");
             printf(" %-20s |   %4d   | %8.3fms| %7.4fms\n", n.c_str(), agg[n].first, agg[n].second, agg[n].second / agg[n].first);
+        }
         printf("--------------------------------------------------------\n");
+        printf("TIMING ");
+        for (auto& n : order)
+            if (prefix("PCGInit1", n) || prefix("PCGStep1", n) || prefix("overall", n)) printf("%f ", agg[n].second);
+        printf("\n");
+        int linIters = 0, nonLinIters = 0;
+        for (auto& n : order) {
+            if (prefix("PCGInit1", n)) linIters = agg[n].first;
+            if (prefix("PCGStep1", n)) nonLinIters = agg[n].first;
+        }
+        float linAggregate = 0.f, nonLinAggregate = 0.f;
+        for (auto& n : order) {
+            if (agg[n].first == linIters) linAggregate += (float)agg[n].second;
+            if (agg[n].first == nonLinIters) nonLinAggregate += (float)agg[n].second;
+        }
+        printf("Per-iter times ms (nonlinear,linear): %7.4f\t%7.4f\n", linAggregate, nonLinAggregate);
     }
 };
 
@@ -595,8 +635,11 @@ __device__ __forceinline__ bool group_active(const unsigned char* active4, long 
     const long e = (i * VecIO<T>::W) % plane;
     return active4[e >> 2] != 0;
 }
+// `changed` is raised when the Exclude mask differs from the one the previous PCGInit1 saw (a caller that re-uses a plan with
+// another mask image): sites that were unknowns and are excluded now still hold their old delta / r / p / z / Ap, which the
+// streaming kernels, the stencils and the U = 1 flat updates assume to be 0 -- k_zero_if then clears the solver vectors.
 template <class F>
-__global__ void k_active4(F f, long ngroups, unsigned char* active4) {
+__global__ void k_active4(F f, long ngroups, unsigned char* active4, int* changed) {
     const long g = blockIdx.x * (long)blockDim.x + threadIdx.x;
     if (g >= ngroups) return;
     const long N = (long)f.W * f.H * f.D;
@@ -608,7 +651,13 @@ __global__ void k_active4(F f, long ngroups, unsigned char* active4) {
             if (!f.exclude(x, y, z, s)) a |= (unsigned char)(1u << j);     // one bit per site of the group
         }
     }
-    active4[g] = a;
+    if (active4[g] != a) { active4[g] = a; *changed = 1; }
+}
+template <class V4>
+__global__ void __launch_bounds__(256) k_zero_if(const int* __restrict__ flag, V4* __restrict__ v, long n) {
+    if (*flag == 0) return;
+    V4 zero{};
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) v[i] = zero;
 }
 
 template <class T, bool USE_PRE, bool LM>
@@ -884,6 +933,42 @@ __global__ void __launch_bounds__(256) k_halo_push(const V4* __restrict__ src, l
     }
 }
 
+// Fused slab path of a blocked solver vector: the new search direction p' = z + beta p of the two owned boundary slices
+// (the PCGStep3 of those planes, ahead of the fused PCGStep3+1 kernel) is stored straight into the neighbours' ghost
+// slices of THEIR p' buffer; the fused kernel then stages ghost planes from p' (volumetric_packed.cuh).  `local_out`
+// (NCCL fallback): p' goes into this rank's own p' buffer and is exchanged with send/recv afterwards.
+template <class T>
+__global__ void __launch_bounds__(256) k_halo_push_dir(const typename VecIO<T>::V* __restrict__ z, const typename VecIO<T>::V* __restrict__ p,
+                                                       typename VecIO<T>::V* local_out, long cnt, long src_lo, long src_hi, int has_lo, int has_hi,
+                                                       typename VecIO<T>::V* dst_below, typename VecIO<T>::V* dst_above,
+                                                       const double* bNum, const double* aNum,
+                                                       XPeers peers, int rank, int nranks, long long epoch, int* error_flag, unsigned* done_counter, int handshake) {
+    using V4 = typename VecIO<T>::V;
+    const T beta = (T)(*bNum) / (T)(*aNum);
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < 2 * cnt; i += (long)gridDim.x * blockDim.x) {
+        const bool upper = i >= cnt;
+        if (upper ? !has_hi : !has_lo) continue;
+        const long k = upper ? i - cnt : i;
+        const long e = (upper ? src_hi : src_lo) + k;
+        V4 zv = z[e], pv = p[e];
+#pragma unroll
+        for (int c = 0; c < VecIO<T>::W; ++c) comp(zv, c) = fma(beta, comp(pv, c), comp(zv, c));   // the fused kernel's rounding
+        if (local_out) local_out[e] = zv;
+        V4* dst = upper ? dst_above : dst_below;
+        if (dst) dst[k] = zv;
+    }
+    if (!handshake) return;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned arrived = atomicAdd(done_counter, 1u);
+        if (arrived == gridDim.x - 1) {
+            *done_counter = 0;
+            halo_signal_and_wait(peers, rank, nranks, epoch, error_flag);
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------ the engine
 template <class F>
 struct Engine : OptK_Plan {
@@ -899,6 +984,7 @@ struct Engine : OptK_Plan {
     V delta, r, b, Adelta, z, p, Ap, CtC, pre, SSq, prevX;
     V p_alt;                                           // second p buffer of the fused Step3+Step1 kernel
     unsigned char* active4 = nullptr;                       // 1 flag per 4 sites (HAS_EXCLUDE functors only)
+    int* mask_changed = nullptr;                            // raised by k_active4 when the Exclude mask is not the previous one
     unsigned* inc = nullptr;                                // HAS_GATHER: incidence payloads sorted by (vertex, slot)
     int* inc_off = nullptr;                                 //             N*GV + 1 segment offsets
     void* sort_tmp = nullptr; size_t sort_tmp_bytes = 0;
@@ -943,6 +1029,7 @@ struct Engine : OptK_Plan {
         if (F::HAS_EXCLUDE) {
             OPTK_CUDA(cudaMalloc(&active4, Npad / 4));
             OPTK_CUDA(cudaMemsetAsync(active4, 0, Npad / 4, stream));
+            OPTK_CUDA(cudaMalloc(&mask_changed, sizeof(int)));
         }
         // the gather kernel is issue-bound: forming z + beta p for every neighbour costs what the separate PCGStep3 pass costs
         // (arap 1 M vertices: 0.0683 ms fused vs 0.0535 + 0.0148 ms; r1s), so it stays unfused unless OPTB200_GATHER_FUSED is set
@@ -970,7 +1057,7 @@ struct Engine : OptK_Plan {
         for (void* q : xr_opened) cudaIpcCloseMemHandle(q);
         cudaFree(xr_buf); cudaFree(xr_error);
         if (comm) ncclCommDestroy(comm);
-        cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFreeHost(lm_box); cudaFree(active4);
+        cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFreeHost(lm_box); cudaFree(active4); cudaFree(mask_changed);
         cudaFree(inc); cudaFree(inc_off); cudaFree(inc_count); cudaFree(sort_tmp); cudaFree(key_a); cudaFree(key_b); cudaFree(val_a);
         base_destroy();
     }
@@ -991,7 +1078,7 @@ struct Engine : OptK_Plan {
         rank = rk; nranks = nr; halo = h;
         // ghost rows of p are refreshed after PCGStep3; the fused PCGStep3+1 kernel stays on only for functors whose
         // kernel takes its ghost rows from the exchanged p' (FUSE_SLAB, see k_boundary_dir)
-        if (nranks > 1 && !(F::FUSE_SLAB && F::VEC_UB == 0 && f.fuse_slab_ok())) fuse = false;
+        if (nranks > 1 && !(F::FUSE_SLAB && f.fuse_slab_ok())) fuse = false;
         f.o_lo = rank > 0 ? halo : 0;
         f.o_hi = rank < nranks - 1 ? L - halo : L;
         if (f.o_hi - f.o_lo < halo) { fprintf(stderr, "Opt: slab thinner than its halo\n"); return -1; }
@@ -1256,7 +1343,14 @@ struct Engine : OptK_Plan {
     // active4 (one bit per site of a group of 4) and, for functors whose J^T J kernel walks a work list, that list
     void active_groups() {
         if (!F::HAS_EXCLUDE) return;
-        this->launch("activeGroups", dim3((unsigned)((Npad / 4 + 255) / 256)), dim3(256), k_active4<F>, f, Npad / 4, active4);
+        OPTK_CUDA(cudaMemsetAsync(mask_changed, 0, sizeof(int), stream));
+        this->launch("activeGroups", dim3((unsigned)((Npad / 4 + 255) / 256)), dim3(256), k_active4<F>, f, Npad / 4, active4, mask_changed);
+        {   // delta r z p Ap pre prevX p_alt are the first eight vectors of the pool; all but pre / prevX must be 0 at excluded sites
+            using V4 = typename VecIO<T>::V;
+            const long per = flat_vecs();
+            this->launch("clearAfterMaskChange", flat_grid(), dim3(256), k_zero_if<V4>, (const int*)mask_changed, (V4*)pool, 5 * per);
+            this->launch("clearAfterMaskChange", flat_grid(), dim3(256), k_zero_if<V4>, (const int*)mask_changed, (V4*)(pool + (size_t)7 * U * Npad), per);   // slot 7: whichever of p / p_alt lives there
+        }
         if constexpr (F::HAS_ACTIVE_ITEMS) {
             if (f.fast_ok()) {
                 this->pre_launch("activeItems");
@@ -1318,6 +1412,7 @@ struct Engine : OptK_Plan {
     }
 
     void pcg_iter(int l, int reset) override {
+        struct Range { Range() { nvtxRangePushA("PCG iteration"); } ~Range() { nvtxRangePop(); } } nvtx_range;
         double* aNum = S(S_RZ0 + l % 3);
         double* bNum = S(S_RZ0 + (l + 1) % 3);
         double* nextB = S(S_RZ0 + (l + 2) % 3);
@@ -1336,6 +1431,21 @@ struct Engine : OptK_Plan {
         if (fuse && l > 0) {
             // p' = z + beta p with beta = RZ[l%3] / RZ[(l-1)%3] (the PCGStep3 of iteration l-1), then Ap'
             double* prevA = S(S_RZ0 + (l + 2) % 3);
+            if constexpr (F::VEC_UB > 0) {
+                if (nranks > 1) {                           // blocked vectors: a boundary plane is one contiguous slice
+                    using V4 = typename VecIO<T>::V;
+                    const long per = (long)slow_rowsz() * U / VecIO<T>::W, cnt = per * halo;
+                    const long slot = (long)((p_alt.d - pool) / ((long)U * Npad));
+                    V4 *below = nullptr, *above = nullptr;
+                    if (xh_on && rank > 0) below = (V4*)(nb_pool[0] + slot * U * nb_npad[0]) + nb_row[0] * per;
+                    if (xh_on && rank < nranks - 1) above = (V4*)(nb_pool[1] + slot * U * nb_npad[1]) + nb_row[1] * per;
+                    this->launch("PCGStep3_BoundaryPush", dim3((unsigned)std::min<long>((2 * cnt + 255) / 256, (long)nsm * 4)), dim3(256), k_halo_push_dir<T>,
+                                 (const V4*)z.d, (const V4*)p.d, xh_on ? (V4*)nullptr : (V4*)p_alt.d, cnt, (long)f.o_lo * per, (long)(f.o_hi - halo) * per,
+                                 (int)(rank > 0), (int)(rank < nranks - 1), below, above, (const double*)aNum, (const double*)prevA,
+                                 xr_peers, rank, nranks, xh_on ? ++xh_epoch : 0LL, xr_error, (unsigned*)(xr_error + 1), (int)xh_on);
+                    if (!xh_on) exchange(p_alt);
+                }
+            } else
             if (nranks > 1) {                               // only reached with F::FUSE_SLAB
                 const long rowsz = (long)slow_rowsz();
                 const long total = rowsz * halo * 2 * U;
@@ -1485,17 +1595,36 @@ struct Engine : OptK_Plan {
         for (long s = 0; s < N; ++s) for (int u = 0; u < U; ++u) o[s * U + u] = tmp[(size_t)V::host_index(u, s, Npad)];
         return 0;
     }
+    int debug_read_range(const char* name, long s0, long n, void* host_out) override {
+        V* v = vec_by_name(name);
+        if (!v || !v->d || s0 < 0 || n < 0 || s0 + n > N) return -1;
+        OPTK_CUDA(cudaStreamSynchronize(stream));
+        T* o = (T*)host_out;
+        if (F::VEC_UB == 0) {
+            std::vector<T> tmp((size_t)n);
+            for (int u = 0; u < U; ++u) {
+                OPTK_CUDA(cudaMemcpy(tmp.data(), v->d + (size_t)u * Npad + s0, (size_t)n * sizeof(T), cudaMemcpyDeviceToHost));
+                for (long s = 0; s < n; ++s) o[s * U + u] = tmp[(size_t)s];
+            }
+        } else {
+            const long b0 = s0 >> 5, b1 = (s0 + n + 31) >> 5;
+            std::vector<T> tmp((size_t)(b1 - b0) * 32 * U);
+            OPTK_CUDA(cudaMemcpy(tmp.data(), v->d + (size_t)b0 * 32 * U, tmp.size() * sizeof(T), cudaMemcpyDeviceToHost));
+            for (long s = s0; s < s0 + n; ++s) for (int u = 0; u < U; ++u) o[(s - s0) * U + u] = tmp[(size_t)(((s >> 5) - b0) * 32 * U + u * 32 + (s & 31))];
+        }
+        return 0;
+    }
     void debug_apply_jtj(const void* host_p, void* host_out) override {
         std::vector<T> tmp((size_t)U * Npad, T(0));
         const T* hp = (const T*)host_p;
         for (long s = 0; s < N; ++s) for (int u = 0; u < U; ++u) tmp[(size_t)V::host_index(u, s, Npad)] = hp[s * U + u];
         // on the plan's stream: a pageable cudaMemcpy on the legacy stream may still be in flight when the kernels
         // below start on the (non-blocking) plan stream
+        active_groups();                                    // first: a changed Exclude mask clears the solver vectors
         OPTK_CUDA(cudaMemcpyAsync(p.d, tmp.data(), tmp.size() * sizeof(T), cudaMemcpyHostToDevice, stream));
         OPTK_CUDA(cudaMemsetAsync(Ap.d, 0, tmp.size() * sizeof(T), stream));
         bool saved = lm; lm = false;
         if (use_gather()) build_incidence();
-        active_groups();
         apply_A("PCGStep1", "PCGStep1_Graph", p, Ap, S(S_DUMMY), nullptr);
         lm = saved;
         debug_read("Ap", host_out);

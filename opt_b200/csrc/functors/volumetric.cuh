@@ -17,9 +17,13 @@ struct VolumetricFunctor : FunctorDefaults<T> {
     using Scalar = T;
     static constexpr int U = 6, ND = 3;
     static constexpr bool USE_PRE = true;
-    // the generic lazy p' = z + beta p accessor doubles the 42 stencil loads of this functor and the kernel
-    // is issue-bound, not DRAM-bound (measured: fused 2.28 ms vs 1.44 + 0.17 ms at 256^3)
-    static constexpr bool FUSE_STEP3 = false;
+    // SoA / scalar engine: the generic lazy p' = z + beta p accessor doubles the 42 stencil loads of this functor and the
+    // kernel is issue-bound, not DRAM-bound (measured: fused 2.28 ms vs 1.44 + 0.17 ms at 256^3), so PCGStep3 stays a
+    // separate pass there.  Blocked / packed engine: z is staged next to p and p' is formed in registers
+    // (volumetric_packed.cuh), in slab mode with the ghost planes taken from the pushed p' (engine.cuh k_halo_push_dir).
+    static constexpr bool FUSE_STEP3 = UB > 0;
+    static constexpr bool FUSE_SLAB = UB > 0;
+    bool fuse_slab_ok() const { return UB > 0 && fast_ok(); }
     static constexpr int VEC_UB = UB;                          // blocked layout (common.cuh, Vec) for the packed kernel's bulk copies
     int W, H, D;
     T* O; T* A; const T* Ur; const T* Cn;

@@ -8,18 +8,25 @@
 //     y0+1) with FFMA2 / FADD2 / FMUL2 (sm_100 `fma.rn.f32x2`): one instruction does the work of two.  ptxas folds
 //     negation, half swaps and scalar broadcasts into the operand modifiers, so building "the other row"
 //     operands costs nothing;
-//   * the inputs of a plane (table: 10 planes, direction p: 6 planes; 18 rows each, i.e. a 30 x 16 tile plus one
-//     halo row above and below) are brought into shared memory by the bulk-copy engine (`cp.async.bulk`, the
-//     descriptor-less TMA path: tensor-map loads raise "illegal instruction" on this pool's boxes, even NVIDIA's own
-//     sample, tools/probe/) into a ring of NS stages guarded by full/empty mbarriers.  Both arrays are laid out so
-//     that a stage is ~20 contiguous chunks: the table is tile-ordered [ty][plane][32 lanes] (a whole 8-row record
-//     is one 10 KB copy) and the solver vectors of this functor use the blocked layout [site/32][channel][site%32]
-//     (common.cuh Vec, VEC_UB), in which the six channels of a 64-site row window are one 1536-byte copy.  The warps
-//     take turns issuing a stage, one copy per lane.  Every read of the march is then an LDS at (one base
-//     register) + (compile-time offset) and every store an STG at pointer + immediate: no address arithmetic, no
-//     predicates, and the loads run three planes ahead of the math without holding registers.  Rows / blocks
-//     outside the grid are simply not copied: the ring is zero-filled once and only ever holds finite data, and
-//     every edge that leaves the grid is masked;
+//   * the inputs of a plane (table: 10 planes; direction: 6 channels of p and, in the fused kernel, of z; 18 rows
+//     each, i.e. a 30 x 16 tile plus one halo row above and below) are brought into shared memory asynchronously
+//     into a ring of NS stages guarded by full/empty mbarriers.  The table is tile-ordered [ty][plane][32 lanes]
+//     (a whole 8-row record is one 10 KB chunk) and travels by the bulk-copy engine (`cp.async.bulk`, <= 4 copies
+//     per stage).  The solver vectors use the blocked layout [site/32][channel][site%32] (common.cuh Vec, VEC_UB):
+//     the 32-site window of a tile row starts at x = 30 bx - 1 and straddles two blocks, so it is fetched by
+//     per-lane 4-byte `cp.async` (one coalesced 128-byte request per channel and row, zero-filled outside the grid)
+//     whose completion is tied to the stage's `full` barrier (`cp.async.mbarrier.arrive.noinc`).  (r1: the window was
+//     over-fetched as two whole blocks per row by the bulk engine, 1536 B per row and array; staging z next to p for
+//     the fused kernel would not have fitted into 227 KB that way.)  The warps take turns issuing a stage.  Every
+//     read of the march is then an LDS at (one base register) + (compile-time offset) and every store an STG at
+//     pointer + immediate: no address arithmetic, no predicates, and the loads run three planes ahead of the math
+//     without holding registers.  Rows outside the grid are simply not copied: the ring is zero-filled once and
+//     only ever holds finite data, and every edge that leaves the grid is masked;
+//   * FUSED: PCGStep3 of the previous iteration is folded in (solver:814-845 + 607-632): z is staged next to p, the
+//     new search direction p' = z + beta p is formed in registers wherever the stencil reads it (own rows, the two
+//     halo rows, the plane above) and written once at the thread's own sites into the other p buffer.  In slab mode
+//     the ghost planes hold the neighbours' p' already (pushed before this kernel, engine.cuh k_halo_push_dir):
+//     they are staged from p_new into the z slot and combined with beta = 0;
 //   * the y edge between the two rows of a thread is internal (its J p in both directions comes out of the two
 //     packed y edges); only the rows above and below the pair are recomputed from the table: ONE packed
 //     recompute per two sites instead of two scalar ones per site;
@@ -111,6 +118,15 @@ __device__ __forceinline__ void copy(void* dst, const void* src, unsigned bytes,
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+// per-thread 4-byte asynchronous copy (LDGSTS); src_bytes = 0 zero-fills the destination instead
+__device__ __forceinline__ void copy4(void* dst, const void* src, unsigned src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
+}
+// the barrier receives one arrival from this thread once all its earlier cp.async have landed (no pending-count
+// increment: the barrier's arrival count must include it)
+__device__ __forceinline__ void arrive_on_copies(unsigned long long* bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 }  // namespace bulk
 
 struct VolRing {
@@ -119,8 +135,10 @@ struct VolRing {
     static constexpr int NWARPS = 8, TILEY = 2 * NWARPS; // a warp owns two rows: 30 x 16 tiles
     static constexpr int BOXR = TILEY + 2;               // rows per stage: the tile + one halo row on each side
     static constexpr int TROW = 10 * 32;                 // table: floats per stage row, [plane][32 lanes]
-    static constexpr int DROW = 2 * 6 * 32;              // direction: floats per stage row, two 32-site blocks [channel][32]
-    static constexpr int TABF = BOXR * TROW, DIRF = BOXR * DROW, STAGEF = TABF + DIRF;
+    // direction (p and z): the 18 stage rows are stored as 10 row PAIRS [(r + 1) / 2][channel][32 lanes][(r + 1) % 2], so
+    // that the two rows a thread owns (stage rows 1 + 2 wy, 2 + 2 wy) are one 64-bit shared-memory load per channel
+    static constexpr int DPAIR = 6 * 64, NPAIR = BOXR / 2 + 1;
+    static constexpr int TABF = BOXR * TROW, DIRF = NPAIR * DPAIR, STAGEF = TABF + 2 * DIRF;   // table, p, z
     static constexpr size_t SMEM = (size_t)NS * STAGEF * 4 + 2 * NS * 8 + 128;
 };
 
@@ -131,7 +149,7 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
                           double* zero_a, double* zero_b) {
     using F = VolumetricFunctor<float, 6>;
     using G = VolRing;
-    constexpr int TX = F::FTX, TY = G::TILEY, ZC = F::ZC, NS = G::NS, PL = 32;     // PL: plane / channel stride inside a stage row
+    constexpr int TX = F::FTX, TY = G::TILEY, ZC = F::ZC, NS = G::NS, PL = 32, DL = 64;     // PL / DL: plane / channel stride inside a table row / a direction row pair
     const int W = f.W, H = f.H, D = f.D;
     const long sz = (long)W * H;
     const int zlo = f.z_lo(), zhi = f.z_hi();
@@ -140,6 +158,8 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
     const int lane = threadIdx.x, wy = threadIdx.y, ty0 = 2 * wy, tid = linear_tid();
     const f2 wr2 = bc2(f.w_reg * f.w_reg), wf2 = bc2(f.w_fit * f.w_fit);
     const long orow = 6L * W, oplane = 6L * sz;           // blocked layout: floats from a site to the one a row / a plane further
+    // FUSED: beta of the PCGStep3 folded in here (engine.cuh FusedDir: the same float division as k_pcg_step3)
+    const float beta = FUSED ? (float)(*bNum) / (float)(*aNum) : 0.f;
 
     extern __shared__ __align__(1024) float ring[];
     unsigned long long* full = reinterpret_cast<unsigned long long*>(ring + NS * G::STAGEF);
@@ -147,7 +167,7 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
     for (int i = tid; i < NS * G::STAGEF; i += 256) ring[i] = 0.f;
     if (tid == 0) {
 #pragma unroll
-        for (int i = 0; i < NS; ++i) { bulk::mbar_init(full + i, 1); bulk::mbar_init(empty + i, G::NWARPS); }
+        for (int i = 0; i < NS; ++i) { bulk::mbar_init(full + i, 1 + 32); bulk::mbar_init(empty + i, G::NWARPS); }   // full: expect_tx + the 32 lanes' copies
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         if (blockIdx.x == 0) {
             if (zero_a) *zero_a = 0.0;
@@ -176,24 +196,37 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
         const long rec_y = (long)ntx * F::REC;
         const float* rec = f.tab + ((long)(pr_z * nrec_y + 2 * by) * ntx + bx) * F::REC;
         const bool t0 = by > 0, t2 = 2 * by + 1 < nrec_y, t3 = 2 * by + 2 < nrec_y;
-        // direction: the two 32-site blocks around x0 = 30 bx - 1 of every grid row of the stage
-        const int xb0 = (bx * TX - 1 + 32) / 32 - 1, nxb = W / 32;
-        const bool b0 = xb0 >= 0, b1 = xb0 + 1 < nxb;
+        if (lane == 0) {
+            bulk::mbar_expect_tx(full + st, 10240u + (t0 ? 1280u : 0u) + (t2 ? 10240u : 0u) + (t3 ? 1280u : 0u));
+            bulk::copy(tabs + G::TROW, rec, 10240, full + st);
+        } else if (lane == 1) { if (t2) bulk::copy(tabs + 9 * G::TROW, rec + rec_y, 10240, full + st); }
+        else if (lane == 2) { if (t0) bulk::copy(tabs, rec - rec_y + 7 * F::RWS, 1280, full + st); }
+        else if (lane == 3) { if (t3) bulk::copy(tabs + 17 * G::TROW, rec + 2 * rec_y, 1280, full + st); }
+        // direction: lane = position in the 32-site window that starts at x = 30 bx - 1; one 4-byte copy per lane,
+        // channel and row (a coalesced 128-byte request that straddles two 32-site blocks), zero-filled outside the
+        // grid in x.  Fused: p into the p slot and z into the z slot; a ghost plane of a slab (its p' was pushed by
+        // the neighbour before this kernel) goes from p_new into the z slot and is combined with beta = 0.
+        const int xw = bx * TX - 1 + lane;
+        const unsigned okx = xw >= 0 && xw < W ? 4u : 0u;
+        const long lane_off = okx ? (long)(xw >> 5) * 192 + (xw & 31) : 0;
         const int ya = by * TY - 1;                                         // grid row of stage row 0
         const int r_lo = ya < 0 ? 1 : 0, r_hi = ya + G::BOXR <= H ? G::BOXR : H - ya;   // stage rows [r_lo, r_hi) exist
-        const unsigned rowb = ((b0 ? 1u : 0u) + (b1 ? 1u : 0u)) * 768u;
-        if (lane == 0)
-            bulk::mbar_expect_tx(full + st, 10240u + (t0 ? 1280u : 0u) + (t2 ? 10240u : 0u) + (t3 ? 1280u : 0u) + (unsigned)(r_hi - r_lo) * rowb);
-        if (lane < G::BOXR) {
-            const int r = lane;
-            if (r >= r_lo && r < r_hi) {
-                const long blk = (((long)pr_z * H + (ya + r)) * W >> 5) + (b0 ? xb0 : xb0 + 1);
-                bulk::copy(dirs + r * G::DROW + (b0 ? 0 : 192), p.d + blk * 192, rowb, full + st);
+        const bool ghost = FUSED && (pr_z < zlo || pr_z >= zhi);
+        const long row0 = ((long)pr_z * H + (ya + r_lo)) * orow + lane_off;
+        const float* sa = (ghost ? p_new.d : p.d) + row0;                   // -> p slot (z slot for a ghost plane)
+        const float* sb = zv.d + row0;                                      // -> z slot
+        float* da = dirs + (ghost ? G::DIRF : 0) + 2 * lane;
+        for (int r = r_lo; r < r_hi; ++r) {
+            float* d = da + ((r + 1) >> 1) * G::DPAIR + ((r + 1) & 1);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) bulk::copy4(d + k * 64, sa + k * 32, okx);
+            if (FUSED && !ghost) {
+#pragma unroll
+                for (int k = 0; k < 6; ++k) bulk::copy4(d + G::DIRF + k * 64, sb + k * 32, okx);
             }
-        } else if (lane == G::BOXR) { bulk::copy(tabs + G::TROW, rec, 10240, full + st); }
-        else if (lane == G::BOXR + 1) { if (t2) bulk::copy(tabs + 9 * G::TROW, rec + rec_y, 10240, full + st); }
-        else if (lane == G::BOXR + 2) { if (t0) bulk::copy(tabs, rec - rec_y + 7 * F::RWS, 1280, full + st); }
-        else if (lane == G::BOXR + 3) { if (t3) bulk::copy(tabs + 17 * G::TROW, rec + 2 * rec_y, 1280, full + st); }
+            sa += orow; sb += orow;
+        }
+        bulk::arrive_on_copies(full + st);
     };
     auto produce_one = [&]() {
         if (pr_unit >= nunits) return;
@@ -220,14 +253,14 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
         const bool eup = in1 && y1 + 1 < H, edn = in0 && y0 > 0;
         const f2 m_yp = mk2(in1 ? 1.f : 0.f, eup ? 1.f : 0.f), m_ym = mk2(edn ? 1.f : 0.f, in1 ? 1.f : 0.f);
         const f2 m_ext = mk2(edn ? 1.f : 0.f, eup ? 1.f : 0.f);
-        // a thread's rows of a stage: table at tb[k PL], tb[k PL + TROW]; direction at db[k PL], db[k PL + DROW]
+        // a thread's rows of a stage: table at tb[k PL], tb[k PL + TROW]; direction pair (64-bit) at db[k DL], z slot DIRF further
         const int toff = (1 + ty0) * G::TROW + lane;
-        const int dpos = ((bx * TX - 1) & 31) + lane;                      // position inside the 64-site window
-        const int doff = G::TABF + (1 + ty0) * G::DROW + (dpos >> 5) * 192 + (dpos & 31);
+        const int doff = G::TABF + (wy + 1) * G::DPAIR + 2 * lane;         // the thread's row pair; channel k at + 64 k
         // out (and CtC) in the blocked layout: channel k of this thread's row-0 site at os[k * 32], row 1 at os[k * 32 + orow]
         const long s0 = x + (long)W * y0 + sz * z0;
         float* os = out.d + ((s0 >> 5) * 192 + (s0 & 31));
         const float* cs = CtC.d + ((s0 >> 5) * 192 + (s0 & 31));
+        float* ns = p_new.d + ((s0 >> 5) * 192 + (s0 & 31));            // FUSED: where this thread's p' goes
         bool havePrev = z0 > 0, writePrev = false;
 
         auto acquire = [&](int z) -> const float* {                       // stage base of plane z, once its copies have landed
@@ -242,7 +275,23 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
             produce_one();
         };
         auto tpair = [&](const float* q) { return mk2(q[0], q[G::TROW]); };
-        auto dpair = [&](const float* q) { return mk2(q[0], q[G::DROW]); };
+        // direction of the thread's two rows: p, or p' = z + beta p (b2 = 0 for a ghost plane, whose z slot holds p')
+        auto ld2 = [](const float* q) { f2 r; r.v = *reinterpret_cast<const float2*>(q); return r; };
+        auto dpair = [&](const float* q, f2 b2) {
+            if (FUSED) return fma2(b2, ld2(q), ld2(q + G::DIRF));
+            return ld2(q);
+        };
+        // ... of the stage rows below / above the pair (lo = below: second row of the pair below, hi = above: first
+        // row of the pair above; loaded as whole pairs, which keeps the accesses free of bank conflicts)
+        auto dext = [&](const float* q, f2 b2) {
+            const f2 lo = ld2(q - G::DPAIR), hi = ld2(q + G::DPAIR);
+            if (FUSED) {
+                const f2 zlo = ld2(q - G::DPAIR + G::DIRF), zhi = ld2(q + G::DPAIR + G::DIRF);
+                return fma2(b2, mk2(lo.v.y, hi.v.x), mk2(zlo.v.y, zhi.v.x));
+            }
+            return mk2(lo.v.y, hi.v.x);
+        };
+        auto plane_beta = [&](int z) { return bc2(z >= zlo && z < zhi ? beta : 0.f); };
 
         // Ap_O of a completed plane; `back` = 1 for the plane below the current one
         auto write_O = [&](const VolCarry& c, const f2* acc, int back) {
@@ -271,11 +320,19 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
             const float* __restrict__ tb = stg + toff;
             const float* __restrict__ db = stg + doff;
             f2 tr[6], pA[3];
+            const f2 bz = plane_beta(z);
 #pragma unroll
             for (int k = 0; k < 6; ++k) tr[k] = tpair(tb + k * PL);
 #pragma unroll
-            for (int k = 0; k < 3; ++k) { C.uc[k] = tpair(tb + (6 + k) * PL); C.pO[k] = dpair(db + k * PL); pA[k] = dpair(db + (3 + k) * PL); }
+            for (int k = 0; k < 3; ++k) { C.uc[k] = tpair(tb + (6 + k) * PL); C.pO[k] = dpair(db + k * DL, bz); pA[k] = dpair(db + (3 + k) * DL, bz); }
             C.fit = tpair(tb + 9 * PL);
+            if (FUSED && !last) {                                      // PCGStep3's store: p' once, at the thread's own sites
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    if (w0) { ns[k * 32] = C.pO[k].v.x; ns[(3 + k) * 32] = pA[k].v.x; }
+                    if (w1) { ns[k * 32 + orow] = C.pO[k].v.y; ns[(3 + k) * 32 + orow] = pA[k].v.y; }
+                }
+            }
             RotM2 rm; rm.set(tr);
             f2 M[3][3]; rm.combine(pA[0], pA[1], pA[2], M);
             f2 S[3][3];
@@ -322,13 +379,13 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
             // ---- y: the edge between the two rows is internal; the rows above / below are recomputed ------
             {
                 const float* __restrict__ tu = tb + 2 * G::TROW; const float* __restrict__ td = tb - G::TROW;   // stage rows above / below the pair
-                const float* __restrict__ pu = db + 2 * G::DROW; const float* __restrict__ pd = db - G::DROW;
                 f2 unp[3], pnp[3], unm[3], pnm[3], tn[6], pan[3];
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
-                    unp[k] = mk2(C.uc[k].v.y, tu[(6 + k) * PL]); pnp[k] = mk2(C.pO[k].v.y, pu[k * PL]);
-                    unm[k] = mk2(td[(6 + k) * PL], C.uc[k].v.x); pnm[k] = mk2(pd[k * PL], C.pO[k].v.x);
-                    pan[k] = mk2(pd[(3 + k) * PL], pu[(3 + k) * PL]);
+                    const f2 pe = dext(db + k * DL, bz);                         // (row below, row above)
+                    unp[k] = mk2(C.uc[k].v.y, tu[(6 + k) * PL]); pnp[k] = mk2(C.pO[k].v.y, pe.v.y);
+                    unm[k] = mk2(td[(6 + k) * PL], C.uc[k].v.x); pnm[k] = mk2(pe.v.x, C.pO[k].v.x);
+                    pan[k] = dext(db + (3 + k) * DL, bz);
                 }
 #pragma unroll
                 for (int k = 0; k < 6; ++k) tn[k] = mk2(td[k * PL], tu[k * PL]);
@@ -352,9 +409,10 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
             for (int k = 0; k < 3; ++k) C.jn[k] = bc2(0.f);
             if (z + 1 < D) {
                 const float* __restrict__ nx = acquire(z + 1);
+                const f2 bn = plane_beta(z + 1);
                 f2 un[3], pn[3], u[3], q[3];
 #pragma unroll
-                for (int k = 0; k < 3; ++k) { un[k] = tpair(nx + toff + (6 + k) * PL); pn[k] = dpair(nx + doff + k * PL); }
+                for (int k = 0; k < 3; ++k) { un[k] = tpair(nx + toff + (6 + k) * PL); pn[k] = dpair(nx + doff + k * DL, bn); }
                 edge(un, pn, u, q, C.jn, false, bc2(1.f));
             }
             // ---- the angle block of this plane is complete ------------------------------------------
@@ -374,7 +432,7 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
             }
             release(z);
             havePrev = true; writePrev = true;
-            os += oplane; cs += oplane;
+            os += oplane; cs += oplane; ns += oplane;
             return true;
         };
 
@@ -387,16 +445,17 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
 #pragma unroll
             for (int k = 0; k < 6; ++k) tr[k] = tpair(tb + k * PL);
             RotM2 rn; rn.set(tr);
-            f2 Mn[3][3]; rn.combine(dpair(db + 3 * PL), dpair(db + 4 * PL), dpair(db + 5 * PL), Mn);
+            const f2 bb = plane_beta(z0 - 1), ba = plane_beta(z0);
+            f2 Mn[3][3]; rn.combine(dpair(db + 3 * DL, bb), dpair(db + 4 * DL, bb), dpair(db + 5 * DL, bb), Mn);
             f2 u[3];
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
-                B.uc[k] = tpair(tb + (6 + k) * PL); B.pO[k] = dpair(db + k * PL);
+                B.uc[k] = tpair(tb + (6 + k) * PL); B.pO[k] = dpair(db + k * DL, bb);
                 u[k] = B.uc[k] - tpair(sa + toff + (6 + k) * PL);
             }
 #pragma unroll
             for (int k = 0; k < 3; ++k)
-                B.jn[k] = nfma2(Mn[k][0], u[0], nfma2(Mn[k][1], u[1], nfma2(Mn[k][2], u[2], B.pO[k] - dpair(sa + doff + k * PL))));
+                B.jn[k] = nfma2(Mn[k][0], u[0], nfma2(Mn[k][1], u[1], nfma2(Mn[k][2], u[2], B.pO[k] - dpair(sa + doff + k * DL, ba))));
             release(z0 - 1);
         }
         for (int z = z0;; z += 2) {                                   // roles alternate: no register shuffling

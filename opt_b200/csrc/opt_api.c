@@ -169,7 +169,9 @@ void Opt_SetSolverParameter(Opt_State* state, Opt_Plan* plan, const char* name, 
 void Opt_ProblemInit(Opt_State* state, Opt_Plan* plan, void** problemparams) {
     (void)state;
     OptK_Plan* k = plan->k;
+    optk_range_push("Opt_ProblemInit");
     optk_begin_call(k);
+    optk_overall_begin(k);
     optk_bind(k, problemparams);
     plan->sp.nIter = 0;
     plan->finished_reported = 0;
@@ -185,15 +187,24 @@ void Opt_ProblemInit(Opt_State* state, Opt_Plan* plan, void** problemparams) {
     /* the reference launches one more PCGInit1 here whose results the first Step overwrites
        (solver:1886); it has no observable effect and is not replayed */
     optk_end_call(k);
+    optk_range_pop();
 }
 
 static void cleanup(Opt_Plan* plan) { /* solver:1902-1910 */
     logSolver(plan, "final cost=%.16f\n", plan->prevCost);
+    optk_overall_end(plan->k);
     if (plan->timing && plan->verbosity > 0) optk_print_timing(plan->k);
 }
 
+static int problem_step(Opt_Plan* plan, void** problemparams);
 int Opt_ProblemStep(Opt_State* state, Opt_Plan* plan, void** problemparams) {
     (void)state;
+    optk_range_push("Opt_ProblemStep");
+    const int more = problem_step(plan, problemparams);
+    optk_range_pop();
+    return more;
+}
+static int problem_step(Opt_Plan* plan, void** problemparams) {
     OptK_Plan* k = plan->k;
     SolverParameters* sp = &plan->sp;
     optk_begin_call(k);
@@ -314,6 +325,9 @@ int OptB200_PlanUnknownChannels(Opt_Plan* plan) { return optk_unknown_channels(p
 long OptB200_PlanSiteCount(Opt_Plan* plan) { return optk_site_count(plan->k); }
 int OptB200_DebugReadVector(Opt_Plan* plan, const char* name, void* host_out) {
     return optk_debug_read(plan->k, name, host_out);
+}
+int OptB200_DebugReadVectorRange(Opt_Plan* plan, const char* name, long first_site, long nsites, void* host_out) {
+    return optk_debug_read_range(plan->k, name, first_site, nsites, host_out);
 }
 void OptB200_DebugApplyJTJ(Opt_Plan* plan, void** problemparams, const void* host_p, void* host_out) {
     optk_begin_call(plan->k);

@@ -24,6 +24,10 @@ void  optk_bind(OptK_Plan*, void** problemparams);
 /* LM parameters that the reference injects as problem parameters (o.t:1575-1580) */
 void  optk_set_lm(OptK_Plan*, double trust_region_radius, double min_lm_diagonal, double max_lm_diagonal);
 
+void   optk_range_push(const char* name);     /* NVTX range (no-op without a profiler) */
+void   optk_range_pop(void);
+void   optk_overall_begin(OptK_Plan*);        /* the reference's "overall" timer event (solver:1813): started at Init ... */
+void   optk_overall_end(OptK_Plan*);          /* ... and closed when the solve is cleaned up (solver:1906) */
 void   optk_begin_call(OptK_Plan*);           /* order the plan's stream after the caller's default stream */
 void   optk_end_call(OptK_Plan*);             /* ... and the default stream after the plan's stream */
 
@@ -57,6 +61,7 @@ int    optk_unknown_channels(OptK_Plan*);
 long   optk_site_count(OptK_Plan*);
 /* copies an internal solver vector ("delta","r","p","Ap","z","pre","CtC") to the host as AoS [site][U] of opt_float */
 int    optk_debug_read(OptK_Plan*, const char* name, void* host_out);
+int    optk_debug_read_range(OptK_Plan*, const char* name, long first_site, long nsites, void* host_out);
 /* out = J^T J p for a host AoS [site][U] direction (test hook; runs PCGStep1 on it) */
 void   optk_debug_apply_jtj(OptK_Plan*, const void* host_p, void* host_out);
 

@@ -55,6 +55,10 @@ OptK_Plan* optk_create(const char* energy, int is_double, int is_lm, const unsig
 void optk_destroy(OptK_Plan* p) { delete p; }
 void optk_bind(OptK_Plan* p, void** pp) { p->bind(pp); }
 void optk_set_lm(OptK_Plan* p, double r, double mn, double mx) { p->set_lm(r, mn, mx); }
+void optk_range_push(const char* name) { nvtxRangePushA(name); }
+void optk_range_pop(void) { nvtxRangePop(); }
+void optk_overall_begin(OptK_Plan* p) { p->overall_begin(); }
+void optk_overall_end(OptK_Plan* p) { p->overall_end(); }
 void optk_begin_call(OptK_Plan* p) { p->begin_call(); }
 void optk_end_call(OptK_Plan* p) { p->end_call(); }
 void optk_precompute(OptK_Plan* p) { p->precompute(); }
@@ -82,6 +86,7 @@ void optk_reset_timing(OptK_Plan* p) { p->reset_timing(); }
 int optk_unknown_channels(OptK_Plan* p) { return p->unknown_channels(); }
 long optk_site_count(OptK_Plan* p) { return p->site_count(); }
 int optk_debug_read(OptK_Plan* p, const char* name, void* out) { return p->debug_read(name, out); }
+int optk_debug_read_range(OptK_Plan* p, const char* name, long s0, long n, void* out) { return p->debug_read_range(name, s0, n, out); }
 void optk_debug_apply_jtj(OptK_Plan* p, const void* hp, void* out) { p->debug_apply_jtj(hp, out); }
 
 }  // extern "C"

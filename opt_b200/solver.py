@@ -53,6 +53,8 @@ def load_library():
         _lib.OptB200_PlanSiteCount.argtypes = [P]
         _lib.OptB200_DebugReadVector.restype = C.c_int
         _lib.OptB200_DebugReadVector.argtypes = [P, C.c_char_p, P]
+        _lib.OptB200_DebugReadVectorRange.restype = C.c_int
+        _lib.OptB200_DebugReadVectorRange.argtypes = [P, C.c_char_p, C.c_long, C.c_long, P]
         _lib.OptB200_DebugApplyJTJ.argtypes = [P, C.POINTER(P), P, P]
         _lib.OptB200_DebugPcgBegin.argtypes = [P, C.POINTER(P)]
     return _lib, _fn
@@ -184,6 +186,14 @@ class OptSolver:
     def debug_read(self, name):
         out = np.zeros(self.site_count() * self.unknown_channels(), dtype=self._dtype())
         rc = self.lib.OptB200_DebugReadVector(self.plan, name.encode(), out.ctypes.data)
+        if rc != 0:
+            raise KeyError(name)
+        return out
+
+    def debug_read_range(self, name, first_site, nsites):
+        """Sites [first_site, first_site + nsites) of a solver vector as [nsites, U] (full-size parity checks)."""
+        out = np.zeros((nsites, self.unknown_channels()), dtype=self._dtype())
+        rc = self.lib.OptB200_DebugReadVectorRange(self.plan, name.encode(), first_site, nsites, out.ctypes.data)
         if rc != 0:
             raise KeyError(name)
         return out
