@@ -83,6 +83,13 @@ def build(verbose=False, oracle=True):
                 raise RuntimeError("driver build failed: %s\n%s" % (" ".join(cmd), r.stderr))
     if oracle:
         subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
+        # test infrastructure that is compiled from the reference's own sources where they lie (container only; the
+        # binaries travel to the GPU box): the reference's driver layer / poisson example against this library, and the
+        # reference's CPU driver code as the oracle of driver_ops.cu
+        if os.path.isdir("/root/reference/examples/shared"):
+            for d in ("tests/ref_driver", "oracle/ref_src"):
+                if os.path.exists(os.path.join(ROOT, d, "Makefile")):
+                    subprocess.check_call(["make", "-s", "-j8", "-C", os.path.join(ROOT, d)])
     return LIB
 
 

@@ -118,9 +118,9 @@ __device__ __forceinline__ void copy(void* dst, const void* src, unsigned bytes,
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
-// per-thread 4-byte asynchronous copy (LDGSTS); src_bytes = 0 zero-fills the destination instead
-__device__ __forceinline__ void copy4(void* dst, const void* src, unsigned src_bytes) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
+// per-thread 16-byte asynchronous copy (LDGSTS.128, L2 only); src_bytes = 0 zero-fills the destination instead
+__device__ __forceinline__ void copy16(void* dst, const void* src, unsigned src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
 }
 // the barrier receives one arrival from this thread once all its earlier cp.async have landed (no pending-count
 // increment: the barrier's arrival count must include it)
@@ -135,10 +135,11 @@ struct VolRing {
     static constexpr int NWARPS = 8, TILEY = 2 * NWARPS; // a warp owns two rows: 30 x 16 tiles
     static constexpr int BOXR = TILEY + 2;               // rows per stage: the tile + one halo row on each side
     static constexpr int TROW = 10 * 32;                 // table: floats per stage row, [plane][32 lanes]
-    // direction (p and z): the 18 stage rows are stored as 10 row PAIRS [(r + 1) / 2][channel][32 lanes][(r + 1) % 2], so
-    // that the two rows a thread owns (stage rows 1 + 2 wy, 2 + 2 wy) are one 64-bit shared-memory load per channel
-    static constexpr int DPAIR = 6 * 64, NPAIR = BOXR / 2 + 1;
-    static constexpr int TABF = BOXR * TROW, DIRF = NPAIR * DPAIR, STAGEF = TABF + 2 * DIRF;   // table, p, z
+    // direction (p and z): [row][channel][DW floats]: the 32-site window of a tile row starts at x = 30 bx - 1, which is never
+    // 16-byte aligned; the aligned superset of 36 floats (9 chunks of 16 bytes, none of which straddles a 32-site block)
+    // is staged instead and the march reads at (30 bx - 1) % 4 + lane
+    static constexpr int DW = 36, DROW = 6 * DW;
+    static constexpr int TABF = BOXR * TROW, DIRF = BOXR * DROW, STAGEF = TABF + 2 * DIRF;   // table, p, z
     static constexpr size_t SMEM = (size_t)NS * STAGEF * 4 + 2 * NS * 8 + 128;
 };
 
@@ -149,7 +150,7 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
                           double* zero_a, double* zero_b) {
     using F = VolumetricFunctor<float, 6>;
     using G = VolRing;
-    constexpr int TX = F::FTX, TY = G::TILEY, ZC = F::ZC, NS = G::NS, PL = 32, DL = 64;     // PL / DL: plane / channel stride inside a table row / a direction row pair
+    constexpr int TX = F::FTX, TY = G::TILEY, ZC = F::ZC, NS = G::NS, PL = 32, DL = G::DW;     // PL / DL: plane / channel stride inside a table row / a direction row
     const int W = f.W, H = f.H, D = f.D;
     const long sz = (long)W * H;
     const int zlo = f.z_lo(), zhi = f.z_hi();
@@ -202,29 +203,31 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
         } else if (lane == 1) { if (t2) bulk::copy(tabs + 9 * G::TROW, rec + rec_y, 10240, full + st); }
         else if (lane == 2) { if (t0) bulk::copy(tabs, rec - rec_y + 7 * F::RWS, 1280, full + st); }
         else if (lane == 3) { if (t3) bulk::copy(tabs + 17 * G::TROW, rec + 2 * rec_y, 1280, full + st); }
-        // direction: lane = position in the 32-site window that starts at x = 30 bx - 1; one 4-byte copy per lane,
-        // channel and row (a coalesced 128-byte request that straddles two 32-site blocks), zero-filled outside the
-        // grid in x.  Fused: p into the p slot and z into the z slot; a ghost plane of a slab (its p' was pushed by
-        // the neighbour before this kernel) goes from p_new into the z slot and is combined with beta = 0.
-        const int xw = bx * TX - 1 + lane;
-        const unsigned okx = xw >= 0 && xw < W ? 4u : 0u;
-        const long lane_off = okx ? (long)(xw >> 5) * 192 + (xw & 31) : 0;
+        // direction: 16-byte chunks.  Lanes 0..26 = 3 channels x 9 chunks; two copies per row and array cover the six
+        // channels of the 36-float superset [xa, xa + 36), xa = (30 bx - 1) & ~3, zero-filled outside the grid in x.
+        // Fused: p into the p slot and z into the z slot; a ghost plane of a slab (its p' was pushed by the neighbour
+        // before this kernel) goes from p_new into the z slot and is combined with beta = 0.
+        const int g = lane / 9, ck = lane - 9 * g;                          // channel group member, chunk
+        const int xc = ((bx * TX - 1) & ~3) + 4 * ck;                       // first site of this lane's chunk
+        const unsigned okx = lane < 27 && xc >= 0 && xc + 3 < W ? 16u : 0u;
+        const long lane_off = okx ? (long)(xc >> 5) * 192 + (xc & 31) + g * 32 : 0;
         const int ya = by * TY - 1;                                         // grid row of stage row 0
         const int r_lo = ya < 0 ? 1 : 0, r_hi = ya + G::BOXR <= H ? G::BOXR : H - ya;   // stage rows [r_lo, r_hi) exist
         const bool ghost = FUSED && (pr_z < zlo || pr_z >= zhi);
         const long row0 = ((long)pr_z * H + (ya + r_lo)) * orow + lane_off;
         const float* sa = (ghost ? p_new.d : p.d) + row0;                   // -> p slot (z slot for a ghost plane)
         const float* sb = zv.d + row0;                                      // -> z slot
-        float* da = dirs + (ghost ? G::DIRF : 0) + 2 * lane;
-        for (int r = r_lo; r < r_hi; ++r) {
-            float* d = da + ((r + 1) >> 1) * G::DPAIR + ((r + 1) & 1);
-#pragma unroll
-            for (int k = 0; k < 6; ++k) bulk::copy4(d + k * 64, sa + k * 32, okx);
-            if (FUSED && !ghost) {
-#pragma unroll
-                for (int k = 0; k < 6; ++k) bulk::copy4(d + G::DIRF + k * 64, sb + k * 32, okx);
+        float* da = dirs + (ghost ? G::DIRF : 0) + r_lo * G::DROW + g * G::DW + 4 * ck;
+        if (lane < 27) {
+            for (int r = r_lo; r < r_hi; ++r) {
+                bulk::copy16(da, sa, okx);
+                bulk::copy16(da + 3 * G::DW, sa + 96, okx);
+                if (FUSED && !ghost) {
+                    bulk::copy16(da + G::DIRF, sb, okx);
+                    bulk::copy16(da + G::DIRF + 3 * G::DW, sb + 96, okx);
+                }
+                sa += orow; sb += orow; da += G::DROW;
             }
-            sa += orow; sb += orow;
         }
         bulk::arrive_on_copies(full + st);
     };
@@ -253,9 +256,9 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
         const bool eup = in1 && y1 + 1 < H, edn = in0 && y0 > 0;
         const f2 m_yp = mk2(in1 ? 1.f : 0.f, eup ? 1.f : 0.f), m_ym = mk2(edn ? 1.f : 0.f, in1 ? 1.f : 0.f);
         const f2 m_ext = mk2(edn ? 1.f : 0.f, eup ? 1.f : 0.f);
-        // a thread's rows of a stage: table at tb[k PL], tb[k PL + TROW]; direction pair (64-bit) at db[k DL], z slot DIRF further
+        // a thread's rows of a stage: table at tb[k PL], tb[k PL + TROW]; direction at db[k DL], db[k DL + DROW], z slot DIRF further
         const int toff = (1 + ty0) * G::TROW + lane;
-        const int doff = G::TABF + (wy + 1) * G::DPAIR + 2 * lane;         // the thread's row pair; channel k at + 64 k
+        const int doff = G::TABF + (1 + ty0) * G::DROW + ((bx * TX - 1) & 3) + lane;   // the thread's first row; channel k at + DW k, second row DROW further
         // out (and CtC) in the blocked layout: channel k of this thread's row-0 site at os[k * 32], row 1 at os[k * 32 + orow]
         const long s0 = x + (long)W * y0 + sz * z0;
         float* os = out.d + ((s0 >> 5) * 192 + (s0 & 31));
@@ -276,20 +279,14 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
         };
         auto tpair = [&](const float* q) { return mk2(q[0], q[G::TROW]); };
         // direction of the thread's two rows: p, or p' = z + beta p (b2 = 0 for a ghost plane, whose z slot holds p')
-        auto ld2 = [](const float* q) { f2 r; r.v = *reinterpret_cast<const float2*>(q); return r; };
         auto dpair = [&](const float* q, f2 b2) {
-            if (FUSED) return fma2(b2, ld2(q), ld2(q + G::DIRF));
-            return ld2(q);
+            if (FUSED) return fma2(b2, mk2(q[0], q[G::DROW]), mk2(q[G::DIRF], q[G::DIRF + G::DROW]));
+            return mk2(q[0], q[G::DROW]);
         };
-        // ... of the stage rows below / above the pair (lo = below: second row of the pair below, hi = above: first
-        // row of the pair above; loaded as whole pairs, which keeps the accesses free of bank conflicts)
+        // ... of the stage rows below / above the pair (lo = below, hi = above)
         auto dext = [&](const float* q, f2 b2) {
-            const f2 lo = ld2(q - G::DPAIR), hi = ld2(q + G::DPAIR);
-            if (FUSED) {
-                const f2 zlo = ld2(q - G::DPAIR + G::DIRF), zhi = ld2(q + G::DPAIR + G::DIRF);
-                return fma2(b2, mk2(lo.v.y, hi.v.x), mk2(zlo.v.y, zhi.v.x));
-            }
-            return mk2(lo.v.y, hi.v.x);
+            if (FUSED) return fma2(b2, mk2(q[-G::DROW], q[2 * G::DROW]), mk2(q[G::DIRF - G::DROW], q[G::DIRF + 2 * G::DROW]));
+            return mk2(q[-G::DROW], q[2 * G::DROW]);
         };
         auto plane_beta = [&](int z) { return bc2(z >= zlo && z < zhi ? beta : 0.f); };
 
@@ -361,7 +358,7 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
                     write_O(P, a, 1);
                 }
             }
-            if (last) { release(z); return false; }
+            if (!last) {              // (one release site per step instantiation: the inlined stage-issue code is large)
             // ---- x: both directions through shuffles -------------------------------------------------
             {
                 f2 unr[3], unl[3], pnr[3], pnl[3];
@@ -430,7 +427,9 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
                 }
                 dot += (double)((w0 ? dsum.v.x : 0.f) + (w1 ? dsum.v.y : 0.f));
             }
+            }
             release(z);
+            if (last) return false;
             havePrev = true; writePrev = true;
             os += oplane; cs += oplane; ns += oplane;
             return true;
