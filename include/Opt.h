@@ -37,8 +37,8 @@ struct Opt_InitializationParameters {
     int  collectPerKernelTimingInfo; /* nonzero: cudaEvent pair per kernel launch, table printed at the end */
     char backend[20];                /* "backend_cuda" (or empty). "backend_cpu", "backend_cpu_mt" are rejected */
     int  numthreads;                 /* ignored (CPU-MT backend only in the reference) */
-    int  useMaterializedJTJ;         /* ignored: the engine is matrix-free; results are identical by construction */
-    int  useFusedJTJ;                /* ignored, see above */
+    int  useMaterializedJTJ;         /* PCGStep1 over a stored Jacobian: J^T (J p) through CSR kernels (solver:1523-1761) */
+    int  useFusedJTJ;                /* with useMaterializedJTJ: the product J^T J is formed and PCGStep1 = (J^T J) p */
 };
 typedef struct Opt_InitializationParameters Opt_InitializationParameters;
 

@@ -41,6 +41,13 @@ int  OptB200_PlanSetSlab(Opt_Plan* plan, int rank, int nranks, int halo, const v
 int OptB200_EnergyDescribe(const char* path, char* out, unsigned long cap);
 const char* OptB200_EnergyExpected(const char* energy);
 
+/* Materialized-Jacobian mode in effect for this plan (Opt_InitializationParameters.useMaterializedJTJ / useFusedJTJ,
+ * solverGPUGaussNewton.t:1523-1761): 0 = matrix-free kernels, 1 = PCGStep1 as J^T (J p) over stored CSR matrices, 2 = as
+ * (J^T J) p.  Energies without a Jacobian-row emitter stay at 0 (the iterates are the same in all three modes, as
+ * examples/test_final_cost.py:91-93 requires).  Nnz: 0 = nnz(J), 1 = nnz(J^T J), valid after the first Opt_ProblemStep. */
+int  OptB200_PlanMaterializedMode(Opt_Plan* plan);
+long OptB200_PlanMaterializedNnz(Opt_Plan* plan, int which);
+
 /* Kernels launched by this plan since it was created (bench.py's "gpu_launches"). */
 long OptB200_PlanLaunchCount(Opt_Plan* plan);
 /* PCG iterations executed by this plan since it was created.  Gauss-Newton always runs nIterations x lIterations;

@@ -50,7 +50,7 @@ def _compile(src, verbose):
 
 def build(verbose=False, oracle=True):
     os.makedirs(OBJ, exist_ok=True)
-    srcs = [os.path.join(CSRC, "opt_api.c"), os.path.join(CSRC, "registry.cu"), os.path.join(CSRC, "driver_ops.cu"), os.path.join(CSRC, "formats.c"), os.path.join(CSRC, "energy_check.c")]
+    srcs = [os.path.join(CSRC, "opt_api.c"), os.path.join(CSRC, "registry.cu"), os.path.join(CSRC, "driver_ops.cu"), os.path.join(CSRC, "csr_api.cu"), os.path.join(CSRC, "formats.c"), os.path.join(CSRC, "energy_check.c")]
     ex = os.path.join(CSRC, "examples")
     srcs += sorted(os.path.join(ex, f) for f in os.listdir(ex) if f.endswith(".cu"))
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as pool:
@@ -89,7 +89,9 @@ def build(verbose=False, oracle=True):
         if os.path.isdir("/root/reference/examples/shared"):
             for d in ("tests/ref_driver", "oracle/ref_src"):
                 if os.path.exists(os.path.join(ROOT, d, "Makefile")):
-                    subprocess.check_call(["make", "-s", "-j8", "-C", os.path.join(ROOT, d)])
+                    r = subprocess.run(["make", "-s", "-j8", "-C", os.path.join(ROOT, d)], capture_output=True, text=True)
+                    if r.returncode != 0:
+                        raise RuntimeError("make -C %s failed:\n%s" % (d, r.stderr[-4000:]))
     return LIB
 
 

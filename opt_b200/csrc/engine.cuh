@@ -19,6 +19,7 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_select.cuh>
 #include "common.cuh"
+#include "csr.cuh"
 #include "functors/math.cuh"
 #include "optk.h"
 
@@ -55,6 +56,8 @@ struct OptK_Plan {
     virtual int debug_read_range(const char* name, long first_site, long nsites, void* host_out) = 0;
     virtual void debug_apply_jtj(const void* host_p, void* host_out) = 0;
     virtual int set_slab(int rank, int nranks, int halo, const void* nccl_unique_id) = 0;
+    virtual int set_materialized(int mode) = 0;          // 0 matrix-free, 1 J and J^T, 2 fused J^T J; returns the mode in effect
+    virtual long materialized_nnz(int which) const = 0;   // 0 J, 1 J^T J
 
     // ---- launch bookkeeping shared by all engines -------------------------------------------
     cudaStream_t stream = nullptr;
@@ -933,6 +936,54 @@ __global__ void __launch_bounds__(256) k_halo_push(const V4* __restrict__ src, l
     }
 }
 
+// ------------------------------------------------------------------------------ materialized Jacobian
+// saveJToCRS / saveJToCRS_Graph (solver:1004-1022, 1287-1307, generateDumpJ :385-442): every site / edge writes its residual
+// rows through a RowSink (csr.cuh).  COUNT pass: row lengths; fill pass: columns and values at the scanned row offsets.
+template <class F, bool COUNT>
+__global__ void k_save_j(F f, TileGrid tg, int* cnt_or_ptr, int* colInd, typename F::Scalar* val, long plane) {
+    int x, y, z; long s;
+    f.o_lo = 0; f.o_hi = 0x7fffffff;
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, z, s)) {
+        RowSink<typename F::Scalar, VecOf<F>, COUNT> sink{cnt_or_ptr, colInd, val, s * F::MAT_ROWS, plane};
+        f.rowsJ(x, y, z, s, sink);
+        sink.close();
+    }
+}
+template <class F, bool COUNT>
+__global__ void k_save_j_graph(F f, long E, long row_base, int* cnt_or_ptr, int* colInd, typename F::Scalar* val, long plane) {
+    const long e = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (e >= E) return;
+    RowSink<typename F::Scalar, VecOf<F>, COUNT> sink{cnt_or_ptr, colInd, val, row_base + e * F::MAT_GROWS, plane};
+    f.graphRowsJ(e, sink);
+    sink.close();
+}
+// PCGStep1_Finish (solver:646-660): alphaDenominator = <p, Ap> over the non-excluded unknowns after the sparse products.  The
+// products also fill the entries of Ap that belong to excluded unknowns (their columns exist in J); those are cleared here,
+// because the streaming kernels rely on excluded sites holding 0.  LM: + CtC p, which the matrix-free PCGStep1 adds
+// (o.t:2817-2823) -- the reference's materialized path leaves it out; here the three modes give the same iterates.
+template <class F, bool LM>
+__global__ void k_pcg_step1_finish(F f, TileGrid tg, VecOf<F> dir, VecOf<F> out, VecOf<F> CtC, double* den, double* zero_slot) {
+    using T = typename F::Scalar;
+    constexpr int U = F::U;
+    int x, y, z; long s;
+    double acc = 0.0;
+    if (zero_slot && blockIdx.x == 0 && linear_tid() == 0) *zero_slot = 0.0;
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, z, s)) {
+        const bool ex = f.exclude(x, y, z, s);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (ex) { out(u, s) = T(0); continue; }
+            const T pv = dir(u, s);
+            T o = out(u, s);
+            if (LM) { o += CtC(u, s) * pv; out(u, s) = o; }
+            acc += (double)(pv * o);
+        }
+    }
+    block_accumulate(acc, den);
+}
+
 // Fused slab path of a blocked solver vector: the new search direction p' = z + beta p of the two owned boundary slices
 // (the PCGStep3 of those planes, ahead of the fused PCGStep3+1 kernel) is stored straight into the neighbours' ghost
 // slices of THEIR p' buffer; the fused kernel then stages ghost planes from p' (volumetric_packed.cuh).  `local_out`
@@ -1057,10 +1108,102 @@ struct Engine : OptK_Plan {
         for (void* q : xr_opened) cudaIpcCloseMemHandle(q);
         cudaFree(xr_buf); cudaFree(xr_error);
         if (comm) ncclCommDestroy(comm);
+        release_materialized(); m_tmp.release();
         cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFreeHost(lm_box); cudaFree(active4); cudaFree(mask_changed);
         cudaFree(inc); cudaFree(inc_off); cudaFree(inc_count); cudaFree(sort_tmp); cudaFree(key_a); cudaFree(key_b); cudaFree(val_a);
         base_destroy();
     }
+    // ---- materialized Jacobian: J (and J^T, J^T J) as CSR over the solver-vector index space -----------------------
+    int mat_mode = 0;
+    CsrMat<T> mJ, mJT, mJTJ;
+    int *m_perm = nullptr, *m_rowOf = nullptr;
+    T* m_Jp = nullptr;
+    Scratch m_tmp;
+    void release_materialized() {
+        mJ.release(); mJT.release(); mJTJ.release();
+        cudaFree(m_perm); cudaFree(m_rowOf); cudaFree(m_Jp); m_perm = m_rowOf = nullptr; m_Jp = nullptr;
+    }
+    int set_materialized(int mode) override {
+        if constexpr (!F::HAS_ROWS_J) {
+            if (mode) fprintf(stderr, "Opt: this energy has no Jacobian-row emitter; useMaterializedJTJ is served by the matrix-free kernels (same iterates)\n");
+            return 0;
+        } else {
+            if (mode && (nranks > 1 || F::VEC_UB > 0)) { fprintf(stderr, "Opt: materialized Jacobian is single-GPU / SoA only; using the matrix-free kernels\n"); return 0; }
+            mat_mode = mode;
+            if (mode) fuse = false;                          // PCGStep3 stays its own kernel, as in the reference's materialized path
+            return mode;
+        }
+    }
+    long materialized_nnz(int which) const override { return which == 0 ? mJ.nnz : mJTJ.nnz; }
+    // cusparseOuter (solver:1532-1657).  Pattern (row offsets, columns, transpose permutation, J^T J pattern) once per solve:
+    // the graph index arrays belong to the caller; values at every nonlinear iteration.
+    void materialize(int nIter) {
+        if constexpr (F::HAS_ROWS_J) {
+            const long rows = N * F::MAT_ROWS + E * F::MAT_GROWS;
+            if (nIter == 0 || !mJ.rowPtr) {
+                release_materialized();
+                mJ.nrows = (int)rows; mJ.ncols = (int)((long)U * Npad);
+                int* cnt = nullptr;
+                OPTK_CUDA(cudaMalloc(&cnt, (size_t)(rows + 1) * sizeof(int)));
+                OPTK_CUDA(cudaMalloc(&mJ.rowPtr, (size_t)(rows + 1) * sizeof(int)));
+                OPTK_CUDA(cudaMemsetAsync(cnt, 0, (size_t)(rows + 1) * sizeof(int), stream));
+                if constexpr (F::MAT_ROWS > 0) this->launch_tiles("saveJToCRS_count", tg.n, sblock, k_save_j<F, true>, f, tg, cnt, (int*)nullptr, (T*)nullptr, Npad);
+                if constexpr (F::MAT_GROWS > 0) if (E > 0) this->launch("saveJToCRS_Graph_count", edge_grid(), dim3(256), k_save_j_graph<F, true>, f, E, N * F::MAT_ROWS, cnt, (int*)nullptr, (T*)nullptr, Npad);
+                size_t bytes = 0;
+                cub::DeviceScan::ExclusiveSum(nullptr, bytes, cnt, mJ.rowPtr, (int)(rows + 1), stream);
+                cub::DeviceScan::ExclusiveSum(m_tmp.get(bytes), bytes, cnt, mJ.rowPtr, (int)(rows + 1), stream);
+                int nnz = 0;
+                OPTK_CUDA(cudaMemcpyAsync(&nnz, mJ.rowPtr + rows, sizeof(int), cudaMemcpyDeviceToHost, stream));
+                OPTK_CUDA(cudaStreamSynchronize(stream));
+                cudaFree(cnt);
+                mJ.nnz = nnz;
+                OPTK_CUDA(cudaMalloc(&mJ.colInd, (size_t)std::max(nnz, 1) * sizeof(int)));
+                OPTK_CUDA(cudaMalloc(&mJ.val, (size_t)std::max(nnz, 1) * sizeof(T)));
+                OPTK_CUDA(cudaMalloc(&m_Jp, (size_t)std::max<long>(rows, 1) * sizeof(T)));
+                fill_j();
+                this->pre_launch("JT alloc");
+                csr_transpose_pattern(mJ, mJT, &m_perm, m_tmp, stream);
+                this->post_launch();
+                if (mat_mode == 2) {
+                    this->pre_launch("J^TJ alloc");
+                    csr_ata_pattern(mJ, mJTJ, &m_rowOf, m_tmp, stream);
+                    this->post_launch();
+                }
+            } else fill_j();
+            this->pre_launch("J_transpose");
+            csr_transpose_values(mJ, mJT, m_perm, stream);
+            this->post_launch();
+            if (mat_mode == 2) {
+                this->pre_launch("JTJ multiply");
+                csr_ata_values(mJ, mJT, mJTJ, m_rowOf, stream);
+                this->post_launch();
+            }
+        }
+    }
+    void fill_j() {
+        if constexpr (F::HAS_ROWS_J) {
+            if constexpr (F::MAT_ROWS > 0) this->launch_tiles("saveJToCRS", tg.n, sblock, k_save_j<F, false>, f, tg, mJ.rowPtr, mJ.colInd, mJ.val, Npad);
+            if constexpr (F::MAT_GROWS > 0) if (E > 0) this->launch("saveJToCRS_Graph", edge_grid(), dim3(256), k_save_j_graph<F, false>, f, E, N * F::MAT_ROWS, mJ.rowPtr, mJ.colInd, mJ.val, Npad);
+        }
+    }
+    // cusparseInner + PCGStep1_Finish (solver:1660-1756, 646-660)
+    void apply_materialized(V dir, V out, double* den, double* zero_slot) {
+        if (mat_mode == 2) {
+            this->pre_launch("J^TJp");
+            csr_spmv(mJTJ, (const T*)dir.d, out.d, nsm, stream);
+            this->post_launch();
+        } else {
+            this->pre_launch("Jp");
+            csr_spmv(mJ, (const T*)dir.d, m_Jp, nsm, stream);
+            this->post_launch();
+            this->pre_launch("J^T");
+            csr_spmv(mJT, (const T*)m_Jp, out.d, nsm, stream);
+            this->post_launch();
+        }
+        if (lm) this->launch_tiles("PCGStep1_Finish", tg.n, sblock, k_pcg_step1_finish<F, true>, f, tg, dir, out, CtC, den, zero_slot);
+        else    this->launch_tiles("PCGStep1_Finish", tg.n, sblock, k_pcg_step1_finish<F, false>, f, tg, dir, out, CtC, den, zero_slot);
+    }
+
     int unknown_channels() const override { return U; }
     long site_count() const override { return N; }
     void bind(void** pp) override { f.bind(pp); }
@@ -1388,9 +1531,11 @@ struct Engine : OptK_Plan {
         }
         reduce(S_RZ0);
         exchange(p);                                        // Step1 reads p over the stencil
+        if (mat_mode) materialize(nIter);                   // cusparseOuter (solver:2068)
     }
 
     void apply_A(const char* name, const char* gname, V dir, V out, double* den, double* zero_slot) {
+        if (mat_mode && mJ.rowPtr) { apply_materialized(dir, out, den, zero_slot); return; }
         if constexpr (F::HAS_GATHER) {
             if (use_gather()) {
                 const long nb = (N + 127) / 128;
@@ -1625,6 +1770,7 @@ struct Engine : OptK_Plan {
         OPTK_CUDA(cudaMemsetAsync(Ap.d, 0, tmp.size() * sizeof(T), stream));
         bool saved = lm; lm = false;
         if (use_gather()) build_incidence();
+        if (mat_mode) materialize(0);
         apply_A("PCGStep1", "PCGStep1_Graph", p, Ap, S(S_DUMMY), nullptr);
         lm = saved;
         debug_read("Ap", host_out);
@@ -1646,6 +1792,8 @@ struct FunctorDefaults {
     static constexpr bool HAS_FAST_PRECOMPUTE = false;   // ... and precompute (fast_precompute(stream, nsm))
     static constexpr bool SLAB_OK = true;                // grid functors whose bounds predicates survive a slab cut
     static constexpr bool HAS_GATHER = false;            // graph functors with a per-vertex gather form of J^T J p
+    static constexpr bool HAS_ROWS_J = false;            // functors that emit their Jacobian rows (materialized-J mode, csr.cuh RowSink)
+    static constexpr int MAT_ROWS = 0, MAT_GROWS = 0;    // residual rows per site / per edge
     static constexpr int VEC_UB = 0;                     // solver-vector layout: 0 = SoA, U = blocked (common.cuh, Vec)
     static constexpr bool FUSE_STEP3 = true;             // form p' = z + beta p inside the J^T J kernel (engine.cuh, FusedDir)
     bool fast_ok() const { return false; }

@@ -138,6 +138,15 @@ struct ArapFunctor : FunctorDefaults<T> {
         }
         return sum;
     }
+    // ---- Jacobian rows (materialized-J mode): 3 fit rows per vertex; 3 rows per edge a -> b with +w_r at O_a, -w_r at O_b and
+    // w_r D_ab[k][j] at A_a[j] (saveJToCRS_Graph, solver:1287-1307)
+    static constexpr bool HAS_ROWS_J = true;
+    static constexpr int MAT_ROWS = 3, MAT_GROWS = 3;
+    template <class Sink> __device__ void rowsJ(int, int, int, long s, Sink& sink) const {
+        const T wf = fit_valid(s) ? w_fit : T(0);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { sink.begin(k); sink.add(s, k, wf); }
+    }
     // ---- edge domain
     struct Edge { long a, b; T e[3]; T Dm[3][3]; };
     __device__ __forceinline__ void edge(long ei, Edge& ed, bool need_e) const {
@@ -150,6 +159,16 @@ struct ArapFunctor : FunctorDefaults<T> {
             T Ru[3]; R.apply(u, Ru);
 #pragma unroll
             for (int k = 0; k < 3; ++k) ed.e[k] = (O[ed.a * 3 + k] - O[ed.b * 3 + k]) - Ru[k];
+        }
+    }
+    template <class Sink> __device__ void graphRowsJ(long ei, Sink& sink) const {
+        Edge ed; edge(ei, ed, false);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            sink.begin(k);
+            sink.add(ed.a, k, w_reg); sink.add(ed.b, k, -w_reg);
+#pragma unroll
+            for (int j = 0; j < 3; ++j) sink.add(ed.a, 3 + j, w_reg * ed.Dm[k][j]);
         }
     }
     __device__ T graphCost(long ei) const {

@@ -72,6 +72,35 @@ struct ImageWarpingFunctor : FunctorDefaults<T> {
             d[2] += wr2 * (Dv[0] * Dv[0] + Dv[1] * Dv[1]);
         });
     }
+    // Jacobian rows (materialized-J mode): 4 offsets x 2 channels of the regulariser, then the 2 fit rows.  The structure
+    // depends on the bounds only; a residual that the masks or the constraint test switch off keeps its entries with value 0.
+    static constexpr bool HAS_ROWS_J = true;
+    static constexpr int MAT_ROWS = 10;
+    template <class Sink> __device__ void rowsJ(int x, int y, int, long s, Sink& sink) const {
+        T ui[2], ci[2]; load2(Ur + s * 2, ui); load2(Cn + s * 2, ci);
+        T sa, ca; sincos_t(A[s], sa, ca);
+        const bool inb[4] = {x + 1 < W, x > 0, y + 1 < H, y > 0};
+        const long nb[4] = {s + 1, s - 1, s + W, s - W};
+        const bool mi = M[s] == T(0);
+#pragma unroll
+        for (int o = 0; o < 4; ++o) {
+            T w = T(0), Dv[2] = {T(0), T(0)};
+            if (inb[o]) {
+                T un[2]; load2(Ur + nb[o] * 2, un);
+                T u[2] = {ui[0] - un[0], ui[1] - un[1]}, Ru[2];
+                rot(sa, ca, u, Ru, Dv);
+                w = (mi && M[nb[o]] == T(0)) ? w_reg : T(0);
+            }
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                sink.begin(o * 2 + k);
+                if (inb[o]) { sink.add(s, k, w); sink.add(nb[o], k, -w); sink.add(s, 2, w * Dv[k]); }
+            }
+        }
+        const T wf = (ci[0] >= T(0) && ci[1] >= T(0)) ? w_fit : T(0);
+        sink.begin(8); sink.add(s, 0, wf);
+        sink.begin(9); sink.add(s, 1, wf);
+    }
     template <class P> __device__ void applyJTJ(int x, int y, int, long s, const P& p, T* out) const {
         T ui[2], ci[2]; load2(Ur + s * 2, ui); load2(Cn + s * 2, ci);
         T sa, ca; sincos_t(A[s], sa, ca);

@@ -89,6 +89,21 @@ struct PoissonFunctor : FunctorDefaults<T> {
 #pragma unroll
         for (int c = 0; c < 4; ++c) { g[c] = T(2) * g[c]; d[c] = T(2) * cnt; }
     }
+    // Jacobian rows (materialized-J mode, engine.cuh k_save_j): 4 offsets x 4 channels; residual (o, c) at site s has
+    // +1 at X(s)[c] and -1 at X(n)[c] when the neighbour is in bounds, and is identically 0 otherwise (Select(InBounds, e, 0)).
+    static constexpr bool HAS_ROWS_J = true;
+    static constexpr int MAT_ROWS = 16;
+    template <class Sink> __device__ void rowsJ(int x, int y, int, long s, Sink& sink) const {
+        const bool inb[4] = {x + 1 < W, x > 0, y + 1 < H, y > 0};
+        const long nb[4] = {s + 1, s - 1, s + W, s - W};
+#pragma unroll
+        for (int o = 0; o < 4; ++o)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                sink.begin(o * 4 + c);
+                if (inb[o]) { sink.add(s, c, T(1)); sink.add(nb[o], c, T(-1)); }
+            }
+    }
     template <class P> __device__ void applyJTJ(int x, int y, int, long s, const P& p, T* out) const {
         T pi[4];
 #pragma unroll

@@ -46,6 +46,7 @@ struct Opt_Plan {
     int finished_reported;
     long pcg_iterations;   /* PCG iterations executed since creation (LM leaves the inner loop early) */
     int lm_host_loop;      /* OPTB200_LM_HOSTLOOP=1: blocking fetchQ per iteration, as the reference does */
+    int materialized;      /* 0 matrix-free, 1 J and J^T as CSR, 2 fused J^T J (Opt_InitializationParameters) */
 };
 
 /* opt_float rounding: the reference keeps these host scalars in opt_float */
@@ -141,6 +142,8 @@ Opt_Plan* Opt_ProblemPlan(Opt_State* state, Opt_Problem* problem, unsigned int* 
     plan->verbosity = state->ip.verbosityLevel;
     plan->timing = state->ip.collectPerKernelTimingInfo != 0;
     plan->lm_host_loop = getenv("OPTB200_LM_HOSTLOOP") != NULL;
+    /* solver:1523-1761: useMaterializedJTJ stores J (and J^T); with useFusedJTJ the product J^T J as well */
+    if (state->ip.useMaterializedJTJ) plan->materialized = optk_set_materialized(k, state->ip.useFusedJTJ ? 2 : 1);
     default_parameters(&plan->sp);
     return plan;
 }
@@ -316,6 +319,8 @@ int OptB200_PlanSetSlab(Opt_Plan* plan, int rank, int nranks, int halo, const vo
     return optk_set_slab(plan->k, rank, nranks, halo, nccl_unique_id);
 }
 long OptB200_PlanLaunchCount(Opt_Plan* plan) { return optk_launch_count(plan->k); }
+int OptB200_PlanMaterializedMode(Opt_Plan* plan) { return plan->materialized; }
+long OptB200_PlanMaterializedNnz(Opt_Plan* plan, int which) { return optk_materialized_nnz(plan->k, which); }
 long OptB200_PlanPcgIterations(Opt_Plan* plan) { return plan->pcg_iterations; }
 int OptB200_PlanKernelTime(Opt_Plan* plan, const char* kernel, double* total_ms) {
     return optk_kernel_time(plan->k, kernel, total_ms);

@@ -52,6 +52,12 @@ void   optk_revert_update(OptK_Plan*);        /* revertUpdate (solver:864-869) *
 int    optk_set_slab(OptK_Plan*, int rank, int nranks, int halo, const void* nccl_unique_id);
 void   optk_nccl_unique_id(void* out128);
 
+/* Materialized Jacobian (Opt_InitializationParameters.useMaterializedJTJ / useFusedJTJ; solver:1523-1761): mode 1 =
+ * PCGStep1 as J^T (J p), mode 2 = (J^T J) p, both through the CSR kernels of csr.cuh.  Returns the mode in effect (0 if the
+ * energy has no Jacobian-row emitter: matrix-free, same iterates). */
+int    optk_set_materialized(OptK_Plan*, int mode);
+long   optk_materialized_nnz(OptK_Plan*, int which);   /* 0: nnz(J), 1: nnz(J^T J) */
+
 /* statistics and debugging */
 long   optk_launch_count(OptK_Plan*);         /* kernels launched since creation */
 void   optk_print_timing(OptK_Plan*);         /* Kernel | Count | Total | Average table (backend_cuda.t:152-297) */

@@ -79,6 +79,8 @@ void optk_nccl_unique_id(void* out128) {
     static_assert(sizeof(id) == 128, "ncclUniqueId is 128 bytes");
     memcpy(out128, &id, sizeof(id));
 }
+int optk_set_materialized(OptK_Plan* p, int mode) { return p->set_materialized(mode); }
+long optk_materialized_nnz(OptK_Plan* p, int which) { return p->materialized_nnz(which); }
 long optk_launch_count(OptK_Plan* p) { return p->launches; }
 void optk_print_timing(OptK_Plan* p) { p->print_timing(); }
 int optk_kernel_time(OptK_Plan* p, const char* k, double* ms) { return p->kernel_time(k, ms); }

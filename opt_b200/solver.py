@@ -42,6 +42,10 @@ def load_library():
         _lib.OptB200_FreeState.argtypes = [P]
         _lib.OptB200_PlanLaunchCount.restype = C.c_long
         _lib.OptB200_PlanLaunchCount.argtypes = [P]
+        _lib.OptB200_PlanMaterializedMode.restype = C.c_int
+        _lib.OptB200_PlanMaterializedMode.argtypes = [P]
+        _lib.OptB200_PlanMaterializedNnz.restype = C.c_long
+        _lib.OptB200_PlanMaterializedNnz.argtypes = [P, C.c_int]
         _lib.OptB200_PlanPcgIterations.restype = C.c_long
         _lib.OptB200_PlanPcgIterations.argtypes = [P]
         _lib.OptB200_PlanKernelTime.restype = C.c_int
@@ -93,7 +97,7 @@ class NamedParameters:
 
 class OptSolver:
     def __init__(self, dims, energy_file, solver_kind="gaussNewtonGPU", double=False, verbosity=0,
-                 timing=False, backend="backend_cuda"):
+                 timing=False, backend="backend_cuda", materialized=False, fused_jtj=False):
         self.lib, self.f = load_library()
         ip = capi.Opt_InitializationParameters()
         ip.doublePrecision = int(double)
@@ -101,6 +105,8 @@ class OptSolver:
         ip.collectPerKernelTimingInfo = int(timing)
         ip.backend = backend.encode()
         ip.numthreads = 1
+        ip.useMaterializedJTJ = int(materialized)
+        ip.useFusedJTJ = int(fused_jtj)
         self.double = double
         self.state = self.f["NewState"](ip)
         if not self.state:
@@ -160,6 +166,13 @@ class OptSolver:
     # --- OptB200.h extensions --------------------------------------------------------------------
     def launch_count(self):
         return self.lib.OptB200_PlanLaunchCount(self.plan)
+
+    def materialized_mode(self):
+        """0 matrix-free, 1 J and J^T stored, 2 fused J^T J (the mode in effect, not the one asked for)."""
+        return self.lib.OptB200_PlanMaterializedMode(self.plan)
+
+    def materialized_nnz(self, which=0):
+        return self.lib.OptB200_PlanMaterializedNnz(self.plan, which)
 
     def pcg_iterations(self):
         """PCG iterations executed since the plan was created (LM may leave the inner loop early)."""
