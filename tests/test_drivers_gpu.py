@@ -112,3 +112,86 @@ def test_optical_flow_driver_matches_oracle(built):
     # first one's fp32 solution, whose rounding differences the re-weighted problem amplifies
     for k, (a, b) in enumerate(zip(drv.costs, ref_costs)):
         assert abs(a - b) <= (1e-4 if k % 2 == 0 else 1e-3) * abs(b), (drv.costs, ref_costs)
+
+
+# ------------------------------------------------------------------------------ pinned to the reference's own code
+# oracle/_ref/{iw_raster, of_ops, vol_skin} are the reference's CPU driver functions compiled from /root/reference where
+# they lie (oracle/ref_src/Makefile, built by build() in the container; they travel to the GPU box).  Both the CUDA kernels
+# and the numpy restatement are held to their output: pixel-exact (rasteriser, lines, Prewitt), bit-exact (skinning), 1e-6
+# (Gaussian: expf of the device vs libm).
+import ref_io  # noqa: E402
+
+
+def _need_ref(name):
+    if not ref_io.have(name):
+        pytest.skip("oracle/_ref/%s not built (needs /root/reference; build() makes it in the container)" % name)
+
+
+@pytest.mark.parametrize("H,W,amp", [(9, 11, 0.0), (23, 31, 0.3), (23, 31, 1.5), (16, 16, 6.0), (64, 80, 0.8)])
+def test_rasteriser_equals_reference_code(built, tmp_path, H, W, amp):
+    """examples/image_warping/src/CombinedSolver.h:63-99, 231-308, run as compiled reference code."""
+    _need_ref("iw_raster")
+    from opt_b200 import drivers as D
+    warp, color, mask = warp_case(H, W, 5, amp)
+    (ref,) = ref_io.run_ref("iw_raster", [], [warp, color, mask], [f32], tmp_path)
+    got = D.rasterize_warp(cuda(warp), cuda(color), cuda(mask)).cpu().numpy()
+    assert np.array_equal(got, ref)
+    if H * W <= 1000:
+        assert np.array_equal(R.rasterize_warp(warp, color, mask), ref)          # the restatement is pinned too
+
+
+@pytest.mark.parametrize("shape", [(37, 53), (130, 33), (64, 256)])
+@pytest.mark.parametrize("sigma", [1.0, 5.0])
+def test_gaussian_equals_reference_code(built, tmp_path, shape, sigma):
+    """ImageHelper::filterGaussian, examples/optical_flow/src/ImageHelper.h:63-114."""
+    _need_ref("of_ops")
+    from opt_b200 import drivers as D
+    im = (np.random.default_rng(3).random(shape, dtype=f32) * 255).astype(f32)
+    (ref,) = ref_io.run_ref("of_ops", ["gauss"], [im, np.array([sigma], dtype=f32)], [f32], tmp_path)
+    got = D.filter_gaussian(cuda(im), sigma).cpu().numpy()
+    assert np.abs(got - ref).max() <= 1e-6 * 255
+    assert np.abs(R.filter_gaussian(im, sigma) - ref).max() <= 1e-6 * 255
+
+
+@pytest.mark.parametrize("shape", [(37, 53), (3, 3), (130, 33)])
+def test_prewitt_equals_reference_code(built, tmp_path, shape):
+    """HierarchyLevel::computeDU / computeDV, examples/optical_flow/src/CombinedSolver.h:152-178."""
+    _need_ref("of_ops")
+    from opt_b200 import drivers as D
+    im = (np.random.default_rng(4).random(shape, dtype=f32) * 255).astype(f32)
+    du, dv = ref_io.run_ref("of_ops", ["prewitt"], [im], [f32, f32], tmp_path)
+    assert np.array_equal(D.prewitt(cuda(im), True).cpu().numpy(), du)
+    assert np.array_equal(D.prewitt(cuda(im), False).cpu().numpy(), dv)
+    assert np.array_equal(R.prewitt(im, True), du) and np.array_equal(R.prewitt(im, False), dv)
+
+
+@pytest.mark.parametrize("H,W,scale", [(41, 58, 6.0), (30, 30, 0.4), (77, 45, 15.0)])
+def test_flow_lines_equal_reference_code(built, tmp_path, H, W, scale):
+    """renderFlowVecotors + ImageHelper::drawLine, examples/optical_flow/src/main.cpp:7-24; the line colours are taken from
+    the reference's own expression (evaluated by the harness) and handed to the CUDA entry point."""
+    _need_ref("of_ops")
+    from opt_b200 import drivers as D
+    rng = np.random.default_rng(7)
+    flow = (rng.standard_normal((H, W, 2)) * scale).astype(f32)
+    base = rng.integers(0, 255, (H, W, 4)).astype(np.uint8)
+    ref, colors = ref_io.run_ref("of_ops", ["lines"], [flow, base], [np.uint8, np.uint8], tmp_path)
+    assert colors.shape[0] == D.flow_sample_count(W, H)
+    got = D.render_flow_lines(cuda(base.copy()), cuda(flow), cuda(colors)).cpu().numpy()
+    assert np.array_equal(got, ref)
+    assert np.array_equal(R.render_flow_lines(base, flow, colors), ref)
+
+
+def test_skinning_equals_reference_code(built, tmp_path):
+    """copyResultToCPUFromFloat3, examples/volumetric_mesh_deformation/src/CombinedSolver.h:302-335."""
+    _need_ref("vol_skin")
+    from opt_b200 import drivers as D
+    dims = (5, 20, 5)
+    rng = np.random.default_rng(6)
+    grid = rng.standard_normal(((dims[0] + 1) * (dims[1] + 1) * (dims[2] + 1), 3)).astype(f32)
+    n = 4001
+    voxel = np.stack([rng.integers(0, d, n) for d in dims], axis=1).astype(np.int32)
+    rel = rng.random((n, 3), dtype=f32)
+    (ref,) = ref_io.run_ref("vol_skin", [], [grid, np.array(dims, dtype=np.int32), voxel, rel], [f32], tmp_path)
+    got = D.skin_trilinear(cuda(grid), dims, cuda(voxel), cuda(rel)).cpu().numpy()
+    assert np.array_equal(got, ref)
+    assert np.array_equal(R.skin_trilinear(grid, dims, voxel, rel), ref)

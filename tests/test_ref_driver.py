@@ -140,3 +140,15 @@ def test_unmodified_reference_poisson_example(built, golden_dir, tmp_path):
     golden = float(npz["golden_cost_1x100"])
     got = final_cost(r.stdout)
     assert abs(got - golden) <= 2e-6 * golden, (got, golden)
+
+
+@pytest.mark.parametrize("flags", [["--materialized"], ["--materialized", "--fused"]])
+def test_materialized_flags_through_reference_optsolver(built, golden_dir, tmp_path, flags):
+    """OptSolver forwards CombinedSolverParameters.useMaterializedJTJ / useFusedJTJ into Opt_InitializationParameters
+    (examples/shared/OptSolver.h:58-59); the recorded costs hold in those modes (examples/test_final_cost.py:91-93)."""
+    npz = np.load(os.path.join(golden_dir, "arap_small_armadillo.npz"))
+    out = run_harness(tmp_path, examples.arap_golden(npz), ["w_fitSqrt", "w_regSqrt", "Offset", "Angle", "UrShape", "Constraints", "G"],
+                      graph=("G", 6, 2), extra=flags)
+    assert abs(final_cost(out) - 7183.464843) <= 1e-5 * 7183.464843, out[-2000:]
+    # the kernel table of the library (collectPerKernelTimingInfo = 1 in OptSolver.h) names the sparse products it ran
+    assert ("J^TJp" in out) == ("--fused" in flags) and (" J^T " in out) != ("--fused" in flags)
