@@ -528,6 +528,55 @@ __global__ void k_graph_ctc(F f, long E, VecOf<F> CtC, typename F::Scalar inv_ra
     if (e < E) f.graphCtC(e, CtC, inv_radius);
 }
 
+// ------------------------------------------------------------------------------ graph terms as a segmented scatter
+// (functors with HAS_SEGSCATTER: the closed-form hyper-edge energies of functors/graph_generic.cuh)
+template <class F>
+__global__ void k_segment_keys(F f, long n, unsigned* vertices, unsigned* ids) {
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    vertices[i] = (unsigned)f.edgeVertex(i / F::GV, (int)(i % F::GV));
+    ids[i] = (unsigned)i;
+}
+// PCGStep1_Graph, part 1: one thread per hyper-edge, partials into the edge's own GV * U slots (coalesced rows)
+template <class F>
+__global__ void k_graph_contrib(F f, long E, VecOf<F> dir, typename F::Scalar* __restrict__ contrib) {
+    const long e = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (e >= E) return;
+    typename F::Scalar c[F::GV * F::U];
+    f.graphContrib(e, dir, c);
+#pragma unroll
+    for (int k = 0; k < F::GV * F::U; ++k) contrib[e * (F::GV * F::U) + k] = c[k];
+}
+// PCGStep1 + PCGStep1_Graph, part 2: the vertex terms plus the sum of the vertex' incident partials (sorted by vertex, then by
+// edge-slot id: a fixed summation order), Ap written once, alphaDenominator = <p, Ap> from the same pass
+template <class F, bool LM>
+__global__ void k_apply_jtj_seg(F f, TileGrid tg, VecOf<F> dir, VecOf<F> out, VecOf<F> CtC, const int* __restrict__ off,
+                                const unsigned* __restrict__ ids, const typename F::Scalar* __restrict__ contrib, double* den, double* zero_slot) {
+    using T = typename F::Scalar;
+    constexpr int U = F::U;
+    int x, y, z; long s;
+    double acc = 0.0;
+    if (zero_slot && blockIdx.x == 0 && linear_tid() == 0) *zero_slot = 0.0;
+    OPTK_TILE_LOOP(tg)
+    if (thread_site(f, tg, tile_, x, y, z, s) && !f.exclude(x, y, z, s)) {
+        T o[U];
+        f.applyJTJ(x, y, z, s, dir, o);
+        for (int i = off[s]; i < off[s + 1]; ++i) {
+            const T* row = contrib + (long)ids[i] * U;
+#pragma unroll
+            for (int u = 0; u < U; ++u) o[u] += row[u];
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const T pv = dir(u, s);
+            if (LM) o[u] += CtC(u, s) * pv;
+            out(u, s) = o[u];
+            acc += (double)(pv * o[u]);
+        }
+    }
+    block_accumulate(acc, den);
+}
+
 // ------------------------------------------------------------------------------ graph terms as a gather
 // Instead of one global atomicAdd per edge and channel (the reference, o.t:2586-2600), J^T J p over the
 // graph domain is gathered per vertex: at Init the engine sorts every (edge, slot) incidence by
@@ -1084,7 +1133,7 @@ struct Engine : OptK_Plan {
         }
         // the gather kernel is issue-bound: forming z + beta p for every neighbour costs what the separate PCGStep3 pass costs
         // (arap 1 M vertices: 0.0683 ms fused vs 0.0535 + 0.0148 ms; r1s), so it stays unfused unless OPTB200_GATHER_FUSED is set
-        if (getenv("OPTB200_NO_FUSE") || !F::FUSE_STEP3 || (use_gather() && !getenv("OPTB200_GATHER_FUSED"))) fuse = false;
+        if (getenv("OPTB200_NO_FUSE") || !F::FUSE_STEP3 || (use_gather() && !getenv("OPTB200_GATHER_FUSED")) || use_seg()) fuse = false;
         OPTK_CUDA(cudaMalloc(&scal, S_COUNT * sizeof(double)));
         OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
         OPTK_CUDA(cudaMallocHost(&h_scal, S_COUNT * sizeof(double)));
@@ -1110,6 +1159,7 @@ struct Engine : OptK_Plan {
         if (comm) ncclCommDestroy(comm);
         release_materialized(); m_tmp.release();
         cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFreeHost(lm_box); cudaFree(active4); cudaFree(mask_changed);
+        cudaFree(seg_ids); cudaFree(seg_off); cudaFree(seg_contrib);
         cudaFree(inc); cudaFree(inc_off); cudaFree(inc_count); cudaFree(sort_tmp); cudaFree(key_a); cudaFree(key_b); cudaFree(val_a);
         base_destroy();
     }
@@ -1441,6 +1491,33 @@ struct Engine : OptK_Plan {
         }
     }
     bool use_gather() const { return F::HAS_GATHER && getenv("OPTB200_GRAPH_ATOMICS") == nullptr; }
+    // segmented scatter of the hyper-edge energies: (edge, slot) ids sorted by vertex, offsets per vertex, partial rows
+    bool use_seg() const { return F::HAS_SEGSCATTER && GRAPH && getenv("OPTB200_GRAPH_ATOMICS") == nullptr; }
+    unsigned* seg_ids = nullptr; int* seg_off = nullptr; T* seg_contrib = nullptr;
+    void build_segments() {
+        if constexpr (F::HAS_SEGSCATTER) {
+            const long n = E * F::GV;
+            if (!seg_off) {
+                OPTK_CUDA(cudaMalloc(&seg_ids, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
+                OPTK_CUDA(cudaMalloc(&seg_off, (size_t)(N + 1) * sizeof(int)));
+                OPTK_CUDA(cudaMalloc(&seg_contrib, (size_t)std::max<long>(n, 1) * U * sizeof(T)));
+                OPTK_CUDA(cudaMalloc(&key_a, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
+                OPTK_CUDA(cudaMalloc(&key_b, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
+                OPTK_CUDA(cudaMalloc(&val_a, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
+                cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp_bytes, key_a, key_b, val_a, seg_ids, (int)n);
+                OPTK_CUDA(cudaMalloc(&sort_tmp, sort_tmp_bytes));
+            }
+            int vbits = 1;
+            while ((1L << vbits) < N) ++vbits;
+            if (n > 0) {
+                this->launch("graphSegmentKeys", dim3((unsigned)((n + 255) / 256)), dim3(256), k_segment_keys<F>, f, n, key_a, val_a);
+                this->pre_launch("graphSegmentSort");
+                cub::DeviceRadixSort::SortPairs(sort_tmp, sort_tmp_bytes, key_a, key_b, val_a, seg_ids, (int)n, 0, vbits, stream);   // stable
+                this->post_launch();
+            }
+            this->launch("graphSegmentOffsets", dim3((unsigned)((n + 1 + 255) / 256)), dim3(256), k_incidence_offsets, (const unsigned*)key_b, n, N, seg_off);
+        }
+    }
 
     void precompute() override {
         if constexpr (F::HAS_CUSTOM_PRECOMPUTE) {           // functor owns a table in its own layout
@@ -1505,6 +1582,7 @@ struct Engine : OptK_Plan {
     void pcg_begin(int nIter) override {
         OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
         if (nIter == 0 && use_gather()) build_incidence();
+        if (nIter == 0 && use_seg()) build_segments();
         active_groups();                                    // Exclude() may read inputs the caller changed
         bool fast_init = false;
         if constexpr (F::HAS_FAST_INIT) {
@@ -1541,6 +1619,14 @@ struct Engine : OptK_Plan {
                 const long nb = (N + 127) / 128;
                 if (lm) this->launch_tiles(name, nb, dim3(128), k_gather_jtj<F, true>, f, N, (const int*)inc_off, (const unsigned*)inc, dir, out, CtC, den, zero_slot);
                 else    this->launch_tiles(name, nb, dim3(128), k_gather_jtj<F, false>, f, N, (const int*)inc_off, (const unsigned*)inc, dir, out, CtC, den, zero_slot);
+                return;
+            }
+        }
+        if constexpr (F::HAS_SEGSCATTER) {
+            if (use_seg()) {
+                if (E > 0) this->launch(gname, edge_grid(), dim3(256), k_graph_contrib<F>, f, E, dir, seg_contrib);
+                if (lm) this->launch_tiles(name, tg.n, sblock, k_apply_jtj_seg<F, true>, f, tg, dir, out, CtC, (const int*)seg_off, (const unsigned*)seg_ids, (const T*)seg_contrib, den, zero_slot);
+                else    this->launch_tiles(name, tg.n, sblock, k_apply_jtj_seg<F, false>, f, tg, dir, out, CtC, (const int*)seg_off, (const unsigned*)seg_ids, (const T*)seg_contrib, den, zero_slot);
                 return;
             }
         }
@@ -1770,6 +1856,7 @@ struct Engine : OptK_Plan {
         OPTK_CUDA(cudaMemsetAsync(Ap.d, 0, tmp.size() * sizeof(T), stream));
         bool saved = lm; lm = false;
         if (use_gather()) build_incidence();
+        if (use_seg()) build_segments();
         if (mat_mode) materialize(0);
         apply_A("PCGStep1", "PCGStep1_Graph", p, Ap, S(S_DUMMY), nullptr);
         lm = saved;
@@ -1792,6 +1879,7 @@ struct FunctorDefaults {
     static constexpr bool HAS_FAST_PRECOMPUTE = false;   // ... and precompute (fast_precompute(stream, nsm))
     static constexpr bool SLAB_OK = true;                // grid functors whose bounds predicates survive a slab cut
     static constexpr bool HAS_GATHER = false;            // graph functors with a per-vertex gather form of J^T J p
+    static constexpr bool HAS_SEGSCATTER = false;        // graph functors whose J^T J scatter runs as a segmented sum (graph_generic.cuh)
     static constexpr bool HAS_ROWS_J = false;            // functors that emit their Jacobian rows (materialized-J mode, csr.cuh RowSink)
     static constexpr int MAT_ROWS = 0, MAT_GROWS = 0;    // residual rows per site / per edge
     static constexpr int VEC_UB = 0;                     // solver-vector layout: 0 = SoA, U = blocked (common.cuh, Vec)

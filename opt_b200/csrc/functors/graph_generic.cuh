@@ -6,8 +6,12 @@
 //                            unknowns of those vertices (slot-major)
 // and inherits every function the engine needs (the reference generates them from the energy: cost o.t:3119-3129,
 // evalJTF o.t:2870-2913 / 2969-2994, applyJTJ o.t:2770-2867, modelcost o.t:2915-2966, computeCtC o.t:2996-3057).
-// Graph scatters use one atomicAdd per non-zero partial like the reference (o.t:2586-2600); entries of J that are
-// structurally zero are compile-time zeros after inlining, the rest is skipped at run time when exactly 0.
+// J^T J p over the graph domain is a SEGMENTED scatter (engine.cuh, build_segments / k_graph_contrib / k_apply_jtj_seg): the
+// edge kernel stores the partial of every (edge, slot) into its own row of a buffer and the vertex kernel adds up the rows
+// of its incidences, which were sorted by vertex once per solve -- no atomics, deterministic; the reference issues one
+// global atomic per edge, slot and channel (o.t:2586-2600, 2833-2867).  OPTB200_GRAPH_ATOMICS=1 restores that form
+// (graphJTJ below; tests compare the two).  The once-per-nonlinear-iteration scatters (J^T F, CtC) still use atomics.
+// Entries of J that are structurally zero are compile-time zeros after inlining.
 #pragma once
 #include "math.cuh"
 
@@ -135,6 +139,33 @@ struct GraphEnergyBase : FunctorDefaults<T> {
                 if (any) atomicAdd(&out(u, v[s]), a);
             }
         return den;
+    }
+    static constexpr bool HAS_SEGSCATTER = true;
+    // slot-major partials of edge e: contrib[s * U + u] = sum_k J[k][s U + u] (J p)[k]; every entry is written
+    template <class P> __device__ void graphContrib(long e, const P& p, T* contrib) const {
+        long v[GV]; T r[NRE], J[NRE][GV * U]; edge(e, v, r, J);
+        T jp[NRE];
+#pragma unroll
+        for (int k = 0; k < NRE; ++k) jp[k] = T(0);
+#pragma unroll
+        for (int s = 0; s < GV; ++s)
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const T pv = p(u, v[s]);
+#pragma unroll
+                for (int k = 0; k < NRE; ++k) jp[k] += J[k][s * U + u] * pv;
+            }
+#pragma unroll
+        for (int c = 0; c < GV * U; ++c) {
+            T a = T(0);
+#pragma unroll
+            for (int k = 0; k < NRE; ++k) a += J[k][c] * jp[k];
+            contrib[c] = a;
+        }
+    }
+    __device__ long edgeVertex(long e, int slot) const {
+        long v[GV]; T r[NRE], J[NRE][GV * U]; edge(e, v, r, J);
+        return v[slot];
     }
     __device__ T graphModelCost(long e, Vec<T> dl) const {
         long v[GV]; T r[NRE], J[NRE][GV * U]; edge(e, v, r, J);

@@ -361,3 +361,32 @@ def test_plan_reused_with_another_exclude_mask(built, case, mask_index, value):
     # block-level double atomics make two runs agree to rounding, not bit for bit; stale vectors show up at 1e-2 and more
     assert_costs_close(c_reused, c_fresh, False, tol=1e-6)
     assert_unknowns_close(x_reused, x_fresh, False, tol=1e-5)
+
+
+@pytest.mark.parametrize("double", [False, True])
+@pytest.mark.parametrize("case", ["embedded", "cotangent", "robust"])
+def test_graph_segmented_scatter_equals_atomics(built, case, double, monkeypatch):
+    """J^T J p of the hyper-edge energies as a segmented sum over vertex-sorted (edge, slot) partials (the default: no atomicAdd
+    into Ap, deterministic) against the reference's form, one global atomic per edge, slot and channel (OPTB200_GRAPH_ATOMICS=1)."""
+    from opt_b200 import solver as S
+    pr = make(case, double=double)
+    dt = np.float64 if double else np.float32
+    rng = np.random.default_rng(13)
+    U = {"embedded": 12, "cotangent": 3, "robust": None}[case]
+    sol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=double, timing=True)
+    U = sol.unknown_channels()
+    p = rng.standard_normal((pr.dims[0], U)).astype(dt)
+    named = S.upload(pr)
+    seg = sol.debug_apply_jtj(named, p)
+    seg2 = sol.debug_apply_jtj(named, p)
+    assert np.array_equal(seg, seg2)                    # fixed summation order: bit-reproducible
+    monkeypatch.setenv("OPTB200_GRAPH_ATOMICS", "1")
+    sol_a = S.OptSolver(pr.dims, pr.energy, pr.kind, double=double)
+    atom = sol_a.debug_apply_jtj(S.upload(pr), p)
+    assert np.abs(seg - atom).max() <= OP_RTOL[double] * np.abs(atom).max()
+    monkeypatch.delenv("OPTB200_GRAPH_ATOMICS")
+    cs, xs, s2, _ = run_gpu(pr, timing=True)
+    assert s2.kernel_time("PCGStep1_Graph")[0] > 0
+    monkeypatch.setenv("OPTB200_GRAPH_ATOMICS", "1")
+    ca, xa, _, _ = run_gpu(pr)
+    assert_costs_close(cs, ca, double, tol=1e-5 if not double else 1e-10)
