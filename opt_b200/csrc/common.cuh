@@ -38,16 +38,53 @@ template <class T, int UB = 0>
 struct Vec {
     T* d;
     long plane;
+    // UB == -U < 0: AoS, the U channels of a site are adjacent ([site][u]).  For graph functors whose J^T J kernel GATHERS the
+    // direction of a vertex' neighbours (arap): a neighbour is one 24-byte record (1-2 sectors) instead of U sectors in U planes.
     __device__ __forceinline__ static long index(int u, long s, long plane) {
         if constexpr (UB == 0) return (long)u * plane + s;
-        else return (s >> 5) * (32 * UB) + u * 32 + (s & 31);
+        else if constexpr (UB > 0) return (s >> 5) * (32 * UB) + u * 32 + (s & 31);
+        else return s * (-UB) + u;
     }
     __device__ __forceinline__ T& operator()(int u, long s) const { return d[index(u, s, plane)]; }
     static long host_index(int u, long s, long plane) {
         if (UB == 0) return (long)u * plane + s;
-        return (s >> 5) * (32 * UB) + u * 32 + (s & 31);
+        if (UB > 0) return (s >> 5) * (32 * UB) + u * 32 + (s & 31);
+        return s * (-UB) + u;
     }
 };
+
+// all U channels of a site: generic accessors (SoA / blocked / lazily fused directions) read them one by one, the AoS
+// layout with 64-bit (float) / 128-bit (double) accesses
+template <int U, class P, class T> __device__ __forceinline__ void load_channels(const P& p, long s, T* o) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) o[u] = p(u, s);
+}
+template <int U> __device__ __forceinline__ void load_channels(const Vec<float, -U>& p, long s, float* o) {
+    static_assert(U % 2 == 0, "AoS rows of an even number of floats");
+    const float2* q = reinterpret_cast<const float2*>(p.d + s * U);
+#pragma unroll
+    for (int k = 0; k < U / 2; ++k) { const float2 v = q[k]; o[2 * k] = v.x; o[2 * k + 1] = v.y; }
+}
+template <int U> __device__ __forceinline__ void load_channels(const Vec<double, -U>& p, long s, double* o) {
+    static_assert(U % 2 == 0, "AoS rows of an even number of doubles");
+    const double2* q = reinterpret_cast<const double2*>(p.d + s * U);
+#pragma unroll
+    for (int k = 0; k < U / 2; ++k) { const double2 v = q[k]; o[2 * k] = v.x; o[2 * k + 1] = v.y; }
+}
+template <int U, class V, class T> __device__ __forceinline__ void store_channels(const V& p, long s, const T* o) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) p(u, s) = o[u];
+}
+template <int U> __device__ __forceinline__ void store_channels(const Vec<float, -U>& p, long s, const float* o) {
+    float2* q = reinterpret_cast<float2*>(p.d + s * U);
+#pragma unroll
+    for (int k = 0; k < U / 2; ++k) q[k] = make_float2(o[2 * k], o[2 * k + 1]);
+}
+template <int U> __device__ __forceinline__ void store_channels(const Vec<double, -U>& p, long s, const double* o) {
+    double2* q = reinterpret_cast<double2*>(p.d + s * U);
+#pragma unroll
+    for (int k = 0; k < U / 2; ++k) q[k] = make_double2(o[2 * k], o[2 * k + 1]);
+}
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll

@@ -293,6 +293,14 @@ struct FusedDir {
     T beta;
     __device__ __forceinline__ T operator()(int u, long s) const { return z(u, s) + beta * p(u, s); }
 };
+// all channels of the fused direction at a site of AoS vectors: two vectorised record reads instead of 2 U scalar ones
+template <int U, class T> __device__ __forceinline__ void load_channels(const FusedDir<Vec<T, -U>, T>& d, long s, T* o) {
+    T a[U], b[U];
+    load_channels<U>(d.z, s, a);
+    load_channels<U>(d.p, s, b);
+#pragma unroll
+    for (int u = 0; u < U; ++u) o[u] = a[u] + d.beta * b[u];
+}
 template <class F, bool LM>
 __global__ void k_apply_jtj_fused(F f, TileGrid tg, VecOf<F> z, VecOf<F> p_old,
                                   VecOf<F> p_new, VecOf<F> out,
@@ -628,16 +636,16 @@ __global__ void __launch_bounds__(128, sizeof(typename F::Scalar) == 4 ? 5 : 2) 
     double acc = 0.0;
     if (zero_slot && blockIdx.x == 0 && threadIdx.x == 0) *zero_slot = 0.0;
     for (long v = blockIdx.x * (long)blockDim.x + threadIdx.x; v < N; v += (long)gridDim.x * blockDim.x) {
-        T o[U];
+        T o[U], pv[U];
         f.gatherJTJ(v, off + v, inc, dir, o);
+        load_channels<U>(dir, v, pv);
         T dsum = T(0);
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const T pv = dir(u, v);
-            if (LM) o[u] += CtC(u, v) * pv;
-            out(u, v) = o[u];
-            dsum += pv * o[u];
+            if (LM) o[u] += CtC(u, v) * pv[u];
+            dsum += pv[u] * o[u];
         }
+        store_channels<U>(out, v, o);
         acc += (double)dsum;
     }
     block_accumulate(acc, den);
@@ -659,17 +667,17 @@ __global__ void __launch_bounds__(128, sizeof(typename F::Scalar) == 4 ? 5 : 2) 
         if (zero_b) *zero_b = 0.0;
     }
     for (long v = blockIdx.x * (long)blockDim.x + threadIdx.x; v < N; v += (long)gridDim.x * blockDim.x) {
-        T o[U];
+        T o[U], pv[U];
         f.gatherJTJ(v, off + v, inc, dir, o);
+        load_channels<U>(dir, v, pv);
+        store_channels<U>(p_new, v, pv);
         T dsum = T(0);
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const T pv = dir(u, v);
-            p_new(u, v) = pv;
-            if (LM) o[u] += CtC(u, v) * pv;
-            out(u, v) = o[u];
-            dsum += pv * o[u];
+            if (LM) o[u] += CtC(u, v) * pv[u];
+            dsum += pv[u] * o[u];
         }
+        store_channels<U>(out, v, o);
         acc += (double)dsum;
     }
     block_accumulate(acc, den);
@@ -1831,7 +1839,9 @@ struct Engine : OptK_Plan {
         if (!v || !v->d || s0 < 0 || n < 0 || s0 + n > N) return -1;
         OPTK_CUDA(cudaStreamSynchronize(stream));
         T* o = (T*)host_out;
-        if (F::VEC_UB == 0) {
+        if (F::VEC_UB < 0) {
+            OPTK_CUDA(cudaMemcpy(o, v->d + (size_t)s0 * U, (size_t)n * U * sizeof(T), cudaMemcpyDeviceToHost));
+        } else if (F::VEC_UB == 0) {
             std::vector<T> tmp((size_t)n);
             for (int u = 0; u < U; ++u) {
                 OPTK_CUDA(cudaMemcpy(tmp.data(), v->d + (size_t)u * Npad + s0, (size_t)n * sizeof(T), cudaMemcpyDeviceToHost));
@@ -1882,7 +1892,7 @@ struct FunctorDefaults {
     static constexpr bool HAS_SEGSCATTER = false;        // graph functors whose J^T J scatter runs as a segmented sum (graph_generic.cuh)
     static constexpr bool HAS_ROWS_J = false;            // functors that emit their Jacobian rows (materialized-J mode, csr.cuh RowSink)
     static constexpr int MAT_ROWS = 0, MAT_GROWS = 0;    // residual rows per site / per edge
-    static constexpr int VEC_UB = 0;                     // solver-vector layout: 0 = SoA, U = blocked (common.cuh, Vec)
+    static constexpr int VEC_UB = 0;                     // solver-vector layout: 0 = SoA, U = blocked, -U = AoS (common.cuh, Vec)
     static constexpr bool FUSE_STEP3 = true;             // form p' = z + beta p inside the J^T J kernel (engine.cuh, FusedDir)
     bool fast_ok() const { return false; }
     size_t fast_smem() const { return 0; }                 // dynamic shared memory of the fast J^T J kernel
