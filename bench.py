@@ -303,7 +303,8 @@ def run_ours(args, pr, w, rank, world, mode):
     for i, p in enumerate(pr.params):
         named.set("p%d" % i, devt[i] if i in devt else p)
     from opt_b200 import slab
-    sol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=pr.double, verbosity=0, timing=False)
+    mat = dict(materialized=args.materialized > 0, fused_jtj=args.materialized == 2)
+    sol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=pr.double, verbosity=0, timing=False, **mat)
     if mode:
         slab.setup_slab(sol, rank, world, 1)
     sol.set_solver_parameters(pr.solver)
@@ -418,7 +419,7 @@ def run_ours(args, pr, w, rank, world, mode):
     # per-kernel time of the dominant kernel, measured live with the library's cudaEvent timer
     roof = None
     if rank == 0 or mode:
-        tsol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=pr.double, verbosity=0, timing=True)
+        tsol = S.OptSolver(pr.dims, pr.energy, pr.kind, double=pr.double, verbosity=0, timing=True, **mat)
         if mode:
             slab.setup_slab(tsol, rank, world, 1)
         tsol.set_solver_parameters(pr.solver)
@@ -431,7 +432,8 @@ def run_ours(args, pr, w, rank, world, mode):
             while tsol.step():
                 pass
         torch.cuda.synchronize()
-        kt = {k: tsol.kernel_time(k) for k in ("PCGStep1", "PCGStep3+1", "PCGStep1_Graph", "PCGStep2", "PCGStep3", "PCGInit1", "computeCost")}
+        kt = {k: tsol.kernel_time(k) for k in ("PCGStep1", "PCGStep3+1", "PCGStep1_Graph", "PCGStep2", "PCGStep3", "PCGInit1", "computeCost",
+                                               "Jp", "J^T", "J^TJp", "PCGStep1_Finish", "saveJToCRS", "J_transpose", "JTJ multiply")}
         # PCG iterations one solve REALLY runs (LM leaves the inner loop early on q_tolerance, solver:2180-2200): the
         # metric counts these, not nIter x lIter.  The library counts them as the reference would (the one iteration
         # LM queues ahead of the exit test's verdict is wasted work, not a counted iteration).
@@ -470,6 +472,23 @@ def run_ours(args, pr, w, rank, world, mode):
                     "iteration": {"algorithmic_bytes": it_alg, "achieved": it_alg * it_rate / 1e9,
                                   "frac": it_alg * it_rate / 1e9 / peak,
                                   "survey_formula": {"algorithmic_bytes": it_survey, "frac": it_survey * it_rate / 1e9 / peak}}}
+        if tsol.materialized_mode() and roof is None:
+            # materialized-Jacobian mode: PCGStep1 is one (J^T J) or two (J, J^T) CSR products.  Algorithmic bytes of y = A x:
+            # values + column indices of every entry, the row offsets, x read once and y written once.
+            peak, peak_src = load_peaks()
+            sz = 8 if pr.double else 4
+            ncol = sol.site_count() * w["U"]
+            fusedm = tsol.materialized_mode() == 2
+            nnz = tsol.materialized_nnz(1 if fusedm else 0)
+            names = ["J^TJp"] if fusedm else ["Jp", "J^T"]
+            t_ms = sum(kt[k][1] / kt[k][0] for k in names if kt[k][0])
+            rows = ncol if fusedm else None
+            alg = (nnz * (sz + 4) + (ncol + 1) * 4 + 2 * ncol * sz) if fusedm else 2 * nnz * (sz + 4) + 3 * ncol * sz
+            roof = {"bound": "hbm", "kernel": " + ".join(names) + " (CSR SpMV, materialized Jacobian)", "achieved": alg / (t_ms * 1e-3) / 1e9 if t_ms else None,
+                    "peak": peak, "unit": "GB/s", "frac": alg / (t_ms * 1e-3) / 1e9 / peak if t_ms else None, "traffic": None,
+                    "frac_of_nominal_8TBs": alg / (t_ms * 1e-3) / 1e9 / 8000.0 if t_ms else None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": alg, "ms_per_launch": t_ms, "nnz": nnz,
+                    "kernel_ms": {k: (v[1] / v[0] if v[0] else None) for k, v in kt.items()}}
         tsol.close()
 
     # units: one PCG iteration over one single-GPU-sized grid.  weak slab / replicas: N such units per
@@ -611,6 +630,8 @@ def main():
     ap.add_argument("--size", type=int, nargs="+", default=None, help="override the workload's grid size")
     ap.add_argument("--double", action="store_true", help="run the workload in fp64 (doublePrecision = 1)")
     ap.add_argument("--kind", default=None, choices=["gaussNewtonGPU", "LMGPU"], help="override the workload's solver kind")
+    ap.add_argument("--materialized", type=int, default=0, choices=[0, 1, 2],
+                    help="Opt_InitializationParameters.useMaterializedJTJ (1) + useFusedJTJ (2): PCGStep1 through stored CSR matrices")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
     args = ap.parse_args()

@@ -44,7 +44,7 @@ struct ArapFunctor : FunctorDefaults<T> {
     __device__ unsigned incidence_payload(long e, int slot) const { return (unsigned)(slot == 0 ? v1[e] : v0[e]); }
     // With M_a = sum_j pA_a[j] dR/da_j(A_a): J p of edge a->b is jp_ab = (pO_a - pO_b) - M_a (U_a - U_b);
     //   Ap_O(v) = vf pO_v + w_r^2 ( sum_{v->n} jp_vn - sum_{n->v} jp_nv ),  Ap_A(v)[j] = -w_r^2 <dR/da_j(A_v), sum_{v->n} jp_vn u^T>
-    template <class P> __device__ void gatherJTJ(long v, const int* off, const unsigned* inc, const P& p, T* o) const {
+    template <bool SIMPLE = false, class P> __device__ void gatherJTJ(long v, const int* off, const unsigned* inc, const P& p, T* o) const {
         T tr[TS], pc[6];
 #pragma unroll
         for (int k = 0; k < TS; k += 4) load4(tab + v * TS + k, tr + k);
@@ -81,6 +81,13 @@ struct ArapFunctor : FunctorDefaults<T> {
                 for (int k = 0; k < 3; ++k) acc[k] += q[k] - mu[k];
             }
         };
+        if (SIMPLE) {                                         // no software pipeline: fewer registers, more resident warps
+            for (int i = b0; i < b1; ++i) {
+                const unsigned e = inc[i];
+                fetch(e, tA, qA);
+                eval(e, tA, qA);
+            }
+        } else {
         unsigned e0 = 0, e1 = 0;
         if (b0 < b1) { e0 = inc[b0]; fetch(e0, tA, qA); }
         if (b0 + 1 < b1) e1 = inc[b0 + 1];
@@ -94,6 +101,7 @@ struct ArapFunctor : FunctorDefaults<T> {
             if (i + 3 < b1) e3 = inc[i + 3];
             eval(e1, tB, qB);
             e0 = e2; e1 = e3;
+        }
         }
         const T wr2 = w_reg * w_reg, vf = tr[9] * w_fit * w_fit;
         RotM<T> rm; rm.set(tr);

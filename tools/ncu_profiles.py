@@ -20,7 +20,7 @@ KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio"]
 UNIT = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "us": 1e-6, "ms": 1e-3, "ns": 1e-9, "s": 1.0}
-WORKLOAD = {"poisson": "poisson_4096", "flow": "optical_flow_2048", "sfs": "sfs_2048", "arap": "arap_1m", "vol256": "volumetric_256"}
+WORKLOAD = {"poisson": "poisson_4096", "flow": "optical_flow_2048", "sfs": "sfs_2048", "arap": "arap_1m", "vol256": "volumetric_256", "vol512": "volumetric_512"}
 
 
 def main():
