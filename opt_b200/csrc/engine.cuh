@@ -16,7 +16,6 @@
 #include <vector>
 #include <nccl.h>
 #include <nvtx3/nvToolsExt.h>      // header-only; ranges are no-ops unless a profiler injects itself
-#include <cooperative_groups.h>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_select.cuh>
 #include "common.cuh"
@@ -330,82 +329,6 @@ __global__ void k_apply_jtj_fused(F f, TileGrid tg, VecOf<F> z, VecOf<F> p_old,
         }
     }
     block_accumulate(acc, den);
-}
-
-// The whole Gauss-Newton inner loop (solver:2072-2227) as ONE cooperative kernel, for problems whose solver vectors live in L2
-// (image_warping 512^2 and the like): the multi-kernel loop costs two dependent launches per PCG iteration, ~9 us each on a
-// problem that needs ~3 us of work; here the phases of an iteration are separated by grid-wide barriers instead.  Per
-// iteration: [PCGStep3 fused +] PCGStep1 (Ap, alphaDen) | barrier | PCGStep2 (delta, r, z, betaNum) | barrier.  The arithmetic
-// per element and the scalar rings are those of k_apply_jtj[_fused] / k_pcg_step2; only the order in which the blocks'
-// partial sums reach the double accumulators differs.
-template <class F>
-__global__ void __launch_bounds__(256) k_pcg_coop(F f, TileGrid tg, VecOf<F> delta, VecOf<F> r, VecOf<F> z, VecOf<F> p_a, VecOf<F> p_b,
-                                                  VecOf<F> Ap, VecOf<F> pre, double* scal, int L) {
-    namespace cg = cooperative_groups;
-    using T = typename F::Scalar;
-    constexpr int U = F::U;
-    cg::grid_group grid = cg::this_grid();
-    const bool lead = blockIdx.x == 0 && linear_tid() == 0;
-    VecOf<F> p_cur = p_a, p_nxt = p_b;
-    int x, y, zc; long s;
-    for (int l = 0; l < L; ++l) {
-        double* aNum = scal + S_RZ0 + l % 3;
-        double* bNum = scal + S_RZ0 + (l + 1) % 3;
-        double* aDen = scal + S_ADEN0 + (l & 1);
-        double* nextDen = scal + S_ADEN0 + ((l + 1) & 1);
-        // ---- PCGStep3 of iteration l - 1 folded into PCGStep1 of iteration l
-        {
-            double acc = 0.0;
-            if (lead) *bNum = 0.0;
-            if (l == 0) {
-                OPTK_TILE_LOOP(tg)
-                if (thread_site(f, tg, tile_, x, y, zc, s) && !f.exclude(x, y, zc, s)) {
-                    T o[U];
-                    f.applyJTJ(x, y, zc, s, p_cur, o);
-#pragma unroll
-                    for (int u = 0; u < U; ++u) { Ap(u, s) = o[u]; acc += (double)(p_cur(u, s) * o[u]); }
-                }
-            } else {
-                const double* prevA = scal + S_RZ0 + (l + 2) % 3;
-                FusedDir<VecOf<F>, T> dir{z, p_cur, (T)(*aNum) / (T)(*prevA)};
-                OPTK_TILE_LOOP(tg)
-                if (thread_site(f, tg, tile_, x, y, zc, s) && !f.exclude(x, y, zc, s)) {
-                    T o[U];
-                    f.applyJTJ(x, y, zc, s, dir, o);
-#pragma unroll
-                    for (int u = 0; u < U; ++u) {
-                        const T pv = dir(u, s);
-                        p_nxt(u, s) = pv;
-                        Ap(u, s) = o[u];
-                        acc += (double)(pv * o[u]);
-                    }
-                }
-                VecOf<F> t = p_cur; p_cur = p_nxt; p_nxt = t;
-            }
-            block_accumulate(acc, aDen);
-        }
-        grid.sync();
-        // ---- PCGStep2
-        {
-            const T alpha = (T)(*aNum) / (T)(*aDen);
-            double bacc = 0.0;
-            if (lead) *nextDen = 0.0;
-            OPTK_TILE_LOOP(tg)
-            if (thread_site(f, tg, tile_, x, y, zc, s) && !f.exclude(x, y, zc, s)) {
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    delta(u, s) = delta(u, s) + alpha * p_cur(u, s);
-                    const T rr = r(u, s) - alpha * Ap(u, s);
-                    r(u, s) = rr;
-                    const T zz = F::USE_PRE ? pre(u, s) * rr : rr;
-                    if (F::USE_PRE) z(u, s) = zz;
-                    bacc += (double)(zz * rr);
-                }
-            }
-            block_accumulate(bacc, bNum);
-        }
-        grid.sync();
-    }
 }
 
 // PCGStep1 / computeAdelta (solver:607-632, 873-878): out = (J^T J [+ CtC]) dir over non-excluded sites
@@ -1828,33 +1751,12 @@ struct Engine : OptK_Plan {
         // fused mode: PCGStep3 of this iteration happens inside the next iteration's first kernel; after
         // the last iteration its result (the next search direction) is never used (solver:2203-2227)
     }
-    // problems whose seven solver vectors fit L2 several times over run the GN inner loop as one cooperative kernel
-    bool coop_ok() const {
-        return !GRAPH && !lm && nranks == 1 && F::VEC_UB == 0 && !mat_mode && !timing &&
-               (long)U * Npad * (long)sizeof(T) * 8 <= (24L << 20) && getenv("OPTB200_NO_COOP") == nullptr;
-    }
+    // (A cooperative single-kernel form of this loop -- grid-wide barriers instead of two launches per iteration -- was built
+    // and measured in r2o on image_warping 512^2: 18.64 us per PCG iteration against 18.59 us for the launches below.  That
+    // problem is bound by the sincos arithmetic of its generic J^T J functor, not by launch latency, so the kernel was removed.)
     void pcg_run(int lIterations) override {
-        if (coop_ok() && lIterations > 0) {
-            if (coop_grid == 0) {
-                int nb = 0, dev = 0, can = 0;
-                cudaGetDevice(&dev);
-                cudaDeviceGetAttribute(&can, cudaDevAttrCooperativeLaunch, dev);
-                OPTK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_pcg_coop<F>, 256, 0));
-                coop_grid = can && nb > 0 ? (int)std::min<long>(tg.n, (long)nsm * std::min(nb, 4)) : -1;
-            }
-            if (coop_grid > 0) {
-                int L = lIterations;
-                void* args[] = {&f, &tg, &delta, &r, &z, &p, &p_alt, &Ap, &pre, &scal, &L};
-                this->pre_launch("PCGLoop_Cooperative");
-                OPTK_CUDA(cudaLaunchCooperativeKernel((const void*)k_pcg_coop<F>, dim3((unsigned)coop_grid), sblock, args, 0, stream));
-                this->post_launch();
-                if ((lIterations - 1) & 1) std::swap(p.d, p_alt.d);      // the kernel ping-pongs p once per fused iteration
-                return;
-            }
-        }
         for (int l = 0; l < lIterations; ++l) pcg_iter(l, 0);
     }
-    int coop_grid = 0;
     // LM inner loop (solver:2072-2201) without a blocking fetchQ per iteration.  The exit test runs on the
     // device (k_lm_zeta); the host queues iteration l+1 BEFORE it looks at the verdict of iteration l, so the
     // GPU never waits for the host.  If iteration l fired the test, iteration l+1 is already in the stream: its
