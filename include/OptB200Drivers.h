@@ -29,6 +29,17 @@ extern "C" {
  * the image.  `scratch` holds W*H floats. */
 int OptB200_FilterGaussian(float* image, unsigned W, unsigned H, float sigma, float* scratch, void* stream);
 
+/* The same filter without any allocation and without a caller-owned scratch image, for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+ * The intermediate image of the row pass lives in a static device array inside the
+ * library, OPTB200_GAUSS_NOALLOC_MAX_PIXELS floats (16 MiB per GPU that loads the library, held until the process exits);
+ * W * H beyond that is rejected with cudaErrorInvalidValue and a message on stderr.  Calls no cudaMalloc / cudaFree and no
+ * allocating library routine; same kernels and bit-identical output as OptB200_FilterGaussian.  All calls on a device share
+ * the array (nothing in it needs clearing between calls: the row pass rewrites all that the column pass reads), so calls
+ * that overlap on the GPU -- different streams, concurrently replayed graphs -- race: serialise them. */
+#define OPTB200_GAUSS_NOALLOC_MAX_PIXELS (2048L * 2048L)
+int OptB200_FilterGaussianNoAlloc(float* image, unsigned W, unsigned H, float sigma, void* stream);
+
 /* 3x3 Prewitt derivative / 8 along x (DU) or y (DV); the one-pixel border of the output is 0. */
 int OptB200_PrewittDU(const float* image, float* out, unsigned W, unsigned H, void* stream);
 int OptB200_PrewittDV(const float* image, float* out, unsigned W, unsigned H, void* stream);

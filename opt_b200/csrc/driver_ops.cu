@@ -4,6 +4,8 @@
 // All of them are memory-bound image passes.  Arithmetic uses the explicit round-to-nearest intrinsics
 // (__fmul_rn / __fadd_rn / __fsub_rn / __fdiv_rn), which the compiler never contracts into FMAs, in the
 // reference's order of operations: the outputs are the ones a plain C++ build of the driver code produces.
+#include <cstdio>
+#include <mutex>
 #include <cuda_runtime.h>
 #include <cmath>
 #include <vector>
@@ -239,6 +241,46 @@ int OptB200_FilterGaussian(float* image, unsigned W, unsigned H, float sigma, fl
     k_gauss_rows<<<dim3((W + ROW_PX - 1) / ROW_PX, H), 256, (ROW_PX + 2 * R) * sizeof(float), st>>>(image, scratch, (int)W, (int)H, R, gk);
     k_gauss_cols<<<dim3((W + 31) / 32, (H + COL_ROWS - 1) / COL_ROWS), dim3(32, 8), (COL_ROWS + 2 * R) * 32 * sizeof(float), st>>>(scratch, image, (int)W, (int)H, R, gk);
     return done();
+}
+
+// ---- OptB200_FilterGaussianNoAlloc: the same filter for callers that can neither allocate nor hand over a scratch image
+// (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The row pass's intermediate image lives in a file-scope device array of a fixed maximum
+// size (OPTB200_GAUSS_NOALLOC_MAX_PIXELS floats = 16 MiB, held by every GPU that loads the library until the process exits).
+// In HOST code the array's name is only a stand-in for the symbol, not a device address: its address is taken once per
+// device, with that device current, by cudaGetSymbolAddress, and that pointer is what the kernels get.  The row pass writes
+// every element of the scratch image that the column pass reads, so nothing has to be cleared between calls; all calls share
+// the array, so two calls that overlap on the GPU (different streams, or graphs replayed concurrently) race.
+static __device__ __align__(256) float g_gauss_scratch[OPTB200_GAUSS_NOALLOC_MAX_PIXELS];
+static float* g_gauss_scratch_ptr[64];                         // per device ordinal; nullptr = address not taken yet
+static std::mutex g_gauss_scratch_mutex;
+
+int OptB200_FilterGaussianNoAlloc(float* image, unsigned W, unsigned H, float sigma, void* stream) {
+    if (W == 0 || H == 0) return (int)cudaErrorInvalidValue;
+    if ((unsigned long long)W * H > (unsigned long long)OPTB200_GAUSS_NOALLOC_MAX_PIXELS) {
+        fprintf(stderr, "OptB200_FilterGaussianNoAlloc: image of %u x %u pixels exceeds the static scratch of %ld pixels "
+                        "(use OptB200_FilterGaussian with a caller-owned scratch image)\n", W, H, (long)OPTB200_GAUSS_NOALLOC_MAX_PIXELS);
+        return (int)cudaErrorInvalidValue;
+    }
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+    float* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_gauss_scratch_mutex);
+        if (!g_gauss_scratch_ptr[dev]) {                       // set-up, once per device, with that device current
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_gauss_scratch);
+            if (e != cudaSuccess) {
+                fprintf(stderr, "OptB200_FilterGaussianNoAlloc: cudaGetSymbolAddress failed on device %d: %s\n", dev, cudaGetErrorString(e));
+                return (int)e;
+            }
+            g_gauss_scratch_ptr[dev] = (float*)p;
+        }
+        scratch = g_gauss_scratch_ptr[dev];
+    }
+    return OptB200_FilterGaussian(image, W, H, sigma, scratch, stream);     // two kernel launches, no allocation
 }
 
 int OptB200_PrewittDU(const float* image, float* out, unsigned W, unsigned H, void* stream) {

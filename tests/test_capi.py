@@ -16,8 +16,10 @@ def declared_symbols(header):
 
 def test_library_exports_every_declared_symbol(built):
     lib = C.CDLL(built)
-    names = declared_symbols("Opt.h") + declared_symbols("OptB200.h")
-    assert len(names) >= 10 + 6
+    names = []
+    for header in sorted(os.listdir(os.path.join(ROOT, "include"))):          # every include/*.h, not only the two solver headers
+        names += declared_symbols(header)
+    assert len(names) >= 10 + 6 and "OptB200_FilterGaussianNoAlloc" in names and "OptB200_CsrSpmv" in names
     for n in names:
         assert hasattr(lib, n), n
 
