@@ -73,6 +73,17 @@ WORKLOADS = {
     "arap_1m": dict(builder=examples.arap_synthetic, args=(1024, 1024), kw=dict(n_iter=2, l_iter=100),
                     U=6, ijtj=9, iexcl=0, extra=48, mask=None, ref_sample=(192, 192),
                     desc="arap_mesh_deformation 1024x1024-vertex mesh (6.28M directed edges), GN 2x100 PCG, fp32"),
+    # the other three graph energies (hyper-edge terms as a segmented scatter, engine.cuh k_graph_contrib / k_apply_jtj_seg).
+    # ijtj = input channels J^T J reads per vertex; extra = bytes of index arrays per vertex (GV arrays x 4 B x ~6 edges)
+    "embedded_1m": dict(builder=examples.embedded_synthetic, args=(1024, 1024), kw=dict(n_iter=2, l_iter=50),
+                        U=12, ijtj=15, iexcl=0, extra=48, mask=None, ref_sample=(128, 128),
+                        desc="embedded_mesh_deformation 1024x1024-vertex mesh (6.28M directed edges), GN 2x50 PCG, fp32"),
+    "cotangent_1m": dict(builder=examples.cotangent_synthetic, args=(1024, 1024), kw=dict(n_iter=2, l_iter=50),
+                         U=3, ijtj=3, iexcl=0, extra=96, mask=None, ref_sample=(128, 128),
+                         desc="cotangent_mesh_smoothing 1024x1024-vertex mesh (6.28M 4-vertex hyper-edges), GN 2x50 PCG, fp32"),
+    "robust_1m": dict(builder=examples.robust_synthetic, args=(1024, 1024), kw=dict(n_iter=2, l_iter=50, kind="LMGPU"),
+                      U=7, ijtj=16, iexcl=0, extra=48, mask=None, ref_sample=(128, 128),
+                      desc="robust_nonrigid_alignment 1024x1024-vertex mesh (6.28M directed edges), LM 2x50 PCG, fp32"),
 }
 
 
@@ -218,7 +229,12 @@ def cpu_pcg_rate(pr, threads, budget_s=20.0):
     return rate, sample, l2, costs, solved
 
 
+CPU_THREADS = 0          # --cpu-threads
+
+
 def host_threads():
+    if CPU_THREADS > 0:
+        return CPU_THREADS
     try:
         return len(os.sched_getaffinity(0))
     except Exception:
@@ -443,6 +459,9 @@ def run_ours(args, pr, w, rank, world, mode):
         # the J^T J apply runs either as PCGStep1 or fused with the previous iteration's PCGStep3
         n1, t1 = kt["PCGStep3+1"] if kt["PCGStep3+1"][0] else kt["PCGStep1"]
         fused = kt["PCGStep3+1"][0] > 0
+        two_pass = not fused and n1 > 0 and kt["PCGStep1_Graph"][0] == n1      # graph energies: edge pass + vertex pass = one J^T J apply
+        if two_pass:
+            t1 += kt["PCGStep1_Graph"][1]
         peak, peak_src = load_peaks()
         N = sol.site_count()
         m = w["mask"]
@@ -461,7 +480,7 @@ def run_ours(args, pr, w, rank, world, mode):
             it_alg = alg_bytes(iter_words, 3 * w["iexcl"]) + w["extra"] * N
             it_rate = iters * args.steps / (ms * 1e-3)
             it_survey = sz * N * (iter_words + 3 * w["iexcl"]) + w["extra"] * N
-            roof = {"bound": "hbm", "kernel": "PCGStep3+PCGStep1 (fused)" if fused else "PCGStep1",
+            roof = {"bound": "hbm", "kernel": "PCGStep3+PCGStep1 (fused)" if fused else ("PCGStep1_Graph + PCGStep1" if two_pass else "PCGStep1"),
                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                     "traffic": (NCU_TRAFFIC.get(args.workload + ("_f64" if pr.double else "")) or {}).get("bytes_per_launch") if world == 1 and not args.size else None,
                     "traffic_source": (NCU_TRAFFIC.get(args.workload + ("_f64" if pr.double else "")) or {}).get("capture"),
@@ -634,7 +653,10 @@ def main():
                     help="Opt_InitializationParameters.useMaterializedJTJ (1) + useFusedJTJ (2): PCGStep1 through stored CSR matrices")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
+    ap.add_argument("--cpu-threads", type=int, default=0, help="threads of the cpu_baseline / reference legs (0 = all host cores; 1 = the serial backend_cpu row)")
     args = ap.parse_args()
+    global CPU_THREADS
+    CPU_THREADS = args.cpu_threads
     load_traffic()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))

@@ -27,8 +27,15 @@ for w in optical_flow_2048 sfs_2048; do
   run ${w}_kindLMGPUdouble --workload $w --kind LMGPU --double
 done
 run arap_1m --workload arap_1m
+run embedded_1m --workload embedded_1m
+run cotangent_1m --workload cotangent_1m
+run robust_1m --workload robust_1m
+# the serial CPU row BASELINE.md section 4 promises (backend_cpu semantics: one thread), on the default workload's sample
+run volumetric_512_cpu1 --cpu-threads 1 --steps 2 --warmup 1
 run image_warping_512 --workload image_warping_512
 run volumetric_256 --workload volumetric_256
+timeout 600 python bench.py --impl reference --steps 3 --warmup 1 2>/dev/null | tail -1 > $OUT/${TAG}_bench_reference_arm.json
+cat $OUT/${TAG}_bench_reference_arm.json | cut -c1-300
 # materialized-Jacobian modes: PCGStep1 through the CSR kernels, SpMV roofline in the line
 run poisson_1024_materialized --workload poisson_4096 --size 1024 1024 --materialized 1 --no-cpu
 run poisson_1024_fusedjtj --workload poisson_4096 --size 1024 1024 --materialized 2 --no-cpu
