@@ -23,7 +23,14 @@ int OptB200_ImageDumpRead(const char* path, int clamp_infinity, OptB200_ImageDum
         return E_FORMAT;
     }
     const size_t elem = hdr[3] == 0 ? sizeof(float) : 1;
-    const size_t count = (size_t)hdr[0] * (size_t)hdr[1] * (size_t)hdr[2];
+    /* three untrusted 31-bit factors: their product overflows size_t.  Bound it by what the file can hold before malloc. */
+    long here = ftell(f), end = -1;
+    if (here >= 0 && fseek(f, 0, SEEK_END) == 0) { end = ftell(f); if (fseek(f, here, SEEK_SET) != 0) end = -1; }
+    if (here < 0 || end < here) { fclose(f); return E_FORMAT; }
+    const unsigned long long avail = (unsigned long long)(end - here) / elem;
+    const unsigned long long wh = (unsigned long long)hdr[0] * (unsigned long long)hdr[1];        /* < 2^62 */
+    if (wh > avail || wh * (unsigned long long)hdr[2] > avail) { fclose(f); return E_FORMAT; }
+    const size_t count = (size_t)(wh * (unsigned long long)hdr[2]);
     void* data = malloc(count * elem);
     if (!data) { fclose(f); return E_MEMORY; }
     if (fread(data, elem, count, f) != count) { free(data); fclose(f); return E_FORMAT; }
@@ -245,7 +252,10 @@ static int read_ply(char* txt, size_t len, int* nv_out, float** v_out, int* nf_o
 static int read_off(char* txt, int* nv_out, float** v_out, int* nf_out, int** f_out) {
     /* drop comments */
     for (char* c = txt; *c; ++c)
-        if (*c == '#') while (*c && *c != '\n') *c++ = ' ';
+        if (*c == '#') {
+            while (*c && *c != '\n') *c++ = ' ';
+            if (!*c) break;                                   /* comment ran to the end of the file: do not step past the NUL */
+        }
     char* cur = txt;
     while (isspace((unsigned char)*cur)) ++cur;
     if (strncmp(cur, "OFF", 3) != 0) return E_FORMAT;

@@ -98,6 +98,16 @@ Opt_Problem* Opt_ProblemDefine(Opt_State* state, const char* filename, const cha
         const int v = optb200_energy_verify(filename, p->energy, why, sizeof(why));
         if (v == -2 && getenv("OPTB200_ALLOW_MODIFIED_ENERGY")) {
             fprintf(stderr, "Opt: warning: energy file '%s': %s (accepted: OPTB200_ALLOW_MODIFIED_ENERGY is set)\n", filename, why);
+        } else if (v == 1) {
+            /* not readable: nothing could be checked.  Say so instead of binding silently (OPTB200_REQUIRE_ENERGY_FILE=1 refuses) */
+            if (getenv("OPTB200_REQUIRE_ENERGY_FILE")) {
+                fprintf(stderr, "Opt: energy file '%s' cannot be read and OPTB200_REQUIRE_ENERGY_FILE is set\n", filename);
+                free(p);
+                return NULL;
+            }
+            if (state->ip.verbosityLevel > 0)
+                fprintf(stderr, "Opt: note: energy file '%s' cannot be read; bound to the built-in functor set '%s' by name, contents unverified\n",
+                        filename, p->energy);
         } else if (v < 0) {
             fprintf(stderr, "Opt: energy file '%s' is not the one the built-in functor set for '%s' implements: %s\n",
                     filename, p->energy, why);

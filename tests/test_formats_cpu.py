@@ -117,3 +117,25 @@ def test_reference_data_files(built, golden_dir):
     v, f = F.read_mesh(REF_DATA + "/raptor_simplify2k.off")
     r = np.load(os.path.join(golden_dir, "embedded_raptor2k.npz"))
     assert np.allclose(v, r["vertices"]) and np.array_equal(f, r["faces"])
+
+
+def test_imagedump_header_that_overflows_is_rejected(tmp_path):
+    """width * height * channels from three unchecked int32 fields must not wrap size_t / outgrow the file."""
+    import struct
+    from opt_b200 import formats as F
+    p = tmp_path / "bad.imagedump"
+    p.write_bytes(struct.pack("<4i", 0x7fffffff, 0x7fffffff, 8, 0) + b"\0" * 64)
+    with pytest.raises(OSError):
+        F.read_imagedump(str(p))
+    p.write_bytes(struct.pack("<4i", 4, 4, 1, 0) + b"\0" * 60)            # one float short of 4 x 4
+    with pytest.raises(OSError):
+        F.read_imagedump(str(p))
+
+
+def test_off_comment_at_end_of_file_without_newline(tmp_path):
+    """the comment stripper must stop at the terminator."""
+    from opt_b200 import formats as F
+    p = tmp_path / "m.off"
+    p.write_text("OFF\n3 1 0\n0 0 0\n1 0 0\n0 1 0\n3 0 1 2\n# trailing comment without newline")
+    v, f = F.read_mesh(str(p))
+    assert v.shape == (3, 3) and f.tolist() == [[0, 1, 2]]
