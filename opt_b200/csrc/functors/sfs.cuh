@@ -58,6 +58,7 @@ struct SfsFunctor : FunctorDefaults<T> {
         cudaGetDevice(&dev); cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
         const long slots = (long)nsm * 8 * (sizeof(T) == 4 ? 2 : 1);
         bandR = (int)std::min<long>(256, std::max<long>(8, ((long)H * strips() + slots - 1) / slots));
+        if (const char* e = getenv("OPTB200_SFS_BAND")) bandR = std::max(4, atoi(e));      // measurement hook: band height sweep
     }
     void bind(void** pp) {
         // sqrt(Param(...)): the float parameter is cast to opt_float, then the square root is taken (o.t:2430)

@@ -256,8 +256,12 @@ def cotangent_synthetic(nx, ny, seed=1234, n_iter=3, l_iter=10):
     ys, xs = np.mgrid[0:ny, 0:nx]
     z = 0.1 * np.sin(6.0 * xs / nx) * np.cos(5.0 * ys / ny)
     pos = np.stack([xs / max(nx, ny), ys / max(nx, ny), z], -1).reshape(-1, 3)
-    A = (pos + 0.01 * rng.standard_normal(pos.shape)).astype(f32)
-    X = (A + 0.002 * rng.standard_normal(pos.shape)).astype(f32)
+    # noise relative to the mesh spacing h (0.12 h and 0.024 h: 0.01 / 0.002 on the 12-vertex-wide test meshes).  An absolute 0.01
+    # on a 1024-wide mesh (h = 1e-3) scrambles it into folded triangles, and an unperturbed regular grid has opposite angles of
+    # exactly 90 degrees: both put om = (cot + cot) / 2 on the energy's select(om > 0, om, 1e-4), where fp32 rounding decides
+    h = 1.0 / max(nx, ny)
+    A = (pos + 0.12 * h * rng.standard_normal(pos.shape)).astype(f32)
+    X = (A + 0.024 * h * rng.standard_normal(pos.shape)).astype(f32)
     g = grid_mesh_rings(nx, ny)
     ecount = np.array([len(g[0])], dtype=np.int32)
     return Problem("cotangent_mesh_smoothing.t", [nx * ny, len(g[0])],
