@@ -24,7 +24,8 @@ namespace optk {
 // modelCost, scratch, q; solverGPUGaussNewton.t:213-235).  They are kept in double and are
 // rotated through small rings so the PCG loop needs no memset between kernels:
 //   iteration l:  alphaNum = RZ[l%3], betaNum accumulates into RZ[(l+1)%3], alphaDen = ADEN[l&1]
-enum Scal { S_COST = 0, S_MODEL = 1, S_Q = 2, S_ADEN0 = 3, S_ADEN1 = 4, S_RZ0 = 5, S_RZ1 = 6, S_RZ2 = 7, S_DUMMY = 8, S_QPREV = 9, S_STOP = 10, S_COUNT = 16 };
+enum Scal { S_COST = 0, S_MODEL = 1, S_Q = 2, S_ADEN0 = 3, S_ADEN1 = 4, S_RZ0 = 5, S_RZ1 = 6, S_RZ2 = 7, S_DUMMY = 8, S_QPREV = 9, S_STOP = 10, S_APREV = 11, S_COUNT = 16 };
+// S_APREV: alpha of the previous PCG iteration, kept while its delta update is deferred (k_pcg_step2, DM)
 // S_QPREV / S_STOP: Levenberg-Marquardt inner loop run from the device side (Engine::pcg_run_lm): the previous
 // iteration's q and the "q_tolerance reached" flag that turns the step of a speculatively queued iteration into a no-op.
 

@@ -734,9 +734,16 @@ __global__ void __launch_bounds__(256) k_zero_if(const int* __restrict__ flag, V
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) v[i] = zero;
 }
 
-template <class T, bool USE_PRE, bool LM>
+// DM (Gauss-Newton with the fused PCGStep3+1 kernel only): delta is not read inside the inner loop, and the fused kernel's
+// ping-pong keeps p_l and p_{l-1} both alive, so the update delta += alpha p is applied every SECOND iteration for two
+// directions at once.  DM = 0: delta += alpha p (every iteration);  DM = 1: delta untouched, alpha parked in *aprev;
+// DM = 2: delta = fma(alpha, p, fma(*aprev, p_prev, delta)) -- the same two roundings per element as two DM = 0 passes, so the
+// result is bit-identical -- and 14 instead of 16 vector passes over two iterations (10 instead of 12 without preconditioner).
+// This is the dominant kernel of the big grids by time (512^3: 51.6 % of a solve, profiles/r2m_launches_volumetric512.csv)
+// and runs at the copy peak, so fewer bytes is the only way to make it faster.
+template <class T, bool USE_PRE, bool LM, int DM = 0>
 __global__ void __launch_bounds__(256) k_pcg_step2(long i_begin, long nvec, const unsigned char* __restrict__ active4, long plane,
-                                                   T* __restrict__ delta, const T* __restrict__ p,
+                                                   T* __restrict__ delta, const T* __restrict__ p, const T* __restrict__ p_prev, double* aprev,
                                                    T* __restrict__ r, const T* __restrict__ Ap,
                                                    const T* __restrict__ pre, const T* __restrict__ b,
                                                    T* __restrict__ z, const double* aNum, const double* aDen,
@@ -747,12 +754,15 @@ __global__ void __launch_bounds__(256) k_pcg_step2(long i_begin, long nvec, cons
     // LM: once the q_tolerance test has fired, an iteration that was queued ahead of the host's
     // decision must leave delta untouched (pcg_run_lm); nothing else of it is read afterwards
     const T alpha = (LM && stop && *stop != 0.0) ? T(0) : (T)(*aNum) / (T)(*aDen);
+    const T alpha_prev = DM == 2 ? (T)(*aprev) : T(0);           // written by the previous launch of this kernel (DM = 1)
     if (i0 == 0 && zero_slot) *zero_slot = 0.0;
+    if (DM == 1 && i0 == 0) *aprev = (double)alpha;
     double bacc = 0.0, qacc = 0.0;
     for (long i = i_begin + i0; i < nvec; i += istride)
     if (group_active<T>(active4, i, plane)) {
-        V d = reinterpret_cast<const V*>(delta)[i];
-        V pv = reinterpret_cast<const V*>(p)[i];
+        V d, pv, pq;
+        if (DM != 1) { d = reinterpret_cast<const V*>(delta)[i]; pv = reinterpret_cast<const V*>(p)[i]; }
+        if (DM == 2) pq = reinterpret_cast<const V*>(p_prev)[i];
         V rv = reinterpret_cast<const V*>(r)[i];
         V av = reinterpret_cast<const V*>(Ap)[i];
         V mv, bv, zv;
@@ -761,8 +771,10 @@ __global__ void __launch_bounds__(256) k_pcg_step2(long i_begin, long nvec, cons
         T bsum = T(0), qsum = T(0);
 #pragma unroll
         for (int k = 0; k < VW; ++k) {
-            T dl = comp(d, k) + alpha * comp(pv, k);
-            comp(d, k) = dl;
+            T dl = T(0);
+            if (DM == 2) dl = comp(d, k) + alpha_prev * comp(pq, k);
+            if (DM == 0) dl = comp(d, k);
+            if (DM != 1) { dl = dl + alpha * comp(pv, k); comp(d, k) = dl; }
             T rr = comp(rv, k) - alpha * comp(av, k);
             comp(rv, k) = rr;
             T zz = USE_PRE ? comp(mv, k) * rr : rr;
@@ -770,7 +782,7 @@ __global__ void __launch_bounds__(256) k_pcg_step2(long i_begin, long nvec, cons
             bsum += zz * rr;
             if (LM) qsum += dl * (rr + comp(bv, k));
         }
-        reinterpret_cast<V*>(delta)[i] = d;
+        if (DM != 1) reinterpret_cast<V*>(delta)[i] = d;
         reinterpret_cast<V*>(r)[i] = rv;
         if (USE_PRE) reinterpret_cast<V*>(z)[i] = zv;
         bacc += (double)bsum;
@@ -1752,9 +1764,17 @@ struct Engine : OptK_Plan {
             apply_A("computeAdelta", "computeAdelta_Graph", delta, Adelta, S(S_DUMMY), nullptr);
             this->launch_tiles("PCGStep2_2ndHalf", (flat_vecs() + 255) / 256, dim3(256), k_residual_reset<T, F::USE_PRE>, fb, nv, act, Npad, delta.d, r.d, Adelta.d, pre.d, b.d, z.d, bNum, S(S_Q), nextDen);
         } else if (lm) {
-            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, true>, fb, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)S(S_STOP));
+            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, true>, fb, nv, act, Npad, delta.d, p.d, (const T*)nullptr, (double*)nullptr, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)S(S_STOP));
         } else {
-            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, false>, fb, nv, act, Npad, delta.d, p.d, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)nullptr);
+            // deferred delta update (see k_pcg_step2): only inside pcg_run's Gauss-Newton loop with the fused kernel, where the
+            // other p buffer still holds the previous direction; `lazy_last` = this is the loop's final iteration
+            const int dm = !lazy_delta ? 0 : (l & 1) ? 2 : (lazy_last ? 0 : 1);
+            auto go = [&](auto kernel) {
+                this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), kernel, fb, nv, act, Npad, delta.d, p.d, (const T*)p_alt.d, S(S_APREV), r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)nullptr);
+            };
+            if (dm == 0) go(k_pcg_step2<T, F::USE_PRE, false, 0>);
+            else if (dm == 1) go(k_pcg_step2<T, F::USE_PRE, false, 1>);
+            else go(k_pcg_step2<T, F::USE_PRE, false, 2>);
         }
         reduce(int(bNum - scal));
         if (lm) reduce(S_Q);
@@ -1768,8 +1788,11 @@ struct Engine : OptK_Plan {
     // (A cooperative single-kernel form of this loop -- grid-wide barriers instead of two launches per iteration -- was built
     // and measured in r2o on image_warping 512^2: 18.64 us per PCG iteration against 18.59 us for the launches below.  That
     // problem is bound by the sincos arithmetic of its generic J^T J functor, not by launch latency, so the kernel was removed.)
+    bool lazy_delta = false, lazy_last = false;
     void pcg_run(int lIterations) override {
-        for (int l = 0; l < lIterations; ++l) pcg_iter(l, 0);
+        lazy_delta = fuse && !lm && !mat_mode && getenv("OPTB200_NO_LAZY_DELTA") == nullptr;
+        for (int l = 0; l < lIterations; ++l) { lazy_last = l + 1 == lIterations; pcg_iter(l, 0); }
+        lazy_delta = false;
     }
     // LM inner loop (solver:2072-2201) without a blocking fetchQ per iteration.  The exit test runs on the
     // device (k_lm_zeta); the host queues iteration l+1 BEFORE it looks at the verdict of iteration l, so the
