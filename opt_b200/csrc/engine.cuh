@@ -546,14 +546,23 @@ __global__ void k_segment_keys(F f, long n, unsigned* vertices, unsigned* ids) {
     ids[i] = (unsigned)i;
 }
 // PCGStep1_Graph, part 1: one thread per hyper-edge, partials into the edge's own GV * U slots (coalesced rows)
-// The GV * U partials of an edge are one row of `contrib`.  A thread storing its own row would make every store instruction of
-// the warp touch 32 different sectors (row stride 48-192 bytes; r2n: embedded 1 M vertices 0.69 ms for 603 MB of rows), so the 32
-// rows of a warp are staged in shared memory (row pitch GV U + 1: conflict-free) and written as ONE contiguous block.
+// rank[id] = position of incidence id = edge * GV + slot in the vertex-sorted list (inverse of the sorted id array)
+static __global__ void k_segment_rank(long n, const unsigned* __restrict__ sorted_ids, unsigned* __restrict__ rank) {
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (i < n) rank[sorted_ids[i]] = (unsigned)i;
+}
+// PCGStep1_Graph, part 1: one thread per hyper-edge evaluates the GV * U partials of its edge; the row of incidence (edge, slot)
+// is stored AT ITS SORTED POSITION, so that the rows of a vertex are one contiguous range for part 2.  A thread storing its own
+// rows would make every store instruction of the warp touch 32 sectors (r2n: embedded, 1 M vertices, 0.69 ms), so the 32 GV
+// rows of a warp are staged in shared memory (row pitch GV U + 1: conflict-free) and written out with consecutive lanes on
+// consecutive channels of a row (U x 4 contiguous bytes per row).
 template <class F>
-__global__ void __launch_bounds__(128) k_graph_contrib(F f, long E, VecOf<F> dir, typename F::Scalar* __restrict__ contrib) {
+__global__ void __launch_bounds__(128) k_graph_contrib(F f, long E, VecOf<F> dir, const unsigned* __restrict__ rank,
+                                                       typename F::Scalar* __restrict__ contrib) {
     using T = typename F::Scalar;
-    constexpr int C = F::GV * F::U, PITCH = C + 1;
+    constexpr int U = F::U, GV = F::GV, C = GV * U, PITCH = C + 1;
     __shared__ T stage[4][32 * PITCH];                                           // 128 threads: <= 25 KB also for U = 12 in fp64
+    __shared__ unsigned pos[4][32 * GV];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long e0 = (blockIdx.x * (long)blockDim.x + threadIdx.x) - lane;       // first edge of this warp
     const long e = e0 + lane;
@@ -563,17 +572,21 @@ __global__ void __launch_bounds__(128) k_graph_contrib(F f, long E, VecOf<F> dir
         f.graphContrib(e, dir, c);
 #pragma unroll
         for (int k = 0; k < C; ++k) stage[warp][lane * PITCH + k] = c[k];
+#pragma unroll
+        for (int s = 0; s < GV; ++s) pos[warp][lane * GV + s] = rank[e * GV + s];
     }
     __syncwarp();
-    const int rows = (int)(E - e0 < 32 ? E - e0 : 32);
-    T* out = contrib + e0 * C;
-    for (int i = lane; i < rows * C; i += 32) out[i] = stage[warp][(i / C) * PITCH + (i % C)];
+    const int rows = (int)(E - e0 < 32 ? E - e0 : 32) * GV;                      // (edge, slot) rows of this warp
+    for (int i = lane; i < rows * U; i += 32) {
+        const int row = i / U, u = i - row * U;
+        contrib[(long)pos[warp][row] * U + u] = stage[warp][(row / GV) * PITCH + (row % GV) * U + u];
+    }
 }
-// PCGStep1 + PCGStep1_Graph, part 2: the vertex terms plus the sum of the vertex' incident partials (sorted by vertex, then by
-// edge-slot id: a fixed summation order), Ap written once, alphaDenominator = <p, Ap> from the same pass
+// PCGStep1 + PCGStep1_Graph, part 2: the vertex terms plus the sum of the vertex' partial rows, which lie contiguously at
+// [off[v], off[v + 1]) in sorted (= fixed) order; Ap written once, alphaDenominator = <p, Ap> from the same pass
 template <class F, bool LM>
 __global__ void k_apply_jtj_seg(F f, TileGrid tg, VecOf<F> dir, VecOf<F> out, VecOf<F> CtC, const int* __restrict__ off,
-                                const unsigned* __restrict__ ids, const typename F::Scalar* __restrict__ contrib, double* den, double* zero_slot) {
+                                const typename F::Scalar* __restrict__ contrib, double* den, double* zero_slot) {
     using T = typename F::Scalar;
     constexpr int U = F::U;
     int x, y, z; long s;
@@ -583,10 +596,20 @@ __global__ void k_apply_jtj_seg(F f, TileGrid tg, VecOf<F> dir, VecOf<F> out, Ve
     if (thread_site(f, tg, tile_, x, y, z, s) && !f.exclude(x, y, z, s)) {
         T o[U];
         f.applyJTJ(x, y, z, s, dir, o);
-        for (int i = off[s]; i < off[s + 1]; ++i) {
-            const T* row = contrib + (long)ids[i] * U;
+        const int b = off[s], e = off[s + 1];
+        if constexpr (U % 4 == 0 && sizeof(T) == 4) {                            // rows of whole 128-bit words
+            const float4* row = reinterpret_cast<const float4*>(contrib + (long)b * U);
+            for (int i = 0; i < (e - b); ++i)
 #pragma unroll
-            for (int u = 0; u < U; ++u) o[u] += row[u];
+                for (int q = 0; q < U / 4; ++q) {
+                    const float4 v = row[i * (U / 4) + q];
+                    o[4 * q] += v.x; o[4 * q + 1] += v.y; o[4 * q + 2] += v.z; o[4 * q + 3] += v.w;
+                }
+        } else {
+            const T* row = contrib + (long)b * U;
+            for (int i = 0; i < (e - b); ++i)
+#pragma unroll
+                for (int u = 0; u < U; ++u) o[u] += row[i * U + u];
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -1193,7 +1216,7 @@ struct Engine : OptK_Plan {
         if (comm) ncclCommDestroy(comm);
         release_materialized(); m_tmp.release();
         cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFreeHost(lm_box); cudaFree(active4); cudaFree(mask_changed);
-        cudaFree(seg_ids); cudaFree(seg_off); cudaFree(seg_contrib);
+        cudaFree(seg_ids); cudaFree(seg_rank); cudaFree(seg_off); cudaFree(seg_contrib);
         cudaFree(inc); cudaFree(inc_off); cudaFree(inc_count); cudaFree(sort_tmp); cudaFree(key_a); cudaFree(key_b); cudaFree(val_a);
         base_destroy();
     }
@@ -1527,12 +1550,13 @@ struct Engine : OptK_Plan {
     bool use_gather() const { return F::HAS_GATHER && getenv("OPTB200_GRAPH_ATOMICS") == nullptr; }
     // segmented scatter of the hyper-edge energies: (edge, slot) ids sorted by vertex, offsets per vertex, partial rows
     bool use_seg() const { return F::HAS_SEGSCATTER && GRAPH && getenv("OPTB200_GRAPH_ATOMICS") == nullptr; }
-    unsigned* seg_ids = nullptr; int* seg_off = nullptr; T* seg_contrib = nullptr;
+    unsigned* seg_ids = nullptr; unsigned* seg_rank = nullptr; int* seg_off = nullptr; T* seg_contrib = nullptr;
     void build_segments() {
         if constexpr (F::HAS_SEGSCATTER) {
             const long n = E * F::GV;
             if (!seg_off) {
                 OPTK_CUDA(cudaMalloc(&seg_ids, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
+                OPTK_CUDA(cudaMalloc(&seg_rank, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
                 OPTK_CUDA(cudaMalloc(&seg_off, (size_t)(N + 1) * sizeof(int)));
                 OPTK_CUDA(cudaMalloc(&seg_contrib, (size_t)std::max<long>(n, 1) * U * sizeof(T)));
                 OPTK_CUDA(cudaMalloc(&key_a, (size_t)std::max<long>(n, 1) * sizeof(unsigned)));
@@ -1548,6 +1572,7 @@ struct Engine : OptK_Plan {
                 this->pre_launch("graphSegmentSort");
                 cub::DeviceRadixSort::SortPairs(sort_tmp, sort_tmp_bytes, key_a, key_b, val_a, seg_ids, (int)n, 0, vbits, stream);   // stable
                 this->post_launch();
+                this->launch("graphSegmentRank", dim3((unsigned)((n + 255) / 256)), dim3(256), k_segment_rank, n, (const unsigned*)seg_ids, seg_rank);
             }
             this->launch("graphSegmentOffsets", dim3((unsigned)((n + 1 + 255) / 256)), dim3(256), k_incidence_offsets, (const unsigned*)key_b, n, N, seg_off);
         }
@@ -1660,9 +1685,9 @@ struct Engine : OptK_Plan {
         }
         if constexpr (F::HAS_SEGSCATTER) {
             if (use_seg()) {
-                if (E > 0) this->launch(gname, dim3((unsigned)((E + 127) / 128)), dim3(128), k_graph_contrib<F>, f, E, dir, seg_contrib);
-                if (lm) this->launch_tiles(name, tg.n, sblock, k_apply_jtj_seg<F, true>, f, tg, dir, out, CtC, (const int*)seg_off, (const unsigned*)seg_ids, (const T*)seg_contrib, den, zero_slot);
-                else    this->launch_tiles(name, tg.n, sblock, k_apply_jtj_seg<F, false>, f, tg, dir, out, CtC, (const int*)seg_off, (const unsigned*)seg_ids, (const T*)seg_contrib, den, zero_slot);
+                if (E > 0) this->launch(gname, dim3((unsigned)((E + 127) / 128)), dim3(128), k_graph_contrib<F>, f, E, dir, (const unsigned*)seg_rank, seg_contrib);
+                if (lm) this->launch_tiles(name, tg.n, sblock, k_apply_jtj_seg<F, true>, f, tg, dir, out, CtC, (const int*)seg_off, (const T*)seg_contrib, den, zero_slot);
+                else    this->launch_tiles(name, tg.n, sblock, k_apply_jtj_seg<F, false>, f, tg, dir, out, CtC, (const int*)seg_off, (const T*)seg_contrib, den, zero_slot);
                 return;
             }
         }
