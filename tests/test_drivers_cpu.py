@@ -20,7 +20,7 @@ f32 = np.float32
 def test_driver_symbols_exported(built):
     txt = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "OptB200Drivers.h")).read(), flags=re.S)
     names = sorted(set(re.findall(r"\b(OptB200_[A-Za-z]+)\s*\(", txt)))
-    assert len(names) == 6
+    assert len(names) == 7          # six driver kernels + OptB200_FilterGaussianNoAlloc
     lib = C.CDLL(built)
     for n in names:
         assert hasattr(lib, n), n
