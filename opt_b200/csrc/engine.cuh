@@ -931,6 +931,17 @@ __global__ void k_lm_zeta(int l, double q_tol, const double* q, double* qprev, d
     b->seq = seq;
 }
 
+// Scalar read-back without the copy engine: one thread stores the device scalar (and the peer-spin error flag) straight into
+// pinned, device-mapped host memory.  A cudaMemcpyAsync D2H of 8 bytes queues behind whatever else the D2H copy engine is doing:
+// a caller that streams problems through the API has the previous result's download in flight (bench.py's e2e leg: 268 MB / 3.2 GB),
+// and every cost read-back of the solve stalled for one such download (r2s: +6.9 ms on a 24.9 ms poisson solve, +68 ms on a 951 ms
+// volumetric one).
+static __global__ void k_publish_scalar(const double* __restrict__ src, const int* __restrict__ err, volatile double* host_val, volatile int* host_err) {
+    *host_val = *src;
+    *host_err = err ? *err : 0;
+    __threadfence_system();
+}
+
 // ---- scalar all-reduce over NVLink peer memory ------------------------------------------------------------
 // The PCG loop needs two dependent scalar all-reduces per iteration (alphaDen after PCGStep1, betaNum after PCGStep2).
 // ncclAllReduce of 8 bytes costs a full collective launch each (~10-15 us); here every rank stores its partial sums
@@ -1149,7 +1160,8 @@ struct Engine : OptK_Plan {
     unsigned *key_a = nullptr, *key_b = nullptr, *val_a = nullptr;
     bool fuse = true;                                       // fused PCGStep3+PCGStep1 (single rank)
     double* scal = nullptr;
-    double* h_scal = nullptr;    // pinned
+    double* h_scal = nullptr;    // pinned + device-mapped
+    double* h_scal_dev = nullptr; // its device address (read_scalar publishes through it); nullptr: cudaMemcpyAsync instead
     LmMailbox* lm_box = nullptr; // pinned + device-mapped, ring of 2 (pcg_run_lm)
     long long lm_seq = 0;
     T radius = 0, min_diag = 0, max_diag = 0;
@@ -1193,7 +1205,12 @@ struct Engine : OptK_Plan {
         if (getenv("OPTB200_NO_FUSE") || !F::FUSE_STEP3 || (use_gather() && !getenv("OPTB200_GATHER_FUSED")) || use_seg()) fuse = false;
         OPTK_CUDA(cudaMalloc(&scal, S_COUNT * sizeof(double)));
         OPTK_CUDA(cudaMemsetAsync(scal, 0, S_COUNT * sizeof(double), stream));
-        OPTK_CUDA(cudaMallocHost(&h_scal, S_COUNT * sizeof(double)));
+        OPTK_CUDA(cudaHostAlloc(&h_scal, S_COUNT * sizeof(double), cudaHostAllocMapped | cudaHostAllocPortable));
+        memset(h_scal, 0, S_COUNT * sizeof(double));
+        if (getenv("OPTB200_SCALAR_MEMCPY") == nullptr) {
+            void* dp = nullptr;
+            if (cudaHostGetDevicePointer(&dp, h_scal, 0) == cudaSuccess) h_scal_dev = (double*)dp; else cudaGetLastError();
+        }
         if (lm) {
             OPTK_CUDA(cudaHostAlloc(&lm_box, 2 * sizeof(LmMailbox), cudaHostAllocMapped | cudaHostAllocPortable));
             memset(lm_box, 0, 2 * sizeof(LmMailbox));
@@ -1494,8 +1511,13 @@ struct Engine : OptK_Plan {
     }
 
     double read_scalar(int slot) {                          // blocking D2H (backend_cuda.t:353-355)
-        OPTK_CUDA(cudaMemcpyAsync(h_scal, scal + slot, sizeof(double), cudaMemcpyDeviceToHost, stream));
-        if (xr_on) OPTK_CUDA(cudaMemcpyAsync(h_scal + 1, xr_error, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        if (h_scal_dev) {                                    // zero-copy publish (no copy engine), then wait for the stream
+            k_publish_scalar<<<1, 1, 0, stream>>>(scal + slot, xr_on ? xr_error : nullptr, h_scal_dev, (volatile int*)(h_scal_dev + 1));
+            OPTK_CUDA(cudaGetLastError());
+        } else {
+            OPTK_CUDA(cudaMemcpyAsync(h_scal, scal + slot, sizeof(double), cudaMemcpyDeviceToHost, stream));
+            if (xr_on) OPTK_CUDA(cudaMemcpyAsync(h_scal + 1, xr_error, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        }
         OPTK_CUDA(cudaStreamSynchronize(stream));
         if (xr_on && *(const int*)(h_scal + 1) != 0) {
             printf("Opt: a peer rank never arrived at a scalar all-reduce (rank %d of %d)\n", rank, nranks);
