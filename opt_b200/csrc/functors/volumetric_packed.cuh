@@ -106,11 +106,14 @@ __device__ __forceinline__ void mbar_expect_tx(unsigned long long* b, unsigned b
 __device__ __forceinline__ void mbar_arrive(unsigned long long* b) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(unsigned long long* b, unsigned parity) {
+// try_wait may suspend the thread in hardware up to `hint_ns` before it reports "not yet" (0: return at once, i.e. spin): with
+// the short default limit the full-barrier waits of the march spun ~35 times per step (profiles/README.md r2d opcode mix:
+// SYNCS 55 + BRA + YIELD), issue slots and power that a power-capped part pays for in clock.
+__device__ __forceinline__ void mbar_wait(unsigned long long* b, unsigned parity, unsigned hint_ns) {
     unsigned ok;
     do {
-        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.b32 %0, 1, 0, p;\n}"
-                     : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n selp.b32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(smem_u32(b)), "r"(parity), "r"(hint_ns) : "memory");
     } while (!ok);
 }
 // contiguous global -> shared copy by the bulk-copy engine; 16-byte aligned addresses and size
@@ -154,6 +157,7 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
     const int W = f.W, H = f.H, D = f.D;
     const long sz = (long)W * H;
     const int zlo = f.z_lo(), zhi = f.z_hi();
+    const unsigned hint = f.mbar_hint_ns;
     const int ntx = f.ntx(), nty = (f.nty() + 1) / 2, nrec_y = f.nty();
     const int nunits = ntx * nty * f.nseg();
     const int lane = threadIdx.x, wy = threadIdx.y, ty0 = 2 * wy, tid = linear_tid();
@@ -189,7 +193,7 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
     };
     auto issue = [&]() {                                  // all lanes of the issuing warp
         const int st = pr_e % NS;
-        if (pr_e >= NS) bulk::mbar_wait(empty + st, ((pr_e / NS) - 1) & 1);
+        if (pr_e >= NS) bulk::mbar_wait(empty + st, ((pr_e / NS) - 1) & 1, hint);
         const int bx = pr_unit % ntx, by = (pr_unit / ntx) % nty;
         float* tabs = ring + st * G::STAGEF;
         float* dirs = tabs + G::TABF;
@@ -268,7 +272,7 @@ k_volumetric_apply_packed(VolumetricFunctor<float, 6> f, Vec<float, 6> zv, Vec<f
 
         auto acquire = [&](int z) -> const float* {                       // stage base of plane z, once its copies have landed
             const int e = e0 + (z - zs);
-            bulk::mbar_wait(full + (e % NS), (e / NS) & 1);
+            bulk::mbar_wait(full + (e % NS), (e / NS) & 1, hint);
             return ring + (e % NS) * G::STAGEF;
         };
         auto release = [&](int z) {

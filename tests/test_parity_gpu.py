@@ -390,3 +390,22 @@ def test_graph_segmented_scatter_equals_atomics(built, case, double, monkeypatch
     monkeypatch.setenv("OPTB200_GRAPH_ATOMICS", "1")
     ca, xa, _, _ = run_gpu(pr)
     assert_costs_close(cs, ca, double, tol=1e-5 if not double else 1e-10)
+
+
+@pytest.mark.parametrize("l_iter", [7, 8])
+@pytest.mark.parametrize("case", ["poisson_strips", "volumetric_packed", "optical_flow", "sfs_quads", "image_warping"])
+def test_deferred_delta_update_is_bit_identical(built, case, l_iter, monkeypatch):
+    """k_pcg_step2's deferred form (delta updated every second PCG iteration for two directions at once; odd and even loop lengths)
+    performs the same two FMAs per element as the eager form: costs and unknowns must agree bit for bit wherever the reductions are
+    order-independent, and to rounding of the block-partial sums otherwise."""
+    b, args, kw = CASES[case]
+    pr = b(*args, **dict(kw, l_iter=l_iter))
+    lazy_c, lazy_x, sol, _ = run_gpu(pr, timing=True)
+    assert sol.kernel_time("PCGStep3+1")[0] > 0              # the fused path, where the deferred form is active
+    monkeypatch.setenv("OPTB200_NO_LAZY_DELTA", "1")
+    eager_c, eager_x, _, _ = run_gpu(pr)
+    assert_costs_close(lazy_c, eager_c, False, tol=1e-6)
+    assert_unknowns_close(lazy_x, eager_x, False, tol=1e-5)
+    rc, rx, _ = run_oracle(pr)
+    assert_costs_close(lazy_c, rc, False)
+    assert_unknowns_close(lazy_x, rx, False)
