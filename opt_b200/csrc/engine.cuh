@@ -757,6 +757,35 @@ __global__ void __launch_bounds__(256) k_zero_if(const int* __restrict__ flag, V
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) v[i] = zero;
 }
 
+// LM inner-loop exit test (solver:2180-2200) evaluated on the device.  One thread: zeta = (l+1)(Q1-Q0)/Q1 in
+// opt_float (the same roundings as the reference's host code), sets the stop flag the step kernels of a
+// speculatively queued iteration look at, rolls Q0 forward and posts the result into a pinned host mailbox
+// (payload, system-scope fence, sequence number) that the host polls without any stream synchronisation.
+struct LmMailbox { double zeta, q; long long stop; long long seq; };
+template <class T>
+__global__ void k_lm_begin(const double* q, double* qprev) { *qprev = (double)(T)(*q); }
+template <class T>
+__device__ __forceinline__ void lm_zeta_body(int l, double q_tol, double q_now, double* qprev, double* stop, LmMailbox* box, long long seq) {
+    const double Q1 = (double)(T)q_now, Q0 = *qprev;
+    const double zeta = (double)(T)((double)(T)((double)(T)(l + 1) * (double)(T)(Q1 - Q0)) / Q1);
+    const bool was = *stop != 0.0;
+    const bool now = was || zeta < q_tol;
+    if (!was) { *qprev = Q1; if (now) *stop = 1.0; }
+    volatile LmMailbox* b = box;
+    b->zeta = zeta; b->q = Q1; b->stop = now ? 1 : 0;
+    __threadfence_system();
+    b->seq = seq;
+}
+template <class T>
+__global__ void k_lm_zeta(int l, double q_tol, const double* q, double* qprev, double* stop, LmMailbox* box, long long seq) {
+    lm_zeta_body<T>(l, q_tol, *q, qprev, stop, box, seq);
+}
+// The exit test folded into the tail of PCGStep2 (single GPU, no residual reset): the last block to retire -- arrival counter
+// behind a device-scope fence, so every block's contribution to q is visible to it -- evaluates the test.  One launch less per
+// LM iteration (the separate one-thread kernel cost 8.5 us of a 80 us shape_from_shading iteration, profiles/r1k_timing_sfs_lm.txt).
+struct LmFold { int on; int l; double q_tol; double* qprev; double* stop_w; LmMailbox* box; long long seq; unsigned* counter; };
+
+
 // DM (Gauss-Newton with the fused PCGStep3+1 kernel only): delta is not read inside the inner loop, and the fused kernel's
 // ping-pong keeps p_l and p_{l-1} both alive, so the update delta += alpha p is applied every SECOND iteration for two
 // directions at once.  DM = 0: delta += alpha p (every iteration);  DM = 1: delta untouched, alpha parked in *aprev;
@@ -770,7 +799,7 @@ __global__ void __launch_bounds__(256) k_pcg_step2(long i_begin, long nvec, cons
                                                    T* __restrict__ r, const T* __restrict__ Ap,
                                                    const T* __restrict__ pre, const T* __restrict__ b,
                                                    T* __restrict__ z, const double* aNum, const double* aDen,
-                                                   double* bNum, double* q, double* zero_slot, const double* stop) {
+                                                   double* bNum, double* q, double* zero_slot, const double* stop, LmFold fold) {
     using V = typename VecIO<T>::V;
     constexpr int VW = VecIO<T>::W;
     const long i0 = blockIdx.x * (long)blockDim.x + threadIdx.x, istride = (long)gridDim.x * blockDim.x;
@@ -813,6 +842,14 @@ __global__ void __launch_bounds__(256) k_pcg_step2(long i_begin, long nvec, cons
     }
     block_accumulate(bacc, bNum);
     if (LM) block_accumulate(qacc, q);
+    if (LM && fold.on && threadIdx.x == 0) {                  // thread 0 issued this block's atomics just above
+        __threadfence();
+        if (atomicAdd(fold.counter, 1u) == gridDim.x - 1) {
+            *fold.counter = 0;                                // next launch
+            __threadfence();
+            lm_zeta_body<T>(fold.l, fold.q_tol, *(volatile double*)q, fold.qprev, fold.stop_w, fold.box, fold.seq);
+        }
+    }
 }
 
 // PCGStep3 (solver:814-845): beta = bNum/aNum; p = z + beta p
@@ -909,26 +946,6 @@ __global__ void __launch_bounds__(256) k_residual_reset(long i_begin, long nvec,
     }
     block_accumulate(bacc, bNum);
     block_accumulate(qacc, q);
-}
-
-// LM inner-loop exit test (solver:2180-2200) evaluated on the device.  One thread: zeta = (l+1)(Q1-Q0)/Q1 in
-// opt_float (the same roundings as the reference's host code), sets the stop flag the step kernels of a
-// speculatively queued iteration look at, rolls Q0 forward and posts the result into a pinned host mailbox
-// (payload, system-scope fence, sequence number) that the host polls without any stream synchronisation.
-struct LmMailbox { double zeta, q; long long stop; long long seq; };
-template <class T>
-__global__ void k_lm_begin(const double* q, double* qprev) { *qprev = (double)(T)(*q); }
-template <class T>
-__global__ void k_lm_zeta(int l, double q_tol, const double* q, double* qprev, double* stop, LmMailbox* box, long long seq) {
-    const double Q1 = (double)(T)(*q), Q0 = *qprev;
-    const double zeta = (double)(T)((double)(T)((double)(T)(l + 1) * (double)(T)(Q1 - Q0)) / Q1);
-    const bool was = *stop != 0.0;
-    const bool now = was || zeta < q_tol;
-    if (!was) { *qprev = Q1; if (now) *stop = 1.0; }
-    volatile LmMailbox* b = box;
-    b->zeta = zeta; b->q = Q1; b->stop = now ? 1 : 0;
-    __threadfence_system();
-    b->seq = seq;
 }
 
 // Scalar read-back without the copy engine: one thread stores the device scalar (and the peer-spin error flag) straight into
@@ -1214,6 +1231,8 @@ struct Engine : OptK_Plan {
         if (lm) {
             OPTK_CUDA(cudaHostAlloc(&lm_box, 2 * sizeof(LmMailbox), cudaHostAllocMapped | cudaHostAllocPortable));
             memset(lm_box, 0, 2 * sizeof(LmMailbox));
+            OPTK_CUDA(cudaMalloc(&lm_counter, sizeof(unsigned)));
+            OPTK_CUDA(cudaMemsetAsync(lm_counter, 0, sizeof(unsigned), stream));
         }
         if (F::ND == 1) { sblock = dim3(256, 1, 1); }
         else if (F::ND == 2) { sblock = dim3(32, 8, 1); }
@@ -1232,7 +1251,7 @@ struct Engine : OptK_Plan {
         cudaFree(xr_buf); cudaFree(xr_error);
         if (comm) ncclCommDestroy(comm);
         release_materialized(); m_tmp.release();
-        cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFreeHost(lm_box); cudaFree(active4); cudaFree(mask_changed);
+        cudaFree(pool); cudaFree(scal); cudaFreeHost(h_scal); cudaFreeHost(lm_box); cudaFree(lm_counter); cudaFree(active4); cudaFree(mask_changed);
         cudaFree(seg_ids); cudaFree(seg_rank); cudaFree(seg_off); cudaFree(seg_contrib);
         cudaFree(inc); cudaFree(inc_off); cudaFree(inc_count); cudaFree(sort_tmp); cudaFree(key_a); cudaFree(key_b); cudaFree(val_a);
         base_destroy();
@@ -1811,13 +1830,14 @@ struct Engine : OptK_Plan {
             apply_A("computeAdelta", "computeAdelta_Graph", delta, Adelta, S(S_DUMMY), nullptr);
             this->launch_tiles("PCGStep2_2ndHalf", (flat_vecs() + 255) / 256, dim3(256), k_residual_reset<T, F::USE_PRE>, fb, nv, act, Npad, delta.d, r.d, Adelta.d, pre.d, b.d, z.d, bNum, S(S_Q), nextDen);
         } else if (lm) {
-            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, true>, fb, nv, act, Npad, delta.d, p.d, (const T*)nullptr, (double*)nullptr, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)S(S_STOP));
+            this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), k_pcg_step2<T, F::USE_PRE, true>, fb, nv, act, Npad, delta.d, p.d, (const T*)nullptr, (double*)nullptr, r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)S(S_STOP), lm_fold);
+            lm_fold_used = lm_fold.on != 0;
         } else {
             // deferred delta update (see k_pcg_step2): only inside pcg_run's Gauss-Newton loop with the fused kernel, where the
             // other p buffer still holds the previous direction; `lazy_last` = this is the loop's final iteration
             const int dm = !lazy_delta ? 0 : (l & 1) ? 2 : (lazy_last ? 0 : 1);
             auto go = [&](auto kernel) {
-                this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), kernel, fb, nv, act, Npad, delta.d, p.d, (const T*)p_alt.d, S(S_APREV), r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)nullptr);
+                this->launch_tiles("PCGStep2", (flat_vecs() + 255) / 256, dim3(256), kernel, fb, nv, act, Npad, delta.d, p.d, (const T*)p_alt.d, S(S_APREV), r.d, Ap.d, pre.d, b.d, z.d, aNum, aDen, bNum, S(S_Q), nextDen, (const double*)nullptr, LmFold{});
             };
             if (dm == 0) go(k_pcg_step2<T, F::USE_PRE, false, 0>);
             else if (dm == 1) go(k_pcg_step2<T, F::USE_PRE, false, 1>);
@@ -1835,6 +1855,8 @@ struct Engine : OptK_Plan {
     // (A cooperative single-kernel form of this loop -- grid-wide barriers instead of two launches per iteration -- was built
     // and measured in r2o on image_warping 512^2: 18.64 us per PCG iteration against 18.59 us for the launches below.  That
     // problem is bound by the sincos arithmetic of its generic J^T J functor, not by launch latency, so the kernel was removed.)
+    LmFold lm_fold{}; bool lm_fold_used = false; unsigned* lm_counter = nullptr;
+    bool lm_fold_ok = getenv("OPTB200_LM_SEPARATE_TEST") == nullptr;
     bool lazy_delta = false, lazy_last = false;
     void pcg_run(int lIterations) override {
         lazy_delta = fuse && !lm && !mat_mode && getenv("OPTB200_NO_LAZY_DELTA") == nullptr;
@@ -1866,9 +1888,17 @@ struct Engine : OptK_Plan {
         *zeta_out = 0.0; *fired = 0;
         for (int l = 0; l <= lIterations; ++l) {
             if (l < lIterations) {
-                pcg_iter(l, ((l + 1) % reset_period) == 0);
+                const bool reset = ((l + 1) % reset_period) == 0;
                 seq_of[l & 1] = ++lm_seq;
-                this->launch("LMExitTest", dim3(1), dim3(1), k_lm_zeta<T>, l, q_tol, (const double*)S(S_Q), S(S_QPREV), S(S_STOP), lm_box + (l & 1), seq_of[l & 1]);
+                // single GPU, plain PCGStep2: the test rides in that kernel's tail (LmFold); otherwise its own launch
+                lm_fold = LmFold{};
+                if (lm_fold_ok && nranks == 1 && !reset)
+                    lm_fold = LmFold{1, l, q_tol, S(S_QPREV), S(S_STOP), lm_box + (l & 1), seq_of[l & 1], lm_counter};
+                lm_fold_used = false;
+                pcg_iter(l, reset);
+                lm_fold = LmFold{};
+                if (!lm_fold_used)
+                    this->launch("LMExitTest", dim3(1), dim3(1), k_lm_zeta<T>, l, q_tol, (const double*)S(S_Q), S(S_QPREV), S(S_STOP), lm_box + (l & 1), seq_of[l & 1]);
             }
             if (l > 0) {                                    // verdict of iteration l-1, while iteration l runs
                 const int k = (l - 1) & 1;
