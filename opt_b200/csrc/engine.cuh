@@ -1653,7 +1653,14 @@ struct Engine : OptK_Plan {
     double model_cost() override {
         exchange(delta);
         OPTK_CUDA(cudaMemsetAsync(S(S_MODEL), 0, sizeof(double), stream));
-        this->launch_tiles("computeModelCost", tg.n, sblock, k_model_cost<F>, f, tg, delta, S(S_MODEL));
+        bool fast_mc = false;
+        if constexpr (F::HAS_FAST_MODEL_COST) {
+            if (f.fast_ok() && getenv("OPTB200_GENERIC_MODEL_COST") == nullptr) {
+                this->launch_tiles_smem("computeModelCost", f.fast_tiles(), f.fast_block(), f.fast_smem(), f.fast_model_cost_kernel(), f, delta, S(S_MODEL));
+                fast_mc = true;
+            }
+        }
+        if (!fast_mc) this->launch_tiles("computeModelCost", tg.n, sblock, k_model_cost<F>, f, tg, delta, S(S_MODEL));
         if (GRAPH) this->launch("computeModelCost_Graph", edge_grid(), dim3(256), k_graph_model_cost<F>, f, E, delta, S(S_MODEL));
         reduce(S_MODEL);
         return (double)(T)read_scalar(S_MODEL);
@@ -2005,6 +2012,7 @@ struct FunctorDefaults {
     static constexpr bool HAS_ACTIVE_ITEMS = false;      // ... whose kernel walks a compacted list of work items (poisson)
     static constexpr bool HAS_FAST_INIT = false;         // ... and with a specialised PCGInit1 (fast_init_kernel())
     static constexpr bool HAS_FAST_COST = false;         // ... and computeCost (fast_cost_kernel())
+    static constexpr bool HAS_FAST_MODEL_COST = false;   // ... and computeModelCost (fast_model_cost_kernel())
     static constexpr bool HAS_FAST_PRECOMPUTE = false;   // ... and precompute (fast_precompute(stream, nsm))
     static constexpr bool SLAB_OK = true;                // grid functors whose bounds predicates survive a slab cut
     static constexpr bool HAS_GATHER = false;            // graph functors with a per-vertex gather form of J^T J p

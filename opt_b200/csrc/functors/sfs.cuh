@@ -44,6 +44,8 @@ struct SfsFunctor : FunctorDefaults<T> {
     static auto fast_init_kernel();
     static constexpr bool HAS_FAST_COST = true;        // computeCost likewise (k_sfs_cost)
     static auto fast_cost_kernel();
+    static constexpr bool HAS_FAST_MODEL_COST = true;  // computeModelCost likewise (k_sfs_model_cost, MODE 4 of the march)
+    static auto fast_model_cost_kernel();
     static constexpr bool HAS_FAST_PRECOMPUTE = true;  // one thread per quad of a row (k_sfs_precompute4)
     void fast_precompute(cudaStream_t stream, int nsm) const;
     size_t fast_smem() const;
@@ -318,11 +320,12 @@ struct SfsMarch {
     using F = SfsFunctor<T>;
     static constexpr bool HAS_G = MODE != 3;                                        // the cost pass needs no gradient images
     static constexpr bool USE_C = LM && MODE < 2;
-    static constexpr int NF = (HAS_G ? 5 : 2) + (MODE == 1) + USE_C + (MODE >= 2);  // float arrays per row
+    static constexpr bool COSTLIKE = MODE >= 3;                                     // 3: computeCost, 4: computeModelCost
+    static constexpr int NF = (HAS_G ? 5 : 2) + (MODE == 1) + USE_C + (MODE >= 2) + (MODE == 4);  // float arrays per row
     static constexpr int QB = 4 * (int)sizeof(T);                                   // bytes of a lane's quad
     static constexpr int STAGE = NF * 256 * QB + 3 * 256 * 4;
     static constexpr int D = NF <= 5 ? 4 : 3;                                       // ring depth
-    static constexpr int A_P = 0, A_G0 = 1, A_G1 = 2, A_G2 = 3, A_DI = HAS_G ? 4 : 1, A_Z = A_DI + 1, A_C = A_DI + 1 + (MODE == 1), A_BI = A_DI + 1;
+    static constexpr int A_P = 0, A_G0 = 1, A_G1 = 2, A_G2 = 3, A_DI = HAS_G ? 4 : 1, A_Z = A_DI + 1, A_C = A_DI + 1 + (MODE == 1), A_BI = A_DI + 1, A_DL = A_DI + 2;
 
     static __device__ __forceinline__ unsigned char* slot(unsigned char* ring, int stage, int arr, int tid) {
         return ring + (size_t)stage * STAGE + (size_t)arr * 256 * QB + (size_t)tid * QB;
@@ -348,6 +351,7 @@ struct SfsMarch {
         if (MODE == 1) cpq(slot(ring, st, A_Z, tid), a.z + s, on);
         if (USE_C) cpq(slot(ring, st, A_C, tid), a.ctc + s, on);
         if (MODE >= 2) cpq(slot(ring, st, A_BI, tid), f.BI + s, on);
+        if (MODE == 4) cpq(slot(ring, st, A_DL, tid), a.delta + s, on);
         sfsm::cp4(bslot(ring, st, 0, tid), f.mR + s, on);
         sfsm::cp4(bslot(ring, st, 1, tid), f.mC + s, on);
         sfsm::cp4(bslot(ring, st, 2, tid), f.valid + s, on);
@@ -390,13 +394,14 @@ __device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a,
         }
         // rows n-1 ("1") and n-2 ("2") carried between steps
         T p1[4], p2[4], db1[4], th1[4], tvp[4], g0p[4], g1p[4], g2p[4], kv1[4], ks1[4], oA[4], oB[4], p1l = T(0);
+        T dl1[4] = {T(0), T(0), T(0), T(0)};                           // MODE 4: delta of row n - 1
         bool e1[4], e2[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             p1[j] = p2[j] = db1[j] = th1[j] = tvp[j] = g0p[j] = g1p[j] = g2p[j] = kv1[j] = ks1[j] = oA[j] = oB[j] = T(0);
             e1[j] = e2[j] = false;
         }
-        const int nbeg = y0 - (MODE == 3 ? 1 : 2), nend = y1 + (MODE == 3 ? 1 : 2);
+        const int nbeg = y0 - (COSTLIKE ? 1 : 2), nend = y1 + (COSTLIKE ? 1 : 2);
         auto row_on = [&](int n) { return col_in && n >= 0 && n < H && n < nend; };
 #pragma unroll
         for (int k = 0; k < D - 1; ++k) issue(f, a, ring, k, tid, row_on(nbeg + k), x0 + (long)W * (nbeg + k));
@@ -421,12 +426,26 @@ __device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a,
             }
             const T yin = f.row_inb(n) ? T(1) : T(0);
             // ---- shading terms: dB[n], th[n], tv[n-1], T[n-1] ----
-            const T pl = __shfl_up_sync(FULL, pn[3], 1);
+            T pl = __shfl_up_sync(FULL, pn[3], 1);
             T db[4], thn[4], kvn[4], ksn[4], oC[4];
             bool en[4];
             const unsigned char mrb[4] = {mr.x, mr.y, mr.z, mr.w}, mcb[4] = {mc.x, mc.y, mc.z, mc.w}, vab[4] = {va.x, va.y, va.z, va.w};
             if (MODE >= 2) rd(ring, st, A_BI, tid, db);
-            else {
+            if (MODE == 4) {
+                // computeModelCost (solver:1105-1118): 0.5 sum (r + J delta)^2 is the cost of the linearised residuals, i.e. the
+                // cost pass with B_I -> B_I + g0 d + g1 d(x-1) + g2 d[n-1] in the shading terms and X -> X + delta in the terms
+                // that are linear in X (r_p and the regulariser); delta is 0 at excluded pixels
+                T dl[4]; rd(ring, st, A_DL, tid, dl);
+                const T dll = __shfl_up_sync(FULL, dl[3], 1);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    db[j] += g0[j] * dl[j] + g1[j] * (j > 0 ? dl[j > 0 ? j - 1 : 0] : dll) + g2[j] * dl1[j];
+                    pn[j] += dl[j];
+                    dl1[j] = dl[j];
+                }
+                pl = __shfl_up_sync(FULL, pn[3], 1);                   // left neighbour of the linearised row
+            }
+            if (MODE < 2) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) db[j] = g0[j] * pn[j] + g1[j] * (j > 0 ? pn[j > 0 ? j - 1 : 0] : pl) + g2[j] * p1[j];
             }
@@ -441,9 +460,9 @@ __device__ void SfsMarch<T, MODE, LM>::run(const F& f, const SfsMarchArgs<T>& a,
                 ksn[j] = vab[j] == 1 ? ws2 * in : T(0);
                 en[j] = di[j] > T(0);
                 oC[j] = en[j] ? wp2 * (MODE >= 2 ? pn[j] - di[j] : pn[j]) : T(0);
-                if (MODE == 3) oC[j] = oC[j] * (pn[j] - di[j]) + (en[j] ? thn[j] * dh : T(0));      // r_p^2 + r_h^2 of row n
+                if (COSTLIKE) oC[j] = oC[j] * (pn[j] - di[j]) + (en[j] ? thn[j] * dh : T(0));      // r_p^2 + r_h^2 of row n
             }
-            if (MODE == 3) {
+            if (COSTLIKE) {
                 // cost pass: sum of squared residuals centred on non-excluded pixels (k_cost in engine.cuh); rows n and n-1
                 T cs = T(0);
                 const T a1c = ((T)(n - 1 + f.y_off) - f.u_y) * ify;
@@ -582,6 +601,17 @@ __global__ void __launch_bounds__(256, sizeof(T) == 4 ? 2 : 1) k_sfs_cost(SfsFun
     block_accumulate(acc, target);
 }
 
+// computeModelCost (LM, once per nonlinear iteration) on the same pipeline: MODE 4
+template <class T>
+__global__ void __launch_bounds__(256, sizeof(T) == 4 ? 2 : 1) k_sfs_model_cost(SfsFunctor<T> f, Vec<T> delta, double* target) {
+    extern __shared__ __align__(16) unsigned char sfs_ring[];
+    SfsMarchArgs<T> a{};
+    a.delta = delta.d;
+    double acc = 0.0;
+    SfsMarch<T, 4, false>::run(f, a, sfs_ring, acc);
+    block_accumulate(acc, target);
+}
+
 // precompute with one thread per quad of a row: 128-bit loads of the three X / D_i rows and two image rows, lateral
 // neighbours from the adjacent lanes (the first and last lane of a warp fetch theirs), 128-bit stores of B_I, g0..g2.
 template <class T>
@@ -636,6 +666,7 @@ template <class T> void SfsFunctor<T>::fast_precompute(cudaStream_t stream, int 
 }
 
 template <class T> auto SfsFunctor<T>::fast_cost_kernel() { return &k_sfs_cost<T>; }
+template <class T> auto SfsFunctor<T>::fast_model_cost_kernel() { return &k_sfs_model_cost<T>; }
 template <class T> template <bool FUSED, bool LM> auto SfsFunctor<T>::fast_kernel() { return &k_sfs_march<T, FUSED, LM>; }
 template <class T> auto SfsFunctor<T>::fast_init_kernel() { return &k_sfs_init<T>; }
 template <class T> size_t SfsFunctor<T>::fast_smem() const {
@@ -646,6 +677,7 @@ template <class T> size_t SfsFunctor<T>::fast_smem() const {
     m = std::max<size_t>(m, (size_t)SfsMarch<T, 1, true>::STAGE * SfsMarch<T, 1, true>::D);
     m = std::max<size_t>(m, (size_t)SfsMarch<T, 2, false>::STAGE * SfsMarch<T, 2, false>::D);
     m = std::max<size_t>(m, (size_t)SfsMarch<T, 3, false>::STAGE * SfsMarch<T, 3, false>::D);
+    m = std::max<size_t>(m, (size_t)SfsMarch<T, 4, false>::STAGE * SfsMarch<T, 4, false>::D);
     return m;
 }
 

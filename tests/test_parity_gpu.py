@@ -409,3 +409,19 @@ def test_deferred_delta_update_is_bit_identical(built, case, l_iter, monkeypatch
     rc, rx, _ = run_oracle(pr)
     assert_costs_close(lazy_c, rc, False)
     assert_unknowns_close(lazy_x, rx, False)
+
+
+@pytest.mark.parametrize("double", [False, True])
+def test_sfs_marching_model_cost_equals_generic(built, double, monkeypatch):
+    """computeModelCost on the marching pipeline (MODE 4 of k_sfs_march: the cost pass on the linearised residuals) against the
+    generic per-site kernel: the LM trust-region decisions and every per-step cost must coincide, and both match the oracle."""
+    pr = make("sfs_quads", "LMGPU", double)
+    pr.solver["nIterations"] = 5
+    cm, xm, sol, _ = run_gpu(pr, timing=True)
+    assert sol.kernel_time("computeModelCost")[0] > 0
+    monkeypatch.setenv("OPTB200_GENERIC_MODEL_COST", "1")
+    cg, xg, _, _ = run_gpu(pr)
+    assert_costs_close(cm, cg, double, tol=1e-6 if not double else 1e-12)
+    assert_unknowns_close(xm, xg, double, tol=1e-5 if not double else 1e-11)
+    rc, rx, _ = run_oracle(pr)
+    assert_costs_close(cm, rc, double)
