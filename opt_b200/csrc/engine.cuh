@@ -378,8 +378,8 @@ __global__ void k_model_cost(F f, TileGrid tg, VecOf<F> delta, double* target) {
 }
 
 // PCGComputeCtC (solver:1042-1048): CtC = diag(J^T J) / radius
-template <class F>
-__global__ void k_compute_ctc(F f, TileGrid tg, VecOf<F> CtC, typename F::Scalar inv_radius) {
+template <class F, bool GENERIC = false>
+__global__ void k_compute_ctc(F f, TileGrid tg, VecOf<F> CtC, typename F::Scalar inv_radius) {   // GENERIC: always through evalJTF
     using T = typename F::Scalar;
     constexpr int U = F::U;
     int x, y, z; long s;
@@ -388,7 +388,8 @@ __global__ void k_compute_ctc(F f, TileGrid tg, VecOf<F> CtC, typename F::Scalar
         T g[U], d[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) g[u] = d[u] = T(0);
-        f.evalJTF(x, y, z, s, g, d);
+        if constexpr (F::HAS_DIAG_JTJ && !GENERIC) f.diagJTJ(x, y, z, s, d);
+        else f.evalJTF(x, y, z, s, g, d);
 #pragma unroll
         for (int u = 0; u < U; ++u) CtC(u, s) = d[u] * inv_radius;
     }
@@ -1709,7 +1710,8 @@ struct Engine : OptK_Plan {
             if (nIter == 0)                                  // PCGSaveSSq (solver:1052-1057), flat copy
                 OPTK_CUDA(cudaMemcpyAsync(SSq.d, pre.d, (size_t)U * Npad * sizeof(T), cudaMemcpyDeviceToDevice, stream));
             const T inv_radius = T(1) / radius;
-            this->launch_tiles("PCGComputeCtC", tg.n, sblock, k_compute_ctc<F>, f, tg, CtC, inv_radius);
+            if (getenv("OPTB200_GENERIC_CTC")) this->launch_tiles("PCGComputeCtC", tg.n, sblock, k_compute_ctc<F, true>, f, tg, CtC, inv_radius);
+            else this->launch_tiles("PCGComputeCtC", tg.n, sblock, k_compute_ctc<F, false>, f, tg, CtC, inv_radius);
             if (GRAPH) this->launch("PCGComputeCtC_Graph", edge_grid(), dim3(256), k_graph_ctc<F>, f, E, CtC, inv_radius);
             this->launch_tiles("PCGFinalizeDiagonal", tg.n, sblock, k_finalize_diagonal<F>, f, tg, CtC, SSq, pre, r, b, p, delta, radius, min_diag, max_diag, S(S_RZ0), S(S_Q));
             reduce(S_Q);
@@ -2014,6 +2016,7 @@ struct FunctorDefaults {
     static constexpr bool HAS_FAST_COST = false;         // ... and computeCost (fast_cost_kernel())
     static constexpr bool HAS_FAST_MODEL_COST = false;   // ... and computeModelCost (fast_model_cost_kernel())
     static constexpr bool HAS_FAST_PRECOMPUTE = false;   // ... and precompute (fast_precompute(stream, nsm))
+    static constexpr bool HAS_DIAG_JTJ = false;          // functors with diagJTJ(): diag(J^T J) alone, without the gradient (PCGComputeCtC)
     static constexpr bool SLAB_OK = true;                // grid functors whose bounds predicates survive a slab cut
     static constexpr bool HAS_GATHER = false;            // graph functors with a per-vertex gather form of J^T J p
     static constexpr bool HAS_SEGSCATTER = false;        // graph functors whose J^T J scatter runs as a segmented sum (graph_generic.cuh)

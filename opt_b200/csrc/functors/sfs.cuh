@@ -45,6 +45,7 @@ struct SfsFunctor : FunctorDefaults<T> {
     static constexpr bool HAS_FAST_COST = true;        // computeCost likewise (k_sfs_cost)
     static auto fast_cost_kernel();
     static constexpr bool HAS_FAST_MODEL_COST = true;  // computeModelCost likewise (k_sfs_model_cost, MODE 4 of the march)
+    static constexpr bool HAS_DIAG_JTJ = true;         // PCGComputeCtC without the gradient half of evalJTF (diagJTJ)
     static auto fast_model_cost_kernel();
     static constexpr bool HAS_FAST_PRECOMPUTE = true;  // one thread per quad of a row (k_sfs_precompute4)
     void fast_precompute(cudaStream_t stream, int nsm) const;
@@ -233,6 +234,40 @@ struct SfsFunctor : FunctorDefaults<T> {
         gg += a0 * acc[0] + a1 * acc[1] + acc[2];
         dd += an * k2;
         g[0] += gg; d[0] += dd;
+    }
+    // diag(J^T J) alone, in evalJTF's summation order: needs neither X nor B_I, only the gradient images and the weights
+    __device__ void diagJTJ(int x, int y, int, long s, T* d) const {
+        T dd = Di[s] > T(0) ? w_p * w_p : T(0);
+        const T b0 = G0[s], b1 = get(G1, x + 1, y), b2 = get(G2, x, y + 1);
+        // d r_h(c) / d X(s) = k_h(c) (dBI(c) - dBI(c + ex)) over the five centres touching X(s); likewise r_v
+        const T th[5] = {-b0, b0 - b1, b1, -b2, b2};
+        const int hx[5] = {x - 1, x, x + 1, x - 1, x}, hy[5] = {y, y, y, y + 1, y + 1};
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            const T k = inimg(hx[i], hy[i]) ? kh(hx[i], hy[i]) : T(0);
+            const T dr = k * th[i];
+            dd += dr * dr;
+        }
+        const T tv[5] = {-b0, b0 - b2, -b1, b1, b2};
+        const int vx[5] = {x, x, x + 1, x + 1, x}, vy[5] = {y - 1, y, y - 1, y, y + 1};
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            const T k = inimg(vx[i], vy[i]) ? kv(vx[i], vy[i]) : T(0);
+            const T dr = k * tv[i];
+            dd += dr * dr;
+        }
+        const T a0 = ax(x), a1 = ay(y), an = a0 * a0 + a1 * a1 + T(1);
+        const T k0 = ks(x, y);
+        T k2 = T(16) * k0 * k0;
+        const int ox[4] = {1, -1, 0, 0}, oy[4] = {0, 0, 1, -1};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int cx = x - ox[i], cy = y - oy[i];
+            if (!inimg(cx, cy)) continue;
+            const T k = ks(cx, cy);
+            k2 += k * k;
+        }
+        d[0] += dd + an * k2;
     }
     template <class P> __device__ void applyJTJ(int x, int y, int, long s, const P& p, T* out) const {
         PField<P> pf{this, &p};

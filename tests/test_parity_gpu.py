@@ -425,3 +425,18 @@ def test_sfs_marching_model_cost_equals_generic(built, double, monkeypatch):
     assert_unknowns_close(xm, xg, double, tol=1e-5 if not double else 1e-11)
     rc, rx, _ = run_oracle(pr)
     assert_costs_close(cm, rc, double)
+
+
+@pytest.mark.parametrize("double", [False, True])
+def test_sfs_diagonal_only_ctc_equals_generic(built, double, monkeypatch):
+    """PCGComputeCtC through SfsFunctor::diagJTJ (the diagonal of J^T J alone: gradient images and weights, no X / B_I loads, no
+    gradient) against the generic kernel that takes the diagonal out of evalJTF: same summation order, so the LM steps coincide."""
+    pr = make("sfs_quads", "LMGPU", double)
+    pr.solver["nIterations"] = 5
+    cd, xd, _, _ = run_gpu(pr)
+    monkeypatch.setenv("OPTB200_GENERIC_CTC", "1")
+    cg, xg, _, _ = run_gpu(pr)
+    assert_costs_close(cd, cg, double, tol=1e-6 if not double else 1e-12)
+    assert_unknowns_close(xd, xg, double, tol=1e-5 if not double else 1e-11)
+    rc, rx, _ = run_oracle(pr)
+    assert_costs_close(cd, rc, double)
