@@ -12,6 +12,21 @@ extern "C" {
 /* The reference never frees an Opt_State (createwrapper.t has no destructor); this one can be. */
 void OptB200_FreeState(Opt_State* state);
 
+/* ---- fatal errors -----------------------------------------------------------------------------
+ * The reference prints "Cuda reported error ..." and calls exit() on any CUDA failure (backend_cuda.t:26-40, 767-779), and
+ * so does this library as long as no handler is installed - drivers written for the reference see what they always saw.
+ * An application that must survive (a server, a host with its own clean-up) installs a handler: the failing call then unwinds
+ * to the C-ABI boundary, the handler is called once - (code, message, user): the cudaError_t value, 200 + ncclResult_t, or a
+ * small library code, with the text the reference would have printed - and the call returns: Opt_ProblemPlan returns NULL
+ * (everything allocated so far is released), Opt_ProblemInit / Step / Solve return at once (Step with 0),
+ * Opt_ProblemCurrentCost reads NaN and OptB200_PlanFailed 1.  A failed plan can only be freed (Opt_PlanFree); other plans are
+ * not affected unless the CUDA context itself is gone.  The handler may be called from any thread that calls into the library
+ * and must not call back into it, except OptB200_LastError. */
+typedef void (*OptB200_ErrorHandler)(int code, const char* message, void* user);
+void OptB200_SetErrorHandler(OptB200_ErrorHandler handler, void* user);   /* NULL restores print-and-exit */
+const char* OptB200_LastError(int* code);     /* the calling thread's most recent fatal error ("" if none); code may be NULL */
+int  OptB200_PlanFailed(Opt_Plan* plan);
+
 /* ---- multi-GPU domain decomposition (new; the reference is single-device) ---------------------
  * One process per GPU.  A 2-D / 3-D grid problem is cut into slabs along its slowest dimension
  * (d1 for 2-D, d2 for 3-D).  Each rank plans its LOCAL slab: its owned rows/planes plus `halo`

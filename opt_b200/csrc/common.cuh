@@ -6,16 +6,19 @@
 #include <cstring>
 #include <cmath>
 
-// Fatal-error convention of the reference: print and exit (backend_cuda.t:26-40, 767-779).
+// Fatal-error convention.  The reference prints and exits (backend_cuda.t:26-40, 767-779); a shared library that does so kills its
+// host application, so every fatal path goes through optk_fatal() (registry.cu).  With no handler installed
+// (OptB200_SetErrorHandler, include/OptB200.h) that is still the reference's behaviour: the message on stdout, then exit(code).
+// With a handler it throws optk::Fatal instead, which the extern "C" layer catches (optk_guard): the handler is called once with
+// the code and the message, the plan is marked failed, and that call and every later call on the plan return at once.
+namespace optk { struct Fatal { int code; }; }
+extern "C" void optk_fatal(int code, const char* fmt, ...) __attribute__((format(printf, 2, 3)));
 #define OPTK_CUDA(call)                                                                        \
     do {                                                                                       \
         cudaError_t e_ = (call);                                                               \
-        if (e_ != cudaSuccess) {                                                               \
-            printf("Cuda reported error %d: %s\nIn call: %s\nIn file: %s:%d\n", (int)e_,       \
-                   cudaGetErrorString(e_), #call, __FILE__, __LINE__);                         \
-            fflush(stdout);                                                                    \
-            exit((int)e_);                                                                     \
-        }                                                                                      \
+        if (e_ != cudaSuccess)                                                                 \
+            optk_fatal((int)e_, "Cuda reported error %d: %s\nIn call: %s\nIn file: %s:%d\n", (int)e_, \
+                       cudaGetErrorString(e_), #call, __FILE__, __LINE__);                     \
     } while (0)
 
 namespace optk {

@@ -142,7 +142,7 @@ void csr_ata_pattern(const CsrMat<T>& A, CsrMat<T>& ATA, int** rowOf_out, Scratc
     unsigned long long total = 0;
     OPTK_CUDA(cudaMemcpyAsync(&total, base + A.nrows, sizeof(total), cudaMemcpyDeviceToHost, st));
     OPTK_CUDA(cudaStreamSynchronize(st));
-    if (total >= (1ull << 31)) { printf("Opt: J^T J pattern needs %llu candidate pairs (more than 2^31): use the unfused materialized mode\n", total); fflush(stdout); exit(1); }
+    if (total >= (1ull << 31)) optk_fatal(1, "Opt: J^T J pattern needs %llu candidate pairs (more than 2^31): use the unfused materialized mode\n", total);
     unsigned long long *ka = nullptr, *kb = nullptr;
     OPTK_CUDA(cudaMalloc(&ka, (size_t)std::max<unsigned long long>(total, 1) * sizeof(unsigned long long)));
     OPTK_CUDA(cudaMalloc(&kb, (size_t)std::max<unsigned long long>(total, 1) * sizeof(unsigned long long)));

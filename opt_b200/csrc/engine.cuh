@@ -26,12 +26,9 @@
 #define OPTK_NCCL(call)                                                                        \
     do {                                                                                       \
         ncclResult_t r_ = (call);                                                              \
-        if (r_ != ncclSuccess) {                                                               \
-            printf("NCCL reported error %d: %s\nIn call: %s\nIn file: %s:%d\n", (int)r_,       \
-                   ncclGetErrorString(r_), #call, __FILE__, __LINE__);                         \
-            fflush(stdout);                                                                    \
-            exit(200 + (int)r_);                                                               \
-        }                                                                                      \
+        if (r_ != ncclSuccess)                                                                 \
+            optk_fatal(200 + (int)r_, "NCCL reported error %d: %s\nIn call: %s\nIn file: %s:%d\n", (int)r_, \
+                       ncclGetErrorString(r_), #call, __FILE__, __LINE__);                     \
     } while (0)
 
 // The C handle is the abstract base class of every Engine<F>.
@@ -58,6 +55,8 @@ struct OptK_Plan {
     virtual int set_slab(int rank, int nranks, int halo, const void* nccl_unique_id) = 0;
     virtual int set_materialized(int mode) = 0;          // 0 matrix-free, 1 J and J^T, 2 fused J^T J; returns the mode in effect
     virtual long materialized_nnz(int which) const = 0;   // 0 J, 1 J^T J
+
+    bool failed = false;          // a fatal error was reported to the installed handler: every later call returns at once
 
     // ---- launch bookkeeping shared by all engines -------------------------------------------
     cudaStream_t stream = nullptr;
@@ -1197,7 +1196,10 @@ struct Engine : OptK_Plan {
     bool xh_on = false; long long xh_epoch = 0;
     T* nb_pool[2] = {nullptr, nullptr}; long nb_npad[2] = {0, 0}; long nb_row[2] = {0, 0};
 
-    Engine(const unsigned* dims, bool is_lm, bool collect_timing) : lm(is_lm) {
+    explicit Engine(bool is_lm) : lm(is_lm) {}
+    // All allocation happens here, not in the constructor: if it fails part-way with an error handler installed (optk_fatal
+    // throws), make_engine deletes the object and the destructor releases what had been allocated.
+    void init(const unsigned* dims, bool collect_timing) {
         base_init(collect_timing);
         f.plan(dims);
         N = (long)f.W * f.H * f.D;
@@ -1540,9 +1542,7 @@ struct Engine : OptK_Plan {
         }
         OPTK_CUDA(cudaStreamSynchronize(stream));
         if (xr_on && *(const int*)(h_scal + 1) != 0) {
-            printf("Opt: a peer rank never arrived at a scalar all-reduce (rank %d of %d)\n", rank, nranks);
-            fflush(stdout);
-            exit(3);
+            optk_fatal(3, "Opt: a peer rank never arrived at a scalar all-reduce (rank %d of %d)\n", rank, nranks);
         }
         return h_scal[0];
     }
@@ -1885,7 +1885,7 @@ struct Engine : OptK_Plan {
                 cudaError_t e = cudaStreamQuery(stream);
                 if (e == cudaSuccess) {                      // stream drained: the mailbox must be visible now
                     if (__atomic_load_n(&lm_box[slot].seq, __ATOMIC_ACQUIRE) == expect) return true;
-                    printf("Opt: LM mailbox was not written (sequence %lld)\n", expect); fflush(stdout); exit(1);
+                    optk_fatal(1, "Opt: LM mailbox was not written (sequence %lld)\n", expect);
                 }
                 if (e != cudaErrorNotReady) OPTK_CUDA(e);
             }
@@ -2041,10 +2041,17 @@ struct FunctorDefaults {
     template <class V> __device__ void graphCtC(long, V, T) const {}
 };
 
+// new + init; a throw out of init (optk_fatal with an error handler installed) releases what init had allocated
+template <class Fn>
+OptK_Plan* build_engine(int is_lm, const unsigned* dims, int timing) {
+    auto* e = new Engine<Fn>(is_lm != 0);
+    try { e->init(dims, timing != 0); } catch (...) { delete e; throw; }
+    return e;
+}
 template <template <class> class F>
 OptK_Plan* make_engine(int is_double, int is_lm, const unsigned* dims, int timing) {
-    if (is_double) return new Engine<F<double>>(dims, is_lm != 0, timing != 0);
-    return new Engine<F<float>>(dims, is_lm != 0, timing != 0);
+    if (is_double) return build_engine<F<double>>(is_lm, dims, timing);
+    return build_engine<F<float>>(is_lm, dims, timing);
 }
 
 }  // namespace optk

@@ -6,6 +6,6 @@
 
 extern "C" OptK_Plan* optk_make_volumetric_mesh_deformation(int is_double, int is_lm, const unsigned* dims, int timing) {
     if (!is_double && dims[0] % 32 == 0 && getenv("OPTB200_VOL_SCALAR") == nullptr)
-        return new optk::Engine<optk::VolumetricPackedFunctor<float>>(dims, is_lm != 0, timing != 0);
+        return optk::build_engine<optk::VolumetricPackedFunctor<float>>(is_lm, dims, timing);
     return optk::make_engine<optk::VolumetricScalarFunctor>(is_double, is_lm, dims, timing);
 }

@@ -179,6 +179,13 @@ void Opt_SetSolverParameter(Opt_State* state, Opt_Plan* plan, const char* name, 
     logSolver(plan, "Warning: tried to set nonexistent solver parameter %s\n", name);
 }
 
+/* After a fatal error that was handed to the application's handler (OptB200_SetErrorHandler) the plan is dead: the engine
+ * calls below do nothing, so end the solve here - no "final cost" line, the current cost reads as NaN. */
+static int plan_failed(Opt_Plan* plan) {
+    if (!optk_failed(plan->k)) return 0;
+    plan->prevCost = NAN;
+    return 1;
+}
 void Opt_ProblemInit(Opt_State* state, Opt_Plan* plan, void** problemparams) {
     (void)state;
     OptK_Plan* k = plan->k;
@@ -197,6 +204,7 @@ void Opt_ProblemInit(Opt_State* state, Opt_Plan* plan, void** problemparams) {
     }
     optk_precompute(k);
     plan->prevCost = optk_cost(k);
+    (void)plan_failed(plan);
     /* the reference launches one more PCGInit1 here whose results the first Step overwrites
        (solver:1886); it has no observable effect and is not replayed */
     optk_end_call(k);
@@ -220,6 +228,7 @@ int Opt_ProblemStep(Opt_State* state, Opt_Plan* plan, void** problemparams) {
 static int problem_step(Opt_Plan* plan, void** problemparams) {
     OptK_Plan* k = plan->k;
     SolverParameters* sp = &plan->sp;
+    if (plan_failed(plan)) return 0;
     optk_begin_call(k);
     optk_bind(k, problemparams); /* solver:2001: the caller may change pointers/scalars between steps */
     if (sp->nIter >= sp->nIterations) {
@@ -271,6 +280,7 @@ static int problem_step(Opt_Plan* plan, void** problemparams) {
     optk_linear_update(k);
     optk_precompute(k);
     double newCost = optk_cost(k);
+    if (plan_failed(plan)) return 0;
 
     if (plan->is_lm) { /* solver:2240-2300 */
         double cost_change = of(plan, plan->prevCost - newCost);
@@ -324,6 +334,9 @@ double Opt_ProblemCurrentCost(Opt_State* state, Opt_Plan* plan) { /* solver:2354
 }
 
 /* ---- OptB200.h extensions (no counterpart in the reference) -------------------------------- */
+void OptB200_SetErrorHandler(OptB200_ErrorHandler handler, void* user) { optk_set_error_handler(handler, user); }
+const char* OptB200_LastError(int* code) { return optk_last_error(code); }
+int OptB200_PlanFailed(Opt_Plan* plan) { return plan ? optk_failed(plan->k) : 1; }
 void OptB200_GetNcclUniqueId(void* out128) { optk_nccl_unique_id(out128); }
 int OptB200_PlanSetSlab(Opt_Plan* plan, int rank, int nranks, int halo, const void* nccl_unique_id) {
     return optk_set_slab(plan->k, rank, nranks, halo, nccl_unique_id);

@@ -58,6 +58,13 @@ void   optk_nccl_unique_id(void* out128);
 int    optk_set_materialized(OptK_Plan*, int mode);
 long   optk_materialized_nnz(OptK_Plan*, int which);   /* 0: nnz(J), 1: nnz(J^T J) */
 
+/* Fatal errors (common.cuh): with no handler a CUDA / NCCL failure prints and exits as in the reference (backend_cuda.t:26-40);
+ * with one, the failing call unwinds to this layer, the handler is called once with the error code and message, the plan is
+ * marked failed (optk_failed) and every later call on it returns at once (costs read as NaN, counts as 0, status as -1). */
+void   optk_set_error_handler(void (*handler)(int code, const char* message, void* user), void* user);
+const char* optk_last_error(int* code);       /* message (and code) of the calling thread's most recent fatal error; "" if none */
+int    optk_failed(OptK_Plan*);
+
 /* statistics and debugging */
 long   optk_launch_count(OptK_Plan*);         /* kernels launched since creation */
 void   optk_print_timing(OptK_Plan*);         /* Kernel | Count | Total | Average table (backend_cuda.t:152-297) */

@@ -61,7 +61,37 @@ def load_library():
         _lib.OptB200_DebugReadVectorRange.argtypes = [P, C.c_char_p, C.c_long, C.c_long, P]
         _lib.OptB200_DebugApplyJTJ.argtypes = [P, C.POINTER(P), P, P]
         _lib.OptB200_DebugPcgBegin.argtypes = [P, C.POINTER(P)]
+        _lib.OptB200_SetErrorHandler.argtypes = [P, P]
+        _lib.OptB200_LastError.restype = C.c_char_p
+        _lib.OptB200_LastError.argtypes = [C.POINTER(C.c_int)]
+        _lib.OptB200_PlanFailed.restype = C.c_int
+        _lib.OptB200_PlanFailed.argtypes = [P]
     return _lib, _fn
+
+
+ERROR_HANDLER = C.CFUNCTYPE(None, C.c_int, C.c_char_p, C.c_void_p)
+_handler_keepalive = None
+
+
+def set_error_handler(fn):
+    """OptB200_SetErrorHandler: fn(code, message) is called once per fatal CUDA / NCCL error and the failing call returns
+    instead of the process exiting (include/OptB200.h); None restores the reference's print-and-exit."""
+    global _handler_keepalive
+    lib, _ = load_library()
+    if fn is None:
+        lib.OptB200_SetErrorHandler(None, None)
+        _handler_keepalive = None
+        return
+    cb = ERROR_HANDLER(lambda code, msg, user: fn(int(code), (msg or b"").decode(errors="replace")))
+    lib.OptB200_SetErrorHandler(C.cast(cb, C.c_void_p), None)
+    _handler_keepalive = cb
+
+
+def last_error():
+    lib, _ = load_library()
+    code = C.c_int(0)
+    msg = lib.OptB200_LastError(C.byref(code))
+    return code.value, (msg or b"").decode(errors="replace")
 
 
 class NamedParameters:
@@ -164,6 +194,10 @@ class OptSolver:
         return self.current_cost()
 
     # --- OptB200.h extensions --------------------------------------------------------------------
+    def failed(self):
+        """1 after a fatal error on this plan was handed to the installed error handler."""
+        return self.lib.OptB200_PlanFailed(self.plan)
+
     def launch_count(self):
         return self.lib.OptB200_PlanLaunchCount(self.plan)
 

@@ -31,6 +31,12 @@ CASES = {
     "cotangent": (examples.cotangent_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
     "robust": (examples.robust_synthetic, (12, 10), dict(n_iter=3, l_iter=10)),
     "intrinsic": (examples.intrinsic_synthetic, (43, 29), dict(n_iter=3, l_iter=10)),
+    # Well-conditioned variants of the two cases whose fp32 gates are widened below (the fp32 and fp64 ORACLE runs themselves
+    # differ by more than the standard gate on those): the same code paths, held to the standard gates on every step.
+    # pNorm = 1.6: the re-weighting exponent is -0.4 instead of -1.2; interior rings on an equilateral lattice: no triangle of
+    # nearly collinear edge vectors.
+    "intrinsic_p16": (examples.intrinsic_synthetic, (43, 29), dict(n_iter=4, l_iter=10, pnorm=1.6)),
+    "cotangent_interior": (examples.cotangent_synthetic, (12, 10), dict(n_iter=3, l_iter=10, interior_rings=True)),
 }
 
 
@@ -53,7 +59,9 @@ def test_solve_matches_oracle(built, case, kind, double):
         # nonlinear step (lib.t:112-121) and the albedo prior drives |r_c - r_n| towards 0, so from the second
         # step on the weights amplify the rounding of r (and the last-ulp differences between the device's and
         # libm's pow) by 1.2 / |r_c - r_n|.  The first step holds BASELINE's gates (1e-4 fp32 / 1e-9 fp64); the
-        # re-weighted steps are held to 2e-2 (fp32) and 1e-7 (fp64).
+        # re-weighted steps are held to 2e-2 (fp32) and 1e-7 (fp64).  That is the conditioning of the energy at the driver's
+        # pNorm = 0.8, not of this implementation: the ORACLE's own fp32 and fp64 runs of this case are 9.5e-3 and 1.3e-2 apart
+        # after steps 2 and 3.  "intrinsic_p16" runs the same code at pNorm = 1.6 and holds the standard gates on every step.
         assert_costs_close(gc[:2], rc[:2], double)
         assert_costs_close(gc[2:], rc[2:], double, tol=1e-7 if double else 2e-2)
         assert_unknowns_close(gx, rx, double, tol=1e-6 if double else 2e-2)
@@ -85,7 +93,8 @@ def test_jtf_and_jtj_match_oracle(built, case, double):
     tol = OP_RTOL[double]
     if case == "cotangent" and not double:
         # disc = (a.a)(b.b) - (a.b)^2 of the wrapped boundary rings is a catastrophic cancellation in fp32 (nearly
-        # collinear unit vectors): closed form and dual numbers round differently there; fp64 agrees to 1e-12
+        # collinear unit vectors): closed form and dual numbers round differently there; fp64 agrees to 1e-12.  The oracle's
+        # own fp32 and fp64 evaluations of J^T F differ by 5.5e-5 on this mesh; "cotangent_interior" (no wrapped rings) holds 2e-5
         tol = 5e-4
     assert np.abs(r_gpu - r_ref).max() <= tol * np.abs(r_ref).max()
     assert np.abs(pre_gpu - pre_ref).max() <= tol * np.abs(pre_ref).max()
