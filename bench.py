@@ -24,7 +24,9 @@ cut into N slabs of planes.  The other BASELINE configurations are selected with
              times is repeated on the GPU with the same iteration counts (cost and unknowns compared), and for
              workloads whose full-size oracle solve does not fit the time budget (512^3) the operators
              r = -J^T F, the preconditioner and J^T J p of the FULL-SIZE plan are read back on sampled plane
-             ranges and compared with the oracle evaluated on those sub-volumes.
+             ranges and compared with the oracle evaluated on those sub-volumes.  N > 1 (strong-scaled 3-D default): the
+             same operator check on every rank's slab, including the owned planes next to the ghost planes, worst rank
+             reported; each rank runs on the CPUs next to its GPU (NVML affinity) so its staging buffers are NUMA-local.
   cpu_baseline  the CPU oracle (a port of the reference's backend_cpu/_mt path; the reference
              itself is Terra and cannot be built here) timed on this box's host cores.
 """
@@ -304,6 +306,30 @@ def run_reference(args, w):
 
 
 # ------------------------------------------------------------------------------ GPU arm
+def bind_near_gpu(index):
+    """N > 1: run this rank on the CPUs NVML names as local to its GPU, before any pinned buffer is allocated, so that the
+    end-to-end leg's staging memory is first-touched on the NUMA node the GPU's PCIe root hangs off (eight ranks staging
+    through one node's memory is what limited r1's end-to-end curve).  Returns the CPU count, or None if NVML has no answer."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:                                  # CUDA's ordinal need not be NVML's: go through the PCI address
+            import torch
+            pp = torch.cuda.get_device_properties(index)
+            h = pynvml.nvmlDeviceGetHandleByPciBusId(("%08x:%02x:%02x.0" % (pp.pci_domain_id, pp.pci_bus_id, pp.pci_device_id)).encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
 def run_ours(args, pr, w, rank, world, mode):
     import torch
     import torch.distributed as dist
@@ -311,6 +337,7 @@ def run_ours(args, pr, w, rank, world, mode):
 
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0)))
     torch.cuda.set_device(dev)
+    numa = bind_near_gpu(dev.index or 0) if world > 1 else None
     img_idx = [i for i, p in enumerate(pr.params) if isinstance(p, np.ndarray)]
     host = {i: torch.from_numpy(pr.params[i]).pin_memory() for i in img_idx}
     devt = {i: host[i].to(dev, non_blocking=True) for i in img_idx}
@@ -514,9 +541,22 @@ def run_ours(args, pr, w, rank, world, mode):
     # global iteration; strong slab: the global grid IS the single-GPU grid.
     mult = 1 if mode == "strong" else world
     value = mult * iters * args.steps / (ms * 1e-3)
+    slab_parity = None
+    if mode == "strong" and world > 1 and not args.no_cpu and len(pr.dims) == 3:
+        # N > 1: the full-size operator check on every rank's slab, worst rank reported (the whole-solve parity of the slab
+        # paths against the oracle is tests/test_multigpu.py's job; the final cost below is the N = 1 run's to the last digit)
+        local = operator_parity_3d(S, sol, named, pr, devt, pristine, max(1, min(host_threads(), (os.cpu_count() or world) // world)), bottom=rank == 0, top=rank == world - 1)
+        t = torch.tensor([local["max_rel_err_p0"], local["max_rel_err_pre"], local["max_rel_err_JTJp"]], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        worst = [float(v) for v in t.tolist()]
+        slab_parity = {"iters": None, "problem": "every rank's slab of the full-size workload (max over %d ranks)" % world,
+                       "full_size_operators": {"what": local["what"], "gate": local["gate"], "max_rel_err_p0": worst[0],
+                                               "max_rel_err_pre": worst[1], "max_rel_err_JTJp": worst[2],
+                                               "planes_rank0": local["planes"], "ok": bool(max(worst) <= local["gate"])},
+                       "ok": bool(max(worst) <= local["gate"])}
     if rank != 0:
         return
-    cpu, parity = None, None
+    cpu, parity = None, slab_parity
     if not args.no_cpu and world == 1:
         threads = host_threads()
         spr, frac, what = sample_problem(args.workload, "cpu_sample", args.size)
@@ -558,6 +598,7 @@ def run_ours(args, pr, w, rank, world, mode):
         "e2e": {"value": mult * iters * e2e_steps / (ms_e2e * 1e-3),
                 "unit": "PCG iters/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / e2e_steps, "final_cost": cost_e2e, "cold_solve_ms": ms_cold,
+                "host_cpus_bound": numa,          # N > 1: rank 0's CPU set after binding next to its GPU (staging buffers NUMA-local)
                 "note": "pipeline throughput: step k+1's upload and step k-1's download overlap step k's solve; cold_solve_ms is one "
                         "un-overlapped upload + solve + download"},
         "gpu_launches": launches,
@@ -595,12 +636,14 @@ def solve_parity(S, spr, l_iter, ocosts, solved):
             "costs_gpu": gcosts, "costs_oracle": list(ocosts), "gate": gate, "ok": ok}
 
 
-def operator_parity_3d(S, sol, named, pr, devt, pristine, threads, planes=6):
+def operator_parity_3d(S, sol, named, pr, devt, pristine, threads, planes=6, bottom=True, top=True):
     """FULL-SIZE check of a 3-D workload whose oracle solve does not fit the time budget: the full-size plan runs one PCG
     iteration from the initial unknowns; p0 = M^-1 (-J^T F), M^-1 and Ap = J^T J p0 are read back on three ranges of
     `planes` planes (bottom, middle, top of the volume) and compared with the oracle evaluated on those sub-volumes
     (r, the preconditioner and J^T J p are local: radius-1 stencils, so a plane that has both its z-neighbours inside
-    the sub-volume -- or lies on the boundary of the full grid -- is exact)."""
+    the sub-volume -- or lies on the boundary of the full grid -- is exact).  In slab mode (N > 1) every rank calls this on its
+    own slab (the solve inside is collective); bottom / top say whether the slab's first / last plane is the boundary of the
+    full grid or a ghost plane, which - like every other plane without both neighbours in the sub-volume - is left out."""
     from oracle_api import OracleSolver
     import torch
     W, H, D = [int(d) for d in pr.dims]
@@ -631,8 +674,8 @@ def operator_parity_3d(S, sol, named, pr, devt, pristine, threads, planes=6):
         o.close()
         U = p0.shape[1]
         r_ref, pre_ref, ap_ref = r_ref.reshape(-1, U), pre_ref.reshape(-1, U), ap_ref.reshape(-1, U)
-        lo = 0 if za == 0 else 1                       # first / last plane of the sub-volume miss a z-neighbour unless
-        hi = (zb - za) if zb == D else (zb - za - 1)    # they are the boundary of the full grid
+        lo = 0 if (za == 0 and bottom) else 1                     # first / last plane of the sub-volume miss a z-neighbour unless
+        hi = (zb - za) if (zb == D and top) else (zb - za - 1)     # they are the boundary of the full grid
         sl = slice(lo * plane, hi * plane)
         p0_ref = (pre_ref * r_ref).astype(dt)
         e_p = float(np.abs(p0[sl] - p0_ref[sl]).max() / np.abs(p0_ref[sl]).max())
