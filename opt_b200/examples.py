@@ -590,6 +590,20 @@ def embedded_golden(npz, n_iter=1, l_iter=1):
                    {"nIterations": n_iter, "lIterations": l_iter})
 
 
+def embedded_outer_constraints(pr, i, n_outer):
+    """The Constraints image of outer iteration i of n_outer (CombinedSolver.h:57-60, 75-93: alpha = (i + 1) / n_outer in float,
+    z = (1 - alpha) pt + alpha target with pt the INITIAL position of the marker vertex - m_result is only refreshed after the
+    last outer iteration).  `pr` is embedded_golden()'s problem, whose params[6] are the alpha = 1 targets and params[5] the
+    initial positions; the unknowns (params[3], params[4]) carry over from one outer iteration to the next."""
+    f32 = np.float32
+    tgt, v = np.asarray(pr.params[6]), np.asarray(pr.params[5])
+    con = np.isfinite(tgt[:, 0])
+    a = f32(i + 1) / f32(n_outer)
+    z = tgt.astype(f32).copy()
+    z[con] = ((f32(1) - a) * v[con].astype(f32) + a * tgt[con].astype(f32)).astype(f32)
+    return z.astype(tgt.dtype)
+
+
 def sqrt3_subdivide(v, faces):
     """One step of Kobbelt's sqrt(3) subdivision on a closed triangle mesh, as the reference's ARAP driver applies it
     before solving (examples/arap_mesh_deformation/src/main.cpp:65-81, OpenMesh Sqrt3T with numSubdivides = 1):

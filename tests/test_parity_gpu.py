@@ -297,6 +297,31 @@ def test_reference_long_run_cost(built, golden_dir, name):
     assert sol.pcg_iterations() == kw["n_iter"] * kw["l_iter"]
 
 
+def test_embedded_31_outer_iterations(built, golden_dir):
+    """examples/test_example_output.py:63,112: embedded_mesh_deformation --oIterations 31 --nIterations 5 --lIterations 125,
+    recorded 0.0944651290 (niessner/Opt CUDA).  That figure is the final cost of the LAST outer iteration (markers moved all the
+    way); the oracle reaches 0.09448624 in fp32 and 0.09448626 in fp64 there (tests/test_oracle_golden.py, slow case), 2.2e-4
+    from the recorded value with no sensitivity to precision or to the initial rotation - so this anchor is held to 5e-4 against
+    the recorded figure, not to the reference's 1e-5, and to 1e-4 against the oracle's value."""
+    import torch
+    from opt_b200 import solver as S
+    from test_oracle_golden import EMBEDDED_31_ORACLE, EMBEDDED_31_RECORDED
+    pr = examples.embedded_golden(np.load(os.path.join(golden_dir, "embedded_raptor2k.npz")), n_iter=5, l_iter=125)
+    targets = [examples.embedded_outer_constraints(pr, i, 31) for i in range(31)]
+    named = S.upload(pr)
+    sol = S.OptSolver(pr.dims, pr.energy, pr.kind)
+    last = None
+    for z in targets:
+        named.values[6].copy_(torch.from_numpy(z))
+        costs = []
+        sol.solve(pr.solver, named, costs)
+        last = costs
+    torch.cuda.synchronize()
+    assert sol.pcg_iterations() == 31 * 5 * 125
+    assert abs(last[-1] - EMBEDDED_31_ORACLE) <= 1e-4 * EMBEDDED_31_ORACLE, last
+    assert abs(last[-1] - EMBEDDED_31_RECORDED) <= 5e-4 * EMBEDDED_31_RECORDED, last
+
+
 TINY = [("poisson", examples.poisson_synthetic, s) for s in [(4, 1), (1, 5), (4, 4), (8, 2), (12, 3), (5, 2)]] + \
        [("optical_flow", examples.optical_flow_synthetic, s) for s in [(4, 3), (8, 2), (4, 2)]] + \
        [("image_warping", examples.image_warping_synthetic, s) for s in [(3, 3), (4, 2), (2, 5)]] + \
