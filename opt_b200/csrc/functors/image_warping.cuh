@@ -17,7 +17,25 @@ struct ImageWarpingFunctor : FunctorDefaults<T> {
     int W, H, D;
     T* O; T* A; const T* Ur; const T* Cn; const T* M;
     T w_fit, w_reg;
-    void plan(const unsigned* d) { W = d[0]; H = d[1]; D = 1; }
+    // (sin A, cos A) per pixel, refreshed by precompute (once per nonlinear iteration, ghost rows included).  J^T J p reads the
+    // rotation of the site and of its four neighbours: five sincos per site and PCG iteration made the generic kernel
+    // arithmetic-bound on the 512^2 configuration (14.8 us per launch on an L2-resident problem); with the table it is five
+    // 8-byte loads.  Same sincos_t, same operands, so the values are the ones the inline form computes (OPTB200_IW_SINCOS=1 at plan
+    // time restores it; tests compare both).
+    T* SC = nullptr;
+    bool use_table = true;
+    static constexpr bool HAS_PRECOMPUTE = true;
+    void plan(const unsigned* d) { W = d[0]; H = d[1]; D = 1; use_table = getenv("OPTB200_IW_SINCOS") == nullptr; }
+    void alloc_temporaries(cudaStream_t) { OPTK_CUDA(cudaMalloc(&SC, (size_t)2 * round_up((long)W * H, 64) * sizeof(T))); }
+    void free_temporaries() { cudaFree(SC); SC = nullptr; }
+    __device__ void precompute(int, int, int, long s) const {
+        T sc[2]; sincos_t(A[s], sc[0], sc[1]);
+        store2(SC + s * 2, sc);
+    }
+    __device__ __forceinline__ void rotation(long s, T& sa, T& ca) const {
+        if (use_table) { T sc[2]; load2(SC + s * 2, sc); sa = sc[0]; ca = sc[1]; }
+        else sincos_t(A[s], sa, ca);
+    }
     void bind(void** pp) {
         O = (T*)pp[0]; A = (T*)pp[1]; Ur = (const T*)pp[2]; Cn = (const T*)pp[3]; M = (const T*)pp[4];
         w_fit = (T) * (const float*)pp[5]; w_reg = (T) * (const float*)pp[6];
@@ -53,7 +71,7 @@ struct ImageWarpingFunctor : FunctorDefaults<T> {
     }
     __device__ void evalJTF(int x, int y, int, long s, T* g, T* d) const {
         T oi[2], ui[2], ci[2]; load2(O + s * 2, oi); load2(Ur + s * 2, ui); load2(Cn + s * 2, ci);
-        T sa, ca; sincos_t(A[s], sa, ca);
+        T sa, ca; rotation(s, sa, ca);
         const T wf2 = w_fit * w_fit, wr2 = w_reg * w_reg;
         if (ci[0] >= T(0) && ci[1] >= T(0)) {
             g[0] += wf2 * (oi[0] - ci[0]); g[1] += wf2 * (oi[1] - ci[1]);
@@ -61,7 +79,7 @@ struct ImageWarpingFunctor : FunctorDefaults<T> {
         }
         neighbours(x, y, s, [&](long n) {
             T on[2], un[2]; load2(O + n * 2, on); load2(Ur + n * 2, un);
-            T sn, cn; sincos_t(A[n], sn, cn);
+            T sn, cn; rotation(n, sn, cn);
             T u[2] = {ui[0] - un[0], ui[1] - un[1]}, Ru[2], Dv[2], Rnu[2], Dn[2];
             rot(sa, ca, u, Ru, Dv); rot(sn, cn, u, Rnu, Dn);
             T din[2] = {(oi[0] - on[0]) - Ru[0], (oi[1] - on[1]) - Ru[1]};          // d(i,n)
@@ -103,13 +121,13 @@ struct ImageWarpingFunctor : FunctorDefaults<T> {
     }
     template <class P> __device__ void applyJTJ(int x, int y, int, long s, const P& p, T* out) const {
         T ui[2], ci[2]; load2(Ur + s * 2, ui); load2(Cn + s * 2, ci);
-        T sa, ca; sincos_t(A[s], sa, ca);
+        T sa, ca; rotation(s, sa, ca);
         const T wf2 = w_fit * w_fit, wr2 = w_reg * w_reg;
         const T p0 = p(0, s), p1 = p(1, s), pa = p(2, s);
         T a0 = T(0), a1 = T(0), a2 = T(0);
         neighbours(x, y, s, [&](long n) {
             T un[2]; load2(Ur + n * 2, un);
-            T sn, cn; sincos_t(A[n], sn, cn);
+            T sn, cn; rotation(n, sn, cn);
             T u[2] = {ui[0] - un[0], ui[1] - un[1]}, Ru[2], Dv[2], Rnu[2], Dn[2];
             rot(sa, ca, u, Ru, Dv);
             T um[2] = {-u[0], -u[1]}; rot(sn, cn, um, Rnu, Dn);                     // D_ni = -R'(A_n)(U_n - U_i)

@@ -10,6 +10,8 @@ __device__ __forceinline__ void sincos_t(double a, double& s, double& c) { sinco
 // AoS element loads (caller arrays are AoS per element, x fastest; o.t:564-579)
 __device__ __forceinline__ void load2(const float* p, float* o) { float2 v = *reinterpret_cast<const float2*>(p); o[0] = v.x; o[1] = v.y; }
 __device__ __forceinline__ void load2(const double* p, double* o) { double2 v = *reinterpret_cast<const double2*>(p); o[0] = v.x; o[1] = v.y; }
+__device__ __forceinline__ void store2(float* p, const float* v) { *reinterpret_cast<float2*>(p) = make_float2(v[0], v[1]); }
+__device__ __forceinline__ void store2(double* p, const double* v) { *reinterpret_cast<double2*>(p) = make_double2(v[0], v[1]); }
 __device__ __forceinline__ void load4(const float* p, float* o) { float4 v = *reinterpret_cast<const float4*>(p); o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w; }
 __device__ __forceinline__ void load4(const double* p, double* o) {
     double2 a = reinterpret_cast<const double2*>(p)[0], b = reinterpret_cast<const double2*>(p)[1];

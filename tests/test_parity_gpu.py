@@ -474,3 +474,20 @@ def test_sfs_diagonal_only_ctc_equals_generic(built, double, monkeypatch):
     assert_unknowns_close(xd, xg, double, tol=1e-5 if not double else 1e-11)
     rc, rx, _ = run_oracle(pr)
     assert_costs_close(cd, rc, double)
+
+
+@pytest.mark.parametrize("double", [False, True])
+@pytest.mark.parametrize("kind", ["gaussNewtonGPU", "LMGPU"])
+def test_image_warping_rotation_table_equals_inline_sincos(built, kind, double, monkeypatch):
+    """image_warping reads (sin A, cos A) of a site and its neighbours from a per-pixel table refreshed by precompute; with
+    OPTB200_IW_SINCOS=1 (read at plan time) J^T F and J^T J p evaluate sincos inline as before.  Same function on the same
+    operands: the solves must coincide, and both match the oracle."""
+    pr = make("image_warping", kind, double)
+    ct, xt, _, _ = run_gpu(pr)
+    monkeypatch.setenv("OPTB200_IW_SINCOS", "1")
+    ci, xi, _, _ = run_gpu(pr)
+    assert_costs_close(ct, ci, double, tol=1e-6 if not double else 1e-12)
+    assert_unknowns_close(xt, xi, double, tol=1e-5 if not double else 1e-11)
+    rc, rx, _ = run_oracle(pr)
+    assert_costs_close(ct, rc, double)
+    assert_unknowns_close(xt, rx, double)
